@@ -188,6 +188,15 @@ void       qwen_tts_cuda_set_params(qtc_ctx_t *ctx, const qtc_gen_params_t *p);
 void       qwen_tts_cuda_get_perf(const qtc_ctx_t *ctx, qtc_perf_t *out);
 /* 0: separate kernels per op (baseline)  1: fused persistent decode kernels (default) */
 int        qwen_tts_cuda_set_mode(qtc_ctx_t *ctx, int mode);
+/* Arithmetic of the talker / sub-talker path.
+ * 0 (default): fp32 with FMA and tree reductions - weight-streaming speed; differs from the C path by
+ *    fp32 summation order only (logits within ~1e-5 relative).
+ * 1: "strict" - every sum in the reference's order (k ascending, multiply then add, no FMA; expf by
+ *    glibc's algorithm): logits, hidden states and therefore sampled tokens are BIT-IDENTICAL to the
+ *    non-BLAS C build.  Slower: one dependent add per weight column. */
+int        qwen_tts_cuda_set_arith(qtc_ctx_t *ctx, int strict);
+/* the same switch for the kernel-level entry points below */
+int        qwen_tts_cuda_kernel_arith(int strict);
 
 /* ---- stage API: same host-visible semantics as c/qwen_tts.h:483-502 ------- */
 /* resets nothing: caller sets kv_len=0 via _reset() like c/qwen_tts.c:1249 */

@@ -1,0 +1,159 @@
+/*
+ * qtc_internal.h - host-side view of the device-resident model and state.
+ * Layout in HBM is described in DESIGN.md section 3.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/qwen_tts_cuda.h"
+
+/* ---- error plumbing -------------------------------------------------------- */
+void qtc_set_error(const char *fmt, ...);
+#define QTC_CUDA(call)                                                                         \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            qtc_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return -1;                                                                         \
+        }                                                                                      \
+    } while (0)
+#define QTC_CUDA_NULL(call)                                                                    \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            qtc_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return NULL;                                                                       \
+        }                                                                                      \
+    } while (0)
+
+/* ---- device-side descriptors (plain structs, passed by value or by pointer) - */
+struct LmLayerDev {
+    const uint16_t *wq, *wk, *wv, *wo, *gate, *up, *down;   /* bf16, row-major as in the reference */
+    const float *q_norm, *k_norm, *in_norm, *post_norm;
+};
+struct LmDev {
+    int vocab, hidden, inter, layers, heads, kv_heads, head_dim;
+    float eps, theta;
+    LmLayerDev layer[QTC_MAX_LM_LAYERS];
+    const float *final_norm;
+};
+
+/* per-utterance generation state, resident in HBM so that a captured CUDA graph
+ * can be replayed without host-side argument patching */
+struct GenState {
+    int pos;          /* talker KV length (ctx->talker_kv_len)                      */
+    int step;         /* frames generated so far (n_generated)                      */
+    int done;         /* 0 running, 1 EOS, 2 budget reached                          */
+    int stop_step;
+    uint32_t rng;     /* talker RNG: bit pattern of (float)seed, c/qwen_tts.c:1270   */
+    int token;        /* last sampled codebook-0 token                               */
+    int limit;        /* frame budget of this call                                   */
+    int fixed;        /* fixed_codec_tokens > 0                                      */
+    int n_trailing;   /* rows in trailing_text                                       */
+    int pad_[7];
+};
+
+struct SampleCfg {
+    int vocab, top_k;
+    float top_p, temperature;
+    int suppress_from, eos_id;        /* suppress [suppress_from, vocab) except eos_id; -1 = none */
+    float rep_penalty;                /* 1.0 = off */
+};
+
+/* one decoder stack's mutable buffers */
+struct LmBuffers {
+    float *k, *v;                 /* [layers, kv_max, kv_heads*head_dim] f32 */
+    int kv_max;
+    float *cos, *sin;             /* [kv_max, head_dim], host-computed with the oracle's expression */
+    float *x, *xn, *q, *kk, *vv, *att, *g, *logits;
+};
+
+struct CodecDev;   /* qtc_codec.cu */
+
+struct qtc_ctx {
+    qtc_model_desc_t host;        /* dims + host pointers as given (pointers not used after upload) */
+    LmDev talker, sub;
+    int H, G;
+    /* device copies of non-layer tensors */
+    const uint16_t *codec_embedding, *text_embedding, *text_fc1_w, *text_fc2_w, *codec_head;
+    const float *text_fc1_b, *text_fc2_b;
+    const uint16_t *sub_emb[QTC_MAX_GROUPS - 1], *sub_head[QTC_MAX_GROUPS - 1];
+    const uint16_t *sub_in_w;
+    const float *sub_in_b;
+    LmBuffers tk, st;
+    /* generation */
+    GenState *state;              /* device */
+    GenState *state_host;         /* pinned mirror */
+    int *hist_count;              /* [talker.vocab] occurrences of each token in the history */
+    int *frame_codes;             /* [QTC_MAX_GROUPS] device: codes of the frame in flight */
+    int *codes;                   /* [codes_cap, G] device */
+    int codes_cap;
+    int *codes_host;              /* pinned */
+    float *next_embed;            /* [H] */
+    float *trailing;              /* [trailing_cap, H] */
+    int trailing_cap;
+    float *tts_pad;               /* [H] */
+    float *prefill;               /* [prefill_cap, H] */
+    int prefill_cap;
+    float *st_embed, *st_proj;    /* sub-talker input staging */
+    float *text_tmp0, *text_tmp1; /* text projection staging [text_hidden] */
+    uint32_t *st_rng;             /* sub-talker RNG (re-seeded every frame) */
+    int *zero_pos;                /* device int, always 0: position base of the sub-talker */
+    int *sample_scratch;          /* slow-path sampler scratch */
+    float *sample_scratch_f;
+    float *host_stage;            /* pinned staging for stage-API vectors */
+    size_t host_stage_bytes;
+    CodecDev *codec;
+    qtc_gen_params_t params;
+    qtc_perf_t perf;
+    int mode;                     /* 0 per-op kernels, 1 fused persistent kernels */
+    int arith;                    /* QTC_FAST / QTC_STRICT */
+    cudaStream_t stream;
+    cudaEvent_t ev0, ev1;
+    std::vector<void *> allocs;   /* everything cudaMalloc'd, for release() */
+    long long launches;
+    /* CUDA graphs of the frame loop (built lazily, keyed by params) */
+    cudaGraphExec_t g_front, g_talker;
+    int graph_key;
+    int max_batch;
+};
+
+/* ---- launchers implemented in qtc_lm.cu (all enqueue on ctx->stream) ------- */
+struct GemvSeg { const uint16_t *w; float *out; int rows; };
+enum { EPI_STORE = 0, EPI_BIAS = 1, EPI_RESID = 2 };
+/* out[r] = epi(sum_c W[r,c]*x[c]); up to 3 row segments share x (q/k/v).  aux: bias or residual */
+int qtc_gemv(qtc_ctx *c, const GemvSeg *segs, int nseg, const float *x, int cols, int epi, const float *aux);
+int qtc_gemv_swiglu(qtc_ctx *c, float *out, const uint16_t *gate, const uint16_t *up, const float *x, int inter, int cols);
+int qtc_rmsnorm(qtc_ctx *c, float *out, const float *x, const float *w, int n, float eps);
+int qtc_lm_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add);
+int qtc_embed_row(qtc_ctx *c, float *out, const uint16_t *table, const int *idx_ptr, int idx_imm, int n);
+int qtc_sample(qtc_ctx *c, const float *logits, const SampleCfg &cfg, uint32_t *rng, int *hist_count,
+               int *out_token, GenState *st, int role);
+int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need);
+int qtc_talker_forward_dev(qtc_ctx *c, const float *embed_dev);   /* one decode step + head -> tk.logits */
+int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code_ptr, int *codes_out_dev);
+int qtc_sample_talker(qtc_ctx *c);
+int qtc_frame_front(qtc_ctx *c);    /* sample + sub-talker + next embedding, device resident */
+int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit);
+void *qtc_dmalloc(qtc_ctx *c, size_t bytes);
+template <class T> T *qtc_upload(qtc_ctx *c, const T *host, size_t n);
+
+/* ---- codec (qtc_codec.cu) --------------------------------------------------- */
+CodecDev *qtc_codec_upload(qtc_ctx *c, const qtc_codec_t *k);
+void qtc_codec_release(CodecDev *cd);
+float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_samples, float **dev_out);
+
+/* small launchers (qtc_lm.cu) */
+int qtc_copy(qtc_ctx *c, float *dst, const float *src, int n);
+int qtc_silu(qtc_ctx *c, float *x, int n);
+int qtc_add_row(qtc_ctx *c, float *out, const float *a, const uint16_t *table, int idx, int n);
+int qtc_set_int(qtc_ctx *c, int *p, int v);
+int qtc_bump_pos(qtc_ctx *c);
+int qtc_sample_bare(qtc_ctx *c, const float *logits_dev, int vocab, int top_k, float top_p, float temperature,
+                    uint32_t *rng_dev, int *out_dev);
+extern "C" int qwen_tts_cuda_set_arith(qtc_ctx_t *c, int strict);

@@ -1,0 +1,313 @@
+/*
+ * qtc_lm.cu - launch logic of the per-op decode path (mode 0): one decoder
+ * stack step (talker_attention_single x layers, c/qwen_tts_talker.c:119-248,
+ * 520-527; ST_FORWARD :638-691), the talker forward with codec head (:478-533),
+ * the sub-talker code-group loop (:539-736) and the device-resident front half
+ * of a frame (c/qwen_tts.c:1302-1363).  All work is enqueued on ctx->stream and
+ * reads positions / tokens from device memory, so every sequence here can be
+ * captured into a CUDA graph and replayed.
+ */
+#include "qtc_gemv.cuh"
+#include "qtc_internal.h"
+#include "qtc_lm_kernels.cuh"
+#include "qtc_sample.cuh"
+
+#include <math.h>
+
+#define LAUNCH_CHECK(c)                                                             \
+    do {                                                                            \
+        (c)->launches++;                                                            \
+        cudaError_t e_ = cudaGetLastError();                                        \
+        if (e_ != cudaSuccess) { qtc_set_error("%s:%d launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return -1; } \
+    } while (0)
+
+static int g_attr_done = 0;
+static int set_smem_attrs() {
+    if (g_attr_done) return 0;
+    QTC_CUDA(cudaFuncSetAttribute(k_gemv_strict, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    QTC_CUDA(cudaFuncSetAttribute(k_gemv_swiglu_strict, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    QTC_CUDA(cudaFuncSetAttribute(k_gemv_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    QTC_CUDA(cudaFuncSetAttribute(k_gemv_swiglu_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    QTC_CUDA(cudaFuncSetAttribute(k_attn_decode<QTC_FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    QTC_CUDA(cudaFuncSetAttribute(k_attn_decode<QTC_STRICT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    QTC_CUDA(cudaFuncSetAttribute(k_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+    g_attr_done = 1;
+    return 0;
+}
+
+int qtc_gemv(qtc_ctx *c, const GemvSeg *segs, int nseg, const float *x, int cols, int epi, const float *aux) {
+    if (set_smem_attrs()) return -1;
+    GemvArgs a;
+    memset(&a, 0, sizeof(a));
+    a.nseg = nseg; a.cols = cols; a.epi = epi; a.x = x; a.aux = aux;
+    int total = 0, groups = 0;
+    for (int i = 0; i < nseg; i++) { a.w[i] = segs[i].w; a.out[i] = segs[i].out; a.rows[i] = segs[i].rows; total += segs[i].rows; groups += (segs[i].rows + 31) / 32; }
+    a.total_rows = total;
+    if (epi != EPI_STORE && nseg != 1) { qtc_set_error("gemv: epilogue needs a single segment"); return -1; }
+    if (cols % 8 != 0 && c->arith == QTC_FAST) { qtc_set_error("gemv: cols %% 8 != 0"); return -1; }
+    if (c->arith == QTC_STRICT) {
+        if (cols % STRICT_TILE_K == 0) {
+            const size_t smem = (size_t)cols * 4 + STRICT_WARPS * STRICT_WARP_SMEM;
+            k_gemv_strict<<<(groups + STRICT_WARPS - 1) / STRICT_WARPS, STRICT_WARPS * 32, smem, c->stream>>>(a);
+        } else {
+            k_gemv_strict_generic<<<(total + 127) / 128, 128, 0, c->stream>>>(a);
+        }
+    } else {
+        k_gemv_fast<<<(total + GEMV_FAST_ROWS - 1) / GEMV_FAST_ROWS, GEMV_FAST_THREADS, (size_t)cols * 4, c->stream>>>(a);
+    }
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+int qtc_gemv_swiglu(qtc_ctx *c, float *out, const uint16_t *gate, const uint16_t *up, const float *x, int inter, int cols) {
+    if (set_smem_attrs()) return -1;
+    if (c->arith == QTC_STRICT) {
+        if (cols % STRICT_TILE_K == 0) {
+            const size_t smem = (size_t)cols * 4 + STRICT_WARPS * STRICT_WARP_SMEM;
+            k_gemv_swiglu_strict<<<(inter + 63) / 64, STRICT_WARPS * 32, smem, c->stream>>>(out, gate, up, x, inter, cols);
+            LAUNCH_CHECK(c);
+            return 0;
+        }
+        qtc_set_error("swiglu strict: cols %% 64 != 0");
+        return -1;
+    }
+    int grid = (inter + 7) / 8;
+    if (grid > 148 * 4) grid = 148 * 4;
+    k_gemv_swiglu_fast<<<grid, GEMV_FAST_THREADS, (size_t)cols * 4, c->stream>>>(out, gate, up, x, inter, cols);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+int qtc_rmsnorm(qtc_ctx *c, float *out, const float *x, const float *w, int n, float eps) {
+    if (c->arith == QTC_STRICT) k_rmsnorm<QTC_STRICT><<<1, 256, 0, c->stream>>>(out, x, w, n, eps);
+    else k_rmsnorm<QTC_FAST><<<1, 256, 0, c->stream>>>(out, x, w, n, eps);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+int qtc_embed_row(qtc_ctx *c, float *out, const uint16_t *table, const int *idx_ptr, int idx_imm, int n) {
+    k_embed_row<<<(n + 255) / 256, 256, 0, c->stream>>>(out, table, idx_ptr, idx_imm, n);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+/* RoPE rows exactly as the oracle computes them (c/qwen_tts_talker.c:76-113): host libm, uploaded */
+static void rope_rows_host(float *cs, float *sn, int pos0, int npos, int hd, float theta) {
+    const int half = hd / 2;
+    for (int p = 0; p < npos; p++)
+        for (int i = 0; i < half; i++) {
+            const float freq = 1.0f / powf(theta, (float)(2 * i) / (float)hd);
+            const float ang = (float)(pos0 + p) * freq;
+            const float cv = cosf(ang), sv = sinf(ang);
+            cs[(size_t)p * hd + i] = cv; cs[(size_t)p * hd + i + half] = cv;
+            sn[(size_t)p * hd + i] = sv; sn[(size_t)p * hd + i + half] = sv;
+        }
+}
+
+/* grow-only KV cache + rope table; contents are preserved (the reference reallocs, c/qwen_tts_talker.c:489-496) */
+int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
+    if (need <= b->kv_max) return 0;
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    const int nmax = ((need + 255) / 256) * 256;
+    const size_t kvd = (size_t)lm->kv_heads * lm->head_dim, hd = lm->head_dim;
+    float *nk = NULL, *nv = NULL, *ncs = NULL, *nsn = NULL;
+    QTC_CUDA(cudaMalloc(&nk, (size_t)lm->layers * nmax * kvd * 4 + 16));
+    QTC_CUDA(cudaMalloc(&nv, (size_t)lm->layers * nmax * kvd * 4 + 16));
+    QTC_CUDA(cudaMalloc(&ncs, (size_t)nmax * hd * 4));
+    QTC_CUDA(cudaMalloc(&nsn, (size_t)nmax * hd * 4));
+    if (b->kv_max > 0)
+        for (int l = 0; l < lm->layers; l++) {
+            QTC_CUDA(cudaMemcpy(nk + (size_t)l * nmax * kvd, b->k + (size_t)l * b->kv_max * kvd, (size_t)b->kv_max * kvd * 4, cudaMemcpyDeviceToDevice));
+            QTC_CUDA(cudaMemcpy(nv + (size_t)l * nmax * kvd, b->v + (size_t)l * b->kv_max * kvd, (size_t)b->kv_max * kvd * 4, cudaMemcpyDeviceToDevice));
+        }
+    std::vector<float> hc((size_t)nmax * hd), hs((size_t)nmax * hd);
+    rope_rows_host(hc.data(), hs.data(), 0, nmax, (int)hd, lm->theta);
+    QTC_CUDA(cudaMemcpy(ncs, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice));
+    QTC_CUDA(cudaMemcpy(nsn, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
+    cudaFree(b->k); cudaFree(b->v); cudaFree(b->cos); cudaFree(b->sin);
+    b->k = nk; b->v = nv; b->cos = ncs; b->sin = nsn; b->kv_max = nmax;
+    c->graph_key = -1;      /* pointers changed: captured graphs are stale */
+    return 0;
+}
+
+/* One token through every layer + final norm.  b->x holds the input on entry and the post-final-norm
+ * hidden on exit (ctx->tk_x semantics).  Position = *pos_ptr + pos_add. */
+int qtc_lm_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add) {
+    const int H = lm->hidden, hd = lm->head_dim, qd = lm->heads * hd, kvd = lm->kv_heads * hd;
+    if (set_smem_attrs()) return -1;
+    for (int l = 0; l < lm->layers; l++) {
+        const LmLayerDev *w = &lm->layer[l];
+        if (qtc_rmsnorm(c, b->xn, b->x, w->in_norm, H, lm->eps)) return -1;
+        GemvSeg qkv[3] = {{w->wq, b->q, qd}, {w->wk, b->kk, kvd}, {w->wv, b->vv, kvd}};
+        if (qtc_gemv(c, qkv, 3, b->xn, H, EPI_STORE, NULL)) return -1;
+        AttnArgs a;
+        a.q = b->q; a.k = b->kk; a.v = b->vv; a.q_norm = w->q_norm; a.k_norm = w->k_norm;
+        a.cos = b->cos; a.sin = b->sin;
+        a.kc = b->k + (size_t)l * b->kv_max * kvd; a.vc = b->v + (size_t)l * b->kv_max * kvd;
+        a.att = b->att; a.pos_ptr = pos_ptr; a.pos_add = pos_add;
+        a.heads = lm->heads; a.kv_heads = lm->kv_heads; a.hd = hd; a.eps = lm->eps;
+        a.scale = 1.0f / sqrtf((float)hd);
+        const size_t smem = (size_t)(2 * hd + b->kv_max + 32) * 4;
+        if (c->arith == QTC_STRICT) k_attn_decode<QTC_STRICT><<<lm->heads, 128, smem, c->stream>>>(a);
+        else k_attn_decode<QTC_FAST><<<lm->heads, 128, smem, c->stream>>>(a);
+        LAUNCH_CHECK(c);
+        GemvSeg o = {w->wo, b->x, H};
+        if (qtc_gemv(c, &o, 1, b->att, qd, EPI_RESID, b->x)) return -1;
+        if (qtc_rmsnorm(c, b->xn, b->x, w->post_norm, H, lm->eps)) return -1;
+        if (qtc_gemv_swiglu(c, b->g, w->gate, w->up, b->xn, lm->inter, H)) return -1;
+        GemvSeg d = {w->down, b->x, H};
+        if (qtc_gemv(c, &d, 1, b->g, lm->inter, EPI_RESID, b->x)) return -1;
+    }
+    return qtc_rmsnorm(c, b->x, b->x, lm->final_norm, H, lm->eps);
+}
+
+__global__ void k_copy_f32(float *dst, const float *src, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+}
+__global__ void k_bump_pos(GenState *st) { if (!st->done) st->pos += 1; }
+
+/* qwen_tts_talker_forward on device: embed -> all layers -> final norm (tk.x) -> codec head (tk.logits); pos++ */
+int qtc_talker_forward_dev(qtc_ctx *c, const float *embed_dev) {
+    const LmDev *lm = &c->talker;
+    k_copy_f32<<<(lm->hidden + 255) / 256, 256, 0, c->stream>>>(c->tk.x, embed_dev, lm->hidden);
+    LAUNCH_CHECK(c);
+    if (qtc_lm_step(c, lm, &c->tk, &c->state->pos, 0)) return -1;
+    GemvSeg h = {c->codec_head, c->tk.logits, lm->vocab};
+    if (qtc_gemv(c, &h, 1, c->tk.x, lm->hidden, EPI_STORE, NULL)) return -1;
+    k_bump_pos<<<1, 1, 0, c->stream>>>(c->state);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+/* ST_PROJECT_INPUT, c/qwen_tts_talker.c:693-702: st.x = input_proj(src) (+bias), or copy / zero-pad */
+static int sub_project(qtc_ctx *c, const float *src) {
+    const int h = c->sub.hidden, H = c->H;
+    if (c->sub_in_w) {
+        GemvSeg s = {c->sub_in_w, c->st.x, h};
+        return qtc_gemv(c, &s, 1, src, H, c->sub_in_b ? EPI_BIAS : EPI_STORE, c->sub_in_b);
+    }
+    k_copy_pad<<<(h + 255) / 256, 256, 0, c->stream>>>(c->st.x, src, H < h ? H : h, h);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+static int sub_sample(qtc_ctx *c, int g, int *codes_out_dev, int reseed) {
+    SampleArgs a;
+    memset(&a, 0, sizeof(a));
+    a.logits = c->st.logits;
+    a.cfg.vocab = c->sub.vocab; a.cfg.top_k = c->params.subtalker_top_k; a.cfg.top_p = c->params.subtalker_top_p;
+    a.cfg.temperature = c->params.subtalker_temperature; a.cfg.suppress_from = -1; a.cfg.eos_id = -1; a.cfg.rep_penalty = 1.0f;
+    a.rng = c->st_rng; a.out_token = codes_out_dev + g; a.role = 1;
+    a.reseed = reseed;
+    { float f = (float)c->params.sample_seed; memcpy(&a.seed_bits, &f, 4); }   /* re-seeded every frame, :718 */
+    a.scratch_f = c->sample_scratch_f; a.scratch_i = c->sample_scratch;
+    k_sample<<<1, SAMPLE_THREADS, (size_t)a.cfg.vocab * 8, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+
+/* qwen_tts_subtalker_generate on device.  first_code_ptr: device int (codes_out_dev[0] already holds it). */
+int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code_ptr, int *codes_out_dev) {
+    const LmDev *lm = &c->sub;
+    const int G = c->G, H = c->H;
+    const int *g_zero_pos = c->zero_pos;          /* device int 0: the sub-talker's position base */
+    if (sub_project(c, hidden_dev)) return -1;                                 /* pos 0: no logits */
+    if (qtc_lm_step(c, lm, &c->st, g_zero_pos, 0)) return -1;
+    for (int g = 1; g < G; g++) {
+        const uint16_t *table = g == 1 ? c->codec_embedding : c->sub_emb[g - 2];
+        const int *idx = g == 1 ? first_code_ptr : codes_out_dev + (g - 1);
+        if (qtc_embed_row(c, c->st_embed, table, idx, 0, H)) return -1;
+        if (sub_project(c, c->st_embed)) return -1;
+        if (qtc_lm_step(c, lm, &c->st, g_zero_pos, g)) return -1;
+        GemvSeg hd = {c->sub_head[g - 1], c->st.logits, lm->vocab};
+        if (qtc_gemv(c, &hd, 1, c->st.x, lm->hidden, EPI_STORE, NULL)) return -1;
+        if (sub_sample(c, g, codes_out_dev, g == 1)) return -1;
+    }
+    return 0;
+}
+
+int qtc_sample_talker(qtc_ctx *c) {
+    SampleArgs a;
+    memset(&a, 0, sizeof(a));
+    const LmDev *lm = &c->talker;
+    a.logits = c->tk.logits;
+    a.cfg.vocab = lm->vocab; a.cfg.top_k = c->params.top_k; a.cfg.top_p = c->params.top_p;
+    a.cfg.temperature = c->params.temperature;
+    a.cfg.suppress_from = lm->vocab - 1024; a.cfg.eos_id = c->host.codec_eos_id;
+    a.cfg.rep_penalty = c->params.repetition_penalty;
+    a.rng = &c->state->rng; a.hist_count = c->hist_count; a.st = c->state; a.codes = c->frame_codes; a.G = c->G; a.role = 0;
+    a.scratch_f = c->sample_scratch_f; a.scratch_i = c->sample_scratch;
+    if (set_smem_attrs()) return -1;
+    k_sample<<<1, SAMPLE_THREADS, (size_t)a.cfg.vocab * 8, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+/* ---- small launchers used by the host-side frame loop (qtc_generate.cu) ----- */
+__global__ void k_add_row(float *out, const float *a, const uint16_t *table, int idx, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __fadd_rn(a[i], bf16_to_f32(table[(size_t)idx * n + i]));   /* kernel_add_inplace(dst, codec_emb) */
+}
+__global__ void k_set_int(int *p, int v) { *p = v; }
+
+int qtc_copy(qtc_ctx *c, float *dst, const float *src, int n) {
+    k_copy_f32<<<(n + 255) / 256, 256, 0, c->stream>>>(dst, src, n);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+int qtc_silu(qtc_ctx *c, float *x, int n) {
+    if (c->arith == QTC_STRICT) k_silu<QTC_STRICT><<<(n + 255) / 256, 256, 0, c->stream>>>(x, n);
+    else k_silu<QTC_FAST><<<(n + 255) / 256, 256, 0, c->stream>>>(x, n);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+int qtc_add_row(qtc_ctx *c, float *out, const float *a, const uint16_t *table, int idx, int n) {
+    k_add_row<<<(n + 255) / 256, 256, 0, c->stream>>>(out, a, table, idx, n);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+int qtc_set_int(qtc_ctx *c, int *p, int v) {
+    k_set_int<<<1, 1, 0, c->stream>>>(p, v);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+int qtc_bump_pos(qtc_ctx *c) {
+    k_bump_pos<<<1, 1, 0, c->stream>>>(c->state);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+/* c/qwen_tts.c:1302-1363 on device: sample -> sub-talker -> next embedding -> n_generated++ */
+int qtc_frame_front(qtc_ctx *c) {
+    if (qtc_sample_talker(c)) return -1;
+    if (qtc_subtalker_dev(c, c->tk.x, c->frame_codes, c->frame_codes)) return -1;
+    NextEmbedArgs a;
+    memset(&a, 0, sizeof(a));
+    a.out = c->next_embed; a.codec_embedding = c->codec_embedding;
+    for (int g = 0; g < c->G - 1; g++) a.sub_emb[g] = c->sub_emb[g];
+    a.frame_codes = c->frame_codes; a.all_codes = c->codes; a.trailing = c->trailing; a.tts_pad = c->tts_pad;
+    a.st = c->state; a.H = c->H; a.G = c->G;
+    k_next_embed<<<(c->H + 255) / 256, 256, 0, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    k_advance_step<<<1, 1, 0, c->stream>>>(c->state);
+    LAUNCH_CHECK(c);
+    return 0;
+}
+
+/* kernel-level sample for the test surface: logits already on device */
+int qtc_sample_bare(qtc_ctx *c, const float *logits_dev, int vocab, int top_k, float top_p, float temperature,
+                    uint32_t *rng_dev, int *out_dev) {
+    if (set_smem_attrs()) return -1;
+    SampleArgs a;
+    memset(&a, 0, sizeof(a));
+    a.logits = logits_dev;
+    a.cfg.vocab = vocab; a.cfg.top_k = top_k; a.cfg.top_p = top_p; a.cfg.temperature = temperature;
+    a.cfg.suppress_from = -1; a.cfg.eos_id = -1; a.cfg.rep_penalty = 1.0f;
+    a.rng = rng_dev; a.out_token = out_dev; a.role = 1;
+    a.scratch_f = c->sample_scratch_f; a.scratch_i = c->sample_scratch;
+    k_sample<<<1, SAMPLE_THREADS, (size_t)vocab * 8, c->stream>>>(a);
+    LAUNCH_CHECK(c);
+    return 0;
+}

@@ -1,0 +1,281 @@
+/*
+ * qtc_sample.cuh - on-device token sampling with the reference's exact semantics.
+ *
+ * Replaces, per decision, c/qwen_tts.c:1302-1321 (suppress list, repetition
+ * penalty, sample, fixed-length EOS resample) and kernel_sample_top_k
+ * (c/qwen_tts_kernels.c:407-558) + rand_uniform (:384-393).
+ *
+ * One CTA of 1024 threads.  The reference keeps a descending insertion list of
+ * the k best (value, index) pairs with ties resolved to the lower index; that is
+ * the first k elements of the order (value desc, index asc).  Here: an 8-bit
+ * radix select finds the k-th largest value, ties at the threshold are admitted
+ * in index order, the <=k survivors are ranked by counting, and one thread
+ * walks the inverse CDF with the same fp32 operation order (expf via the
+ * glibc algorithm, division not reciprocal, sequential sums).
+ * top_p < 1 or k outside (0, vocab) takes the reference's slow path, restated
+ * with a parallel stable rank in place of its O(V^2) insertion sort.
+ */
+#pragma once
+#include "qtc_device.cuh"
+#include "qtc_internal.h"
+
+#define SAMPLE_THREADS 1024
+#define SAMPLE_MAX_K 1024
+
+__device__ __forceinline__ uint32_t f32_order_key(float v) {
+    const uint32_t u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+struct SampleSmem {
+    uint32_t hist[256];
+    uint32_t prefix, remaining, nsel, eq_total;
+    int pick; int flag;
+    float sel_v[SAMPLE_MAX_K]; int sel_i[SAMPLE_MAX_K];
+    float ord_v[SAMPLE_MAX_K]; int ord_i[SAMPLE_MAX_K];
+    float red[32];
+};
+
+/* lg: logits in shared memory [V] (already suppressed / penalised).  Returns the pick in every thread.
+ * scratch_f/scratch_i: global scratch of V entries each (slow path only). */
+__device__ int block_sample(const float *lg, float *vv, int V, int top_k, float top_p, float temperature,
+                            uint32_t *rng, SampleSmem &S, float *scratch_f, int *scratch_i) {
+    const int tid = threadIdx.x;
+    if (temperature <= 0.0f) temperature = 1e-5f;
+    __syncthreads();
+    if (top_p >= 1.0f && top_k > 0 && top_k < V && top_k <= SAMPLE_MAX_K) {
+        for (int i = tid; i < V; i += SAMPLE_THREADS) vv[i] = __fdiv_rn(lg[i], temperature);
+        if (tid == 0) { S.prefix = 0; S.nsel = 0; S.pick = 0; }
+        __syncthreads();
+        /* candidates: v > -FLT_MAX (the list is initialised with -FLT_MAX and admits only strictly greater) */
+        const uint32_t floor_key = f32_order_key(-3.402823466e+38f);
+        uint32_t nvalid = 0;
+        for (int i = tid; i < V; i += SAMPLE_THREADS) nvalid += f32_order_key(vv[i]) > floor_key && vv[i] == vv[i];
+        nvalid = (uint32_t)(block_sum((float)nvalid, S.red) + 0.5f);
+        const uint32_t kk = nvalid < (uint32_t)top_k ? nvalid : (uint32_t)top_k;
+        if (kk == 0) return 0;                    /* sum == 0 branch: idx[0] < 0 -> token 0, RNG untouched */
+        if (tid == 0) S.remaining = kk;
+        __syncthreads();
+        /* radix select of the kk-th largest key, 8 bits per pass from the top */
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            for (int i = tid; i < 256; i += SAMPLE_THREADS) S.hist[i] = 0;
+            __syncthreads();
+            const uint32_t prefix = S.prefix, himask = shift == 24 ? 0u : (0xffffffffu << (shift + 8));
+            for (int i = tid; i < V; i += SAMPLE_THREADS) {
+                const uint32_t key = f32_order_key(vv[i]);
+                if (key > floor_key && vv[i] == vv[i] && (key & himask) == prefix) atomicAdd(&S.hist[(key >> shift) & 255u], 1u);
+            }
+            __syncthreads();
+            if (tid < 32) {                        /* suffix counts: lane l owns digits 8l..8l+7 */
+                uint32_t c[8], tot = 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) { c[j] = S.hist[tid * 8 + j]; tot += c[j]; }
+                uint32_t sfx = tot;                /* inclusive suffix sum over lanes >= tid */
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_down_sync(0xffffffffu, sfx, o); if (tid + o < 32) sfx += t; }
+                uint32_t above = sfx - tot;        /* elements whose digit lies in a higher lane */
+                const uint32_t rem = S.remaining;
+                __syncwarp();
+#pragma unroll
+                for (int j = 7; j >= 0; j--) {
+                    if (above < rem && above + c[j] >= rem) {
+                        S.prefix = prefix | ((uint32_t)(tid * 8 + j) << shift);
+                        S.remaining = rem - above;
+                        S.eq_total = c[j];
+                    }
+                    above += c[j];
+                }
+            }
+            __syncthreads();
+        }
+        const uint32_t tkey = S.prefix, need_eq = S.remaining, eq_total = S.eq_total;
+        /* admit keys above the threshold, and ties at the threshold in index order */
+        for (int i = tid; i < V; i += SAMPLE_THREADS) {
+            const uint32_t key = f32_order_key(vv[i]);
+            if (vv[i] == vv[i] && key > tkey) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
+            else if (key == tkey && eq_total == need_eq) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
+        }
+        if (eq_total != need_eq && tid < 32) {
+            uint32_t base = 0;
+            for (int c0 = 0; c0 < V && base < need_eq; c0 += 32) {
+                const int i = c0 + tid;
+                const bool eq = i < V && f32_order_key(vv[i]) == tkey;
+                const uint32_t m = __ballot_sync(0xffffffffu, eq);
+                const uint32_t rank = base + __popc(m & ((1u << tid) - 1u));
+                if (eq && rank < need_eq) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
+                base += __popc(m);
+            }
+        }
+        __syncthreads();
+        /* rank by (value desc, index asc) */
+        for (uint32_t j = tid; j < kk; j += SAMPLE_THREADS) {
+            const float v = S.sel_v[j]; const int id = S.sel_i[j];
+            uint32_t r = 0;
+            for (uint32_t m = 0; m < kk; m++) r += (S.sel_v[m] > v) || (S.sel_v[m] == v && S.sel_i[m] < id);
+            S.ord_v[r] = v; S.ord_i[r] = id;
+        }
+        __syncthreads();
+        const float mx = S.ord_v[0];
+        for (uint32_t j = tid; j < kk; j += SAMPLE_THREADS) S.sel_v[j] = expf_libm(__fsub_rn(S.ord_v[j], mx));
+        __syncthreads();
+        if (tid == 0) {
+            float tot = 0.0f;
+            for (uint32_t j = 0; j < kk; j++) tot = __fadd_rn(tot, S.sel_v[j]);
+            int pick = 0;
+            if (tot > 0.0f) {
+                uint32_t st = *rng;
+                const float r = __fmul_rn(rng_next(&st), tot);
+                *rng = st;
+                float run = 0.0f;
+                for (uint32_t j = 0; j < kk; j++) { run = __fadd_rn(run, S.sel_v[j]); if (run >= r) { pick = S.ord_i[j]; break; } }
+            } else {
+                pick = S.ord_i[0];
+            }
+            S.pick = pick;
+        }
+        __syncthreads();
+        return S.pick;
+    }
+
+    if (top_p >= 1.0f && top_k > 0 && top_k < V) {
+        /* k beyond the parallel path's capacity: the literal insertion list, one thread (:419-484) */
+        if (tid == 0) {
+            float *val = scratch_f; int *idx = scratch_i;
+            const int k = top_k;
+            for (int j = 0; j < k; j++) { idx[j] = -1; val[j] = -3.402823466e+38f; }
+            for (int i = 0; i < V; i++) {
+                const float v = __fdiv_rn(lg[i], temperature);
+                if (!(v > val[k - 1])) continue;
+                int q = k - 1;
+                for (; q > 0 && v > val[q - 1]; q--) { val[q] = val[q - 1]; idx[q] = idx[q - 1]; }
+                val[q] = v; idx[q] = i;
+            }
+            const float mx0 = val[0];
+            float tot = 0.0f;
+            for (int j = 0; j < k; j++) {
+                if (idx[j] < 0) { val[j] = 0.0f; continue; }
+                val[j] = expf_libm(__fsub_rn(val[j], mx0)); tot = __fadd_rn(tot, val[j]);
+            }
+            int pick = 0;
+            if (tot > 0.0f) {
+                uint32_t st = *rng;
+                const float r = __fmul_rn(rng_next(&st), tot);
+                *rng = st;
+                float run = 0.0f;
+                for (int j = 0; j < k; j++) { run = __fadd_rn(run, val[j]); if (run >= r) { pick = idx[j] >= 0 ? idx[j] : 0; break; } }
+            } else pick = idx[0] >= 0 ? idx[0] : 0;
+            S.pick = pick;
+        }
+        __syncthreads();
+        return S.pick;
+    }
+    /* ---- slow path, c/qwen_tts_kernels.c:486-557 ---- */
+    float *p = scratch_f; int *ord = scratch_i;
+    for (int i = tid; i < V; i += SAMPLE_THREADS) p[i] = __fdiv_rn(lg[i], temperature);
+    __syncthreads();
+    float mx = -3.402823466e+38f;
+    for (int i = tid; i < V; i += SAMPLE_THREADS) mx = fmaxf(mx, p[i]);
+    mx = block_max(mx, S.red);
+    for (int i = tid; i < V; i += SAMPLE_THREADS) p[i] = expf_libm(__fsub_rn(p[i], mx));
+    __syncthreads();
+    if (tid == 0) {
+        float tot = 0.0f;
+        for (int i = 0; i < V; i++) tot = __fadd_rn(tot, p[i]);
+        S.red[0] = __fdiv_rn(1.0f, tot);
+    }
+    __syncthreads();
+    { const float inv = S.red[0]; __syncthreads(); for (int i = tid; i < V; i += SAMPLE_THREADS) p[i] = __fmul_rn(p[i], inv); }
+    __syncthreads();
+    const bool use_k = top_k > 0 && top_k < V, use_p = top_p < 1.0f;
+    if (use_k || use_p) {                               /* stable descending order == the insertion sort */
+        for (int i = tid; i < V; i += SAMPLE_THREADS) {
+            const float v = p[i];
+            int r = 0;
+            for (int m = 0; m < V; m++) r += (p[m] > v) || (p[m] == v && m < i);
+            ord[r] = i;
+        }
+        __syncthreads();
+    }
+    if (use_k) {
+        const float thr = p[ord[top_k - 1]];
+        __syncthreads();
+        for (int i = tid; i < V; i += SAMPLE_THREADS) if (p[i] < thr) p[i] = 0.0f;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        if (use_p) {
+            /* zeroed entries sort behind every kept one and add nothing, so the pre-zeroing order serves */
+            float run = 0.0f; int cut = V;
+            for (int i = 0; i < V; i++) { run = __fadd_rn(run, p[ord[i]]); if (run >= top_p) { cut = i + 1; break; } }
+            for (int i = cut; i < V; i++) p[ord[i]] = 0.0f;
+        }
+        float tot = 0.0f;
+        for (int i = 0; i < V; i++) tot = __fadd_rn(tot, p[i]);
+        const float inv = tot > 0.0f ? __fdiv_rn(1.0f, tot) : 1.0f;
+        uint32_t st = *rng;
+        const float r = rng_next(&st);
+        *rng = st;
+        float run = 0.0f; int pick = 0;
+        for (int i = 0; i < V; i++) {
+            const float q = tot > 0.0f ? __fmul_rn(p[i], inv) : p[i];
+            run = __fadd_rn(run, q);
+            if (run >= r) { pick = i; break; }
+        }
+        S.pick = pick;
+    }
+    __syncthreads();
+    return S.pick;
+}
+
+struct SampleArgs {
+    const float *logits;
+    SampleCfg cfg;
+    uint32_t *rng;
+    int *hist_count;       /* talker only */
+    int *out_token;        /* where the pick goes (codes[...]) or NULL */
+    GenState *st;          /* talker role: EOS / fixed-length policy */
+    int *codes; int G;     /* talker role: codes[0] = token (the frame's code row) */
+    int role;              /* 0 talker frame decision, 1 sub-talker / bare sample */
+    uint32_t seed_bits; int reseed;   /* sub-talker: re-seed before sampling (first code group of a frame) */
+    float *scratch_f; int *scratch_i;
+};
+
+/* dynamic smem: 2*V floats */
+__global__ void __launch_bounds__(SAMPLE_THREADS) k_sample(const SampleArgs a) {
+    extern __shared__ __align__(16) float dyn[];
+    __shared__ SampleSmem S;
+    const int V = a.cfg.vocab, tid = threadIdx.x;
+    float *lg = dyn, *vv = dyn + V;
+    if (a.role == 0 && a.st->done) return;
+    if (a.reseed && tid == 0) *a.rng = a.seed_bits;
+    for (int i = tid; i < V; i += SAMPLE_THREADS) {
+        float l = a.logits[i];
+        if (a.cfg.suppress_from >= 0 && i >= a.cfg.suppress_from && i != a.cfg.eos_id) l = -1e9f;
+        if (a.hist_count && a.cfg.rep_penalty != 1.0f) {
+            const int c = a.hist_count[i];
+            for (int j = 0; j < c; j++) l = l > 0.0f ? __fdiv_rn(l, a.cfg.rep_penalty) : __fmul_rn(l, a.cfg.rep_penalty);
+        }
+        lg[i] = l;
+    }
+    __syncthreads();
+    int tok = block_sample(lg, vv, V, a.cfg.top_k, a.cfg.top_p, a.cfg.temperature, a.rng, S, a.scratch_f, a.scratch_i);
+    if (a.role == 0) {
+        const int eos = a.cfg.eos_id;
+        if (a.st->fixed && tok == eos) {                       /* c/qwen_tts.c:1315-1321: second draw */
+            __syncthreads();
+            if (tid == 0) lg[eos] = -1e9f;
+            __syncthreads();
+            tok = block_sample(lg, vv, V, a.cfg.top_k, a.cfg.top_p, a.cfg.temperature, a.rng, S, a.scratch_f, a.scratch_i);
+        }
+        if (tid == 0) {
+            if (!a.st->fixed && tok == eos) { a.st->done = 1; a.st->stop_step = a.st->step; }
+            else {
+                a.st->token = tok;
+                a.hist_count[tok] += 1;
+                a.codes[0] = tok;
+            }
+        }
+    } else if (tid == 0 && a.out_token) {
+        *a.out_token = tok;
+    }
+}

@@ -206,6 +206,8 @@ def load_cuda():
     lib.qwen_tts_cuda_set_params.argtypes = [vp, C.POINTER(GenParams)]
     lib.qwen_tts_cuda_get_perf.argtypes = [vp, C.POINTER(Perf)]
     lib.qwen_tts_cuda_set_mode.argtypes = [vp, C.c_int]
+    lib.qwen_tts_cuda_set_arith.argtypes = [vp, C.c_int]
+    lib.qwen_tts_cuda_kernel_arith.argtypes = [C.c_int]
     lib.qwen_tts_cuda_reset.argtypes = [vp]
     lib.qwen_tts_cuda_talker_prefill.argtypes = [vp, f32p, C.c_int]
     lib.qwen_tts_cuda_talker_forward.argtypes = [vp, f32p, f32p]
