@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the B200 backend for Qwen3-TTS-C's per-frame generation path.
+
+Workload (BASELINE.json configs[1]): Qwen3-TTS-12Hz-1.7B-CustomVoice shapes, batch 1, one utterance of
+360 frames (28.8 s of 24 kHz audio) from the reference's fixture prompt, default sampling, fixed frame
+budget instead of EOS (random-init weights: no checkpoints offline).  One "step" = one whole utterance:
+prompt build + prefill + 360 x {talker step, sample, 15-codebook sub-talker, next embedding} + codec decode.
+
+  value : audio-seconds per second with the prompt already in HBM (CUDA events, prompt build .. last codec kernel)
+  e2e   : the same through the C-ABI call a user makes (qwen_tts_cuda_generate: host token string in,
+          host PCM out), wall clock around the call, H2D/D2H inside
+  roofline : talker decode step, algorithmic bytes / event-timed step, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline / --impl reference : the reference's own C path (oracle/_ref, unmodified sources) on the
+          host cores, bounded sample (see REF_FRAMES)
+
+N > 1 (torchrun): utterances are independent, so every rank decodes its own utterance on its own GPU with
+replicated weights and no collective on the data path ("weak" scaling); torch.distributed carries only the
+barrier and the max-over-ranks of the device time.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "qwen3-tts-c_b200"))
+from harness import binding as B, modelgen as mg  # noqa: E402
+
+TOKENS = [151644, 77091, 198, 2354, 2244, 2355, 4041, 2244, 11752, 13, 151645, 198, 151644, 77091, 198]
+CSV = ",".join(str(t) for t in TOKENS).encode()
+FRAMES = 360
+FRAME_S = 1920 / 24000.0
+REF_FRAMES = 2          # frames per reference step: ~2.7 s of single-thread GEMV work per frame on the 1.7B shapes
+METRIC = "audio-sec generated/sec (RTF), 1.7B-CustomVoice batch 1, 360 frames"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks and throttle reasons DURING the timed region"""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                               "--format=csv,noheader,nounits"], timeout=5).decode().strip()
+                self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]) if self.rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def build_model(preset):
+    orc = B.load_oracle()
+    spec = mg.PRESETS[preset]
+    main, cod = mg.build_tensors(spec, seed=0)
+    return orc, spec, main, cod, B.HostModel(spec, main, cod, orc)
+
+
+def run_reference(args, rank, world):
+    """The reference's own C path on the host cores (oracle/_ref/libqtts_ref.so = unmodified c/*.c + shim).
+    Setup (untimed): load the model directory, prefill the fixture prompt.  One step = REF_FRAMES frames of
+    the frame loop (talker forward, logits policy, reference sampler, sub-talker) + codec decode of those
+    frames.  Rank 0 only."""
+    if rank != 0:
+        return
+    if not B.have_ref():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libqtts_ref.so not built (no /root/reference at build time)"}))
+        return
+    import tempfile
+    ref = B.load_ref()
+    orc, spec, main, cod, hm = build_model(args.model)
+    d = tempfile.mkdtemp(prefix="qtts_model_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        mg.write_model_dir(d, spec, main, cod)
+        ctx = ref.ref_load(d.encode(), 0)
+        assert ctx, "reference failed to load the model"
+        H, V, G = spec["talker"]["hidden"], spec["talker"]["vocab"], spec["groups"]
+        p = B.default_params(fixed_codec_tokens=REF_FRAMES)
+        ref.ref_set_params(ctx, C.byref(p))
+        # prompt through the oracle's restatement of the prompt builder (untimed setup; bit-identical to the reference's)
+        s = orc.orc_create(hm.desc)
+        pre, tr, pad = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        plen, ntr = C.c_int(0), C.c_int(0)
+        tok = np.array(TOKENS, dtype=np.int32)
+        orc.orc_build_prompt(s, B.iptr(tok), len(tok), mg.SPEAKERS["aiden"], mg.LANGUAGES["english"], C.byref(pre), C.byref(plen),
+                             C.byref(tr), C.byref(ntr), C.byref(pad))
+        trailing = np.ctypeslib.as_array(C.cast(tr, B.f32p), shape=(ntr.value, H)).copy()
+        padv = np.ctypeslib.as_array(C.cast(pad, B.f32p), shape=(H,)).copy()
+        ref.ref_reset(ctx)
+        ref.ref_prefill(ctx, C.cast(pre, B.f32p), plen.value)
+        logits = np.zeros(V, dtype=np.float32)
+        hidden0 = np.ctypeslib.as_array(ref.ref_hidden(ctx), shape=(H,)).copy()
+        ref.kernel_matvec_bf16(B.fptr(logits), hm.desc.codec_head, B.fptr(hidden0), V, H)
+        emb_t = mg.bf16_to_f32(main["talker.model.codec_embedding.weight"])
+        sub_emb = [main[f"talker.code_predictor.model.codec_embedding.{g}.weight"] for g in range(G - 1)]
+        rng = np.array([p.sample_seed], dtype=np.float32)
+        ref.kernel_apply_repetition_penalty.argtypes = [B.f32p, B.i32p, C.c_int, C.c_int, C.c_float]
+        hist, step_idx = [], 0
+
+        def one_step():
+            nonlocal logits, step_idx
+            codes = np.zeros((REF_FRAMES, G), dtype=np.int32)
+            for f in range(REF_FRAMES):
+                lg = logits.copy()
+                lg[V - 1024:] = np.where(np.arange(V - 1024, V) == hm.desc.codec_eos_id, lg[V - 1024:], -1e9)
+                h = np.array(hist, dtype=np.int32) if hist else np.zeros(1, dtype=np.int32)
+                ref.kernel_apply_repetition_penalty(B.fptr(lg), B.iptr(h), len(hist), V, C.c_float(p.repetition_penalty))
+                t = ref.kernel_sample_top_k(B.fptr(lg), V, p.top_k, C.c_float(p.top_p), C.c_float(p.temperature), B.fptr(rng))
+                if t == hm.desc.codec_eos_id:
+                    lg[t] = -1e9
+                    t = ref.kernel_sample_top_k(B.fptr(lg), V, p.top_k, C.c_float(p.top_p), C.c_float(p.temperature), B.fptr(rng))
+                hist.append(t)
+                out = np.zeros(32, dtype=np.int32)
+                hid = np.ctypeslib.as_array(ref.ref_hidden(ctx), shape=(H,)).copy()
+                ref.ref_subtalker(ctx, B.fptr(hid), t, B.iptr(out))
+                codes[f] = out[:G]
+                nxt = emb_t[t].copy()
+                for g in range(1, G):
+                    nxt += mg.bf16_to_f32(sub_emb[g - 1][out[g]])
+                nxt += trailing[step_idx] if step_idx < len(trailing) else padv
+                step_idx += 1
+                ref.ref_forward(ctx, B.fptr(np.ascontiguousarray(nxt, dtype=np.float32)), B.fptr(logits))
+            ns = C.c_int(0)
+            ptr = ref.ref_codec_decode(ctx, B.iptr(codes), REF_FRAMES, C.byref(ns))
+            ref.ref_free_buf(ptr)
+
+        for _ in range(args.warmup):
+            one_step()
+        t0 = time.time()
+        for _ in range(args.steps):
+            one_step()
+        dt = time.time() - t0
+        rtf = args.steps * REF_FRAMES * FRAME_S / dt
+        cores = os.cpu_count()
+        line = {"impl": "reference", "metric": METRIC, "value": rtf, "unit": "audio_s/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32 (bf16 weights)", "data": "synthetic",
+                "config": {"workload": "1.7B-CustomVoice shapes, batch 1, default sampling, random-init weights",
+                           "sample": f"{REF_FRAMES} frames of the frame loop + codec decode of them per step, after an untimed prefill"},
+                "cpu_baseline": {"value": rtf, "unit": "audio_s/s", "cores": cores, "kind": "reference",
+                                 "sample": f"{args.steps} x {REF_FRAMES} frames; GEMVs single-threaded (no BLAS on the image), codec convs OpenMP x{cores}"},
+                "ms_per_frame": dt / (args.steps * REF_FRAMES) * 1e3,
+                "e2e": {"value": rtf, "unit": "audio_s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        ref.ref_free(ctx)
+    finally:
+        import shutil
+        shutil.rmtree(d, ignore_errors=True)
+
+
+def cpu_baseline_sample(hm, orc, spec, main, frames=1):
+    """bounded CPU sample for the default line: the oracle port (OpenMP over rows) on `frames` frames after prefill"""
+    s = orc.orc_create(hm.desc)
+    p = B.default_params(fixed_codec_tokens=frames)
+    orc.orc_set_params(s, C.byref(p))
+    tok = np.array(TOKENS, dtype=np.int32)
+    pre, tr, pad = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    plen, ntr = C.c_int(0), C.c_int(0)
+    orc.orc_build_prompt(s, B.iptr(tok), len(tok), mg.SPEAKERS["aiden"], mg.LANGUAGES["english"], C.byref(pre), C.byref(plen),
+                         C.byref(tr), C.byref(ntr), C.byref(pad))
+    H, V, G = spec["talker"]["hidden"], spec["talker"]["vocab"], spec["groups"]
+    orc.orc_reset(s)
+    orc.orc_talker_prefill(s, C.cast(pre, B.f32p), plen.value)
+    t0 = time.time()
+    logits = np.zeros(V, dtype=np.float32)
+    codes = np.zeros((frames, G), dtype=np.int32)
+    emb = np.zeros(H, dtype=np.float32)
+    for f in range(frames):
+        out = np.zeros(32, dtype=np.int32)
+        orc.orc_subtalker_generate(s, orc.orc_hidden(s), 100 + f, B.iptr(out))
+        codes[f] = out[:G]
+        orc.orc_talker_forward(s, B.fptr(emb), B.fptr(logits))
+    ns = C.c_int(0)
+    ptr = orc.orc_codec_decode(s, B.iptr(codes), frames, C.byref(ns))
+    orc.orc_free(ptr)
+    dt = time.time() - t0
+    orc.orc_destroy(s)
+    return frames * FRAME_S / dt, dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="1.7b", choices=list(mg.PRESETS))
+    ap.add_argument("--frames", type=int, default=FRAMES)
+    ap.add_argument("--mode", type=int, default=0)
+    ap.add_argument("--strict", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    torch.cuda.set_device(local)
+    cuda = B.load_cuda()                       # raises if the extension was not built: there is no fallback
+    if cuda.qwen_tts_cuda_init(local) != 0:
+        raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
+    orc, spec, main_t, cod, hm = build_model(args.model)
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    if not ctx:
+        raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
+    cuda.qwen_tts_cuda_set_mode(ctx, args.mode)
+    cuda.qwen_tts_cuda_set_arith(ctx, args.strict)
+    frames = args.frames
+    p = B.default_params(fixed_codec_tokens=frames, sample_seed=42 + rank)     # every rank: its own utterance
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
+    G = spec["groups"]
+    codes = np.zeros((frames, G), dtype=np.int32)
+    perf = B.Perf()
+
+    def one_utterance():
+        ns, nf = C.c_int(0), C.c_int(0)
+        t0 = time.perf_counter()
+        ptr = cuda.qwen_tts_cuda_generate(ctx, CSV, b"aiden", b"english", C.byref(ns), B.iptr(codes), frames, C.byref(nf))
+        wall = time.perf_counter() - t0
+        if not ptr or nf.value != frames or ns.value != frames * 1920:
+            raise RuntimeError("generate failed: " + cuda.qwen_tts_cuda_last_error().decode())
+        cuda.qwen_tts_cuda_free_host(ptr)
+        cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+        return wall, perf.device_ms / 1e3, perf.talker_ms / 1e3, ns.value
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_utterance()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    launches0 = perf.kernel_launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    t_all0 = time.perf_counter()
+    walls, devs, loops = [], [], []
+    pcm_bytes = 0
+    for _ in range(args.steps):
+        w, dv, lp, ns = one_utterance()
+        walls.append(w); devs.append(dv); loops.append(lp)
+        pcm_bytes = ns * 4
+    barrier()
+    t_all = time.perf_counter() - t_all0
+    sampler.stop_flag = True
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    launches = perf.kernel_launches - launches0
+
+    dev_total, wall_total = sum(devs), t_all
+    if dist is not None:
+        t = torch.tensor([dev_total, wall_total], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_total, wall_total = t.tolist()
+    audio_s = world * args.steps * frames * FRAME_S
+    value, e2e = audio_s / dev_total, audio_s / wall_total
+
+    line = None
+    if rank == 0:
+        hbm, which = peaks()
+        pos = 10 + frames // 2
+        step_ms = cuda.qwen_tts_cuda_bench_talker_step(ctx, pos, 20, 1)
+        sub_ms = cuda.qwen_tts_cuda_bench_subtalker(ctx, 10, 1)
+        step_bytes = cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos)
+        sub_bytes = cuda.qwen_tts_cuda_subtalker_frame_bytes(ctx)
+        ach = step_bytes / (step_ms * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": value, "unit": "audio_s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": wall_total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 (bf16 weights)", "data": "synthetic",
+                "config": {"workload": f"{args.model} CustomVoice shapes, batch 1 per GPU, {frames} frames ({frames * FRAME_S:.1f} s audio), "
+                                       "default sampling (temp 0.9, top-k 50, rep-pen 1.05), random-init weights, fixed frame budget",
+                           "mode": args.mode, "arith": "strict" if args.strict else "fast",
+                           "l2": "weights per step (2.8 GB talker, 157 MB x16 sub-talker) exceed the 126 MB L2; the roofline probe flushes L2 between iterations"},
+                "ms_per_frame": sum(loops) / (args.steps * frames) * 1e3,
+                "e2e": {"value": e2e, "unit": "audio_s/s", "h2d_bytes_per_step": len(CSV), "d2h_bytes_per_step": pcm_bytes + frames * G * 4},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "kernel": "talker decode step (all kernels of one step)", "achieved": ach, "peak": hbm, "unit": "GB/s",
+                             "frac": ach / hbm, "traffic": None, "peak_source": which, "bytes_per_step": step_bytes, "ms_per_talker_step": step_ms,
+                             "subtalker": {"ms_per_frame": sub_ms, "streamed_bytes": sub_bytes, "achieved": sub_bytes / (sub_ms * 1e-3) / 1e9,
+                                           "frac": sub_bytes / (sub_ms * 1e-3) / 1e9 / hbm}},
+                "clocks": sampler.summary()}
+        if not args.no_cpu and world == 1:
+            rtf_cpu, dt = cpu_baseline_sample(hm, orc, spec, main_t, frames=1)
+            line["cpu_baseline"] = {"value": rtf_cpu, "unit": "audio_s/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"1 frame (sub-talker + talker step) + codec decode of it after an untimed prefill, {dt:.1f} s; "
+                                              "oracle port, OpenMP over output rows (the reference's own GEMVs are single-threaded: see --impl reference)"}
+        print(json.dumps(line))
+    cuda.qwen_tts_cuda_release(ctx)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

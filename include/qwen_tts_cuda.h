@@ -170,7 +170,8 @@ typedef struct {
     int    codec_tokens;
     int    stop_reason;   /* 1 eos, 2 max_tokens  (c/qwen_tts.c:1264) */
     int    stop_step;
-    long long kernel_launches;  /* kernels of this library launched by the call */
+    long long kernel_launches;  /* kernels of this library launched so far on this context */
+    double device_ms;           /* whole utterance on the device: prompt build .. last codec kernel (CUDA events) */
 } qtc_perf_t;
 
 typedef struct qtc_ctx qtc_ctx_t;   /* opaque device-side model + state */

@@ -116,7 +116,7 @@ extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     for (LmBuffers *b : bs) { cudaFree(b->k); cudaFree(b->v); cudaFree(b->cos); cudaFree(b->sin); }
     cudaFree(c->codes); cudaFree(c->trailing); cudaFree(c->prefill);
     cudaFreeHost(c->state_host); cudaFreeHost(c->codes_host); cudaFreeHost(c->host_stage);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -133,7 +133,8 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     memset(&c->talker, 0, sizeof(c->talker)); memset(&c->sub, 0, sizeof(c->sub));
     qwen_tts_cuda_default_params(&c->params);
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess;
+              cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess &&
+              cudaEventCreate(&c->ev2) == cudaSuccess && cudaEventCreate(&c->ev3) == cudaSuccess;
     c->host_stage_bytes = 1 << 20;
     ok = ok && cudaMallocHost(&c->state_host, sizeof(GenState)) == cudaSuccess &&
          cudaMallocHost(&c->host_stage, c->host_stage_bytes) == cudaSuccess;

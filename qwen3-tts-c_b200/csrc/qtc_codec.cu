@@ -351,6 +351,7 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
     k_conv_to_mono<<<(L + 255) / 256, 256, 0, c->stream>>>(wav, voc, d->fin_w, d->fin_b, d->fin_alpha, d->fin_beta, dim, 7, L, 1);
     c->launches++;
 #undef CK
+    cudaEventRecord(c->ev3, c->stream);              /* end of device work; what follows is the D2H of the PCM */
     float *host = (float *)malloc((size_t)L * 4);
     if (!host) return NULL;
     if (cudaMemcpyAsync(host, wav, (size_t)L * 4, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||

@@ -316,6 +316,7 @@ extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const c
     if (spk >= 0) prefix[np++] = spk;
     prefix[np++] = m->codec_pad_id; prefix[np++] = m->codec_bos_id;
     const int H = c->H, plen = 3 + np;
+    cudaEventRecord(c->ev2, c->stream);
     int ntr = ((int)tok.size() - 4 - 5) + 1;
     if (ntr < 1) ntr = 1;
 
@@ -348,6 +349,7 @@ extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const c
     }
     const double t_end = now_ms();
     c->perf.codec_ms = t_end - t_codec;
+    if (pcm) { float dms = 0; cudaEventElapsedTime(&dms, c->ev2, c->ev3); c->perf.device_ms = dms; }
     c->perf.total_ms = t_end - t_start;
     return pcm;
 }

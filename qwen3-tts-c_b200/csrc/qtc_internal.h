@@ -114,7 +114,7 @@ struct qtc_ctx {
     int mode;                     /* 0 per-op kernels, 1 fused persistent kernels */
     int arith;                    /* QTC_FAST / QTC_STRICT */
     cudaStream_t stream;
-    cudaEvent_t ev0, ev1;
+    cudaEvent_t ev0, ev1, ev2, ev3;   /* ev2..ev3: device span of a whole utterance (prompt build .. last codec kernel) */
     std::vector<void *> allocs;   /* everything cudaMalloc'd, for release() */
     long long launches;
     /* CUDA graphs of the frame loop (built lazily, keyed by params) */

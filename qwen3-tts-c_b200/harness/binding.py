@@ -98,7 +98,8 @@ class GenParams(C.Structure):
 class Perf(C.Structure):
     _fields_ = [("total_ms", C.c_double), ("talker_ms", C.c_double), ("codec_ms", C.c_double),
                 ("prefill_ms", C.c_double), ("codec_tokens", C.c_int), ("stop_reason", C.c_int),
-                ("stop_step", C.c_int), ("kernel_launches", C.c_longlong)]
+                ("stop_step", C.c_int), ("kernel_launches", C.c_longlong),
+                ("device_ms", C.c_double)]
 
 
 def default_params(**kw) -> GenParams:
