@@ -270,6 +270,9 @@ double qwen_tts_cuda_bench_subtalker(qtc_ctx_t *ctx, int iters, int flush_l2);
 /* algorithmic bytes the talker step / sub-talker frame read */
 double qwen_tts_cuda_talker_step_bytes(const qtc_ctx_t *ctx, int pos);
 double qwen_tts_cuda_subtalker_frame_bytes(const qtc_ctx_t *ctx);
+/* per-phase SM-clock stamps of the fused talker step (layer `layer`, KV position `pos`): 16 slots per CTA,
+ * out[num_sms*16]; returns the CTA count.  Evidence for profiles/, not part of the reference's interface. */
+int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *ctx, int pos, int layer, long long *out);
 const char *qwen_tts_cuda_last_error(void);
 
 #ifdef __cplusplus

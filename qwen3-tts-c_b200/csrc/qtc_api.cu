@@ -177,6 +177,23 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     c->st_rng = (uint32_t *)qtc_dmalloc(c, 16);
     c->zero_pos = (int *)qtc_dmalloc(c, 16);
     if (c->zero_pos) cudaMemset(c->zero_pos, 0, 16);
+    {
+        cudaDeviceProp prop;
+        cudaGetDeviceProperties(&prop, g_device);
+        c->num_sms = prop.multiProcessorCount;
+        const int heads = desc->talker.heads > desc->sub.heads ? desc->talker.heads : desc->sub.heads;
+        const int hd = desc->talker.head_dim > desc->sub.head_dim ? desc->talker.head_dim : desc->sub.head_dim;
+        c->talker_dev = (LmDev *)qtc_dmalloc(c, sizeof(LmDev));
+        c->sub_dev = (LmDev *)qtc_dmalloc(c, sizeof(LmDev));
+        c->bar = (unsigned long long *)qtc_dmalloc(c, 64);
+        c->head_cnt = (unsigned *)qtc_dmalloc(c, (size_t)(heads > 0 ? heads : 1) * 4);
+        c->attn_part = (float *)qtc_dmalloc(c, (size_t)(heads > 0 ? heads : 1) * 16 * (hd + 2) * 4);   /* FUSED_MAX_SPLIT */
+        if (!c->talker_dev || !c->sub_dev || !c->bar || !c->head_cnt || !c->attn_part) { qwen_tts_cuda_release(c); return NULL; }
+        cudaMemcpy(c->talker_dev, &c->talker, sizeof(LmDev), cudaMemcpyHostToDevice);
+        cudaMemcpy(c->sub_dev, &c->sub, sizeof(LmDev), cudaMemcpyHostToDevice);
+        cudaMemset(c->bar, 0, 64);
+        cudaMemset(c->head_cnt, 0, (size_t)(heads > 0 ? heads : 1) * 4);
+    }
     c->sample_scratch = (int *)qtc_dmalloc(c, (size_t)(V > 0 ? V : 1) * 4);
     c->sample_scratch_f = (float *)qtc_dmalloc(c, (size_t)(V > 0 ? V : 1) * 4);
     if (!c->state || !c->hist_count || !c->frame_codes || !c->next_embed || !c->tts_pad || !c->st_embed || !c->text_tmp0 || !c->text_tmp1 ||

@@ -104,6 +104,13 @@ struct qtc_ctx {
     float *text_tmp0, *text_tmp1; /* text projection staging [text_hidden] */
     uint32_t *st_rng;             /* sub-talker RNG (re-seeded every frame) */
     int *zero_pos;                /* device int, always 0: position base of the sub-talker */
+    /* fused persistent decode kernel (mode 1) */
+    LmDev *talker_dev, *sub_dev;  /* device copies of the stack descriptors */
+    unsigned long long *bar;      /* grid barrier counter */
+    unsigned *head_cnt;           /* [heads] */
+    float *attn_part;             /* [heads, 8, head_dim + 2] */
+    int num_sms;
+    long long *prof; int prof_layer;   /* optional per-phase clock stamps of the fused kernel (debug) */
     int *sample_scratch;          /* slow-path sampler scratch */
     float *sample_scratch_f;
     float *host_stage;            /* pinned staging for stage-API vectors */

@@ -233,6 +233,20 @@ extern "C" double qwen_tts_cuda_bench_talker_step(qtc_ctx_t *c, int pos, int ite
     return total / iters;
 }
 
+/* debug / profiles: SM-clock stamps of the fused talker step's phases in layer `layer`, 16 slots per CTA
+ * (slot meaning: qtc_fused_kernel.cuh PROF(i)); out receives num_sms*16 values, returns num_sms */
+extern "C" int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *c, int pos, int layer, long long *out) {
+    if (!c || !out || c->talker.layers <= 0) return -1;
+    const size_t n = (size_t)c->num_sms * 16;
+    if (!c->prof) { c->prof = (long long *)qtc_dmalloc(c, n * 8); if (!c->prof) return -1; }
+    cudaMemsetAsync(c->prof, 0, n * 8, c->stream);
+    c->prof_layer = layer;
+    if (qwen_tts_cuda_bench_talker_step(c, pos, 2, 1) < 0) return -1;
+    QTC_CUDA(cudaMemcpy(out, c->prof, n * 8, cudaMemcpyDeviceToHost));
+    c->prof_layer = -1;
+    return c->num_sms;
+}
+
 extern "C" double qwen_tts_cuda_bench_subtalker(qtc_ctx_t *c, int iters, int do_flush) {
     if (!c || c->sub.layers <= 0 || iters <= 0) return -1.0;
     cudaMemsetAsync(c->st_proj, 0, (size_t)c->H * 4, c->stream);

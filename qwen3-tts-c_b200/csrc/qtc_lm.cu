@@ -7,6 +7,7 @@
  * reads positions / tokens from device memory, so every sequence here can be
  * captured into a CUDA graph and replayed.
  */
+#include "qtc_fused_kernel.cuh"
 #include "qtc_gemv.cuh"
 #include "qtc_internal.h"
 #include "qtc_lm_kernels.cuh"
@@ -130,10 +131,46 @@ int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
     return 0;
 }
 
+/* mode 1: the whole step (+ optional head GEMV, + pos bump) as one persistent cooperative kernel */
+static int g_fused_attr = 0;
+static bool fused_ok(const qtc_ctx *c, const LmDev *lm) {
+    return c->mode == 1 && c->arith == QTC_FAST && lm->head_dim <= FUSED_THREADS && lm->head_dim % 2 == 0 &&
+           lm->hidden % 8 == 0 && lm->inter % 8 == 0 && (lm->heads * lm->head_dim) % 8 == 0 && lm->heads <= c->num_sms;
+}
+static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
+                      const uint16_t *head_w, int head_rows, float *logits, GenState *st) {
+    if (!g_fused_attr) {
+        QTC_CUDA(cudaFuncSetAttribute(k_lm_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        g_fused_attr = 1;
+    }
+    FusedArgs a;
+    memset(&a, 0, sizeof(a));
+    a.lm = lm == &c->talker ? c->talker_dev : c->sub_dev;
+    a.x = b->x; a.q = b->q; a.kk = b->kk; a.vv = b->vv; a.att = b->att; a.g = b->g;
+    a.kc = b->k; a.vc = b->v; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
+    a.pos_ptr = pos_ptr; a.pos_add = pos_add;
+    a.head_w = head_w; a.head_rows = head_rows; a.logits = logits;
+    a.bar = c->bar; a.head_cnt = c->head_cnt; a.part = c->attn_part; a.st = st;
+    a.prof = lm == &c->talker ? c->prof : NULL; a.prof_layer = c->prof_layer;
+    const int qd = lm->heads * lm->head_dim;
+    int vec = lm->hidden > lm->inter ? lm->hidden : lm->inter;
+    if (qd > vec) vec = qd;
+    const int attn = 2 * lm->head_dim + FUSED_THREADS + (b->kv_max > 64 ? b->kv_max : 64) + 64;
+    a.xs_floats = (vec + 3) & ~3;
+    a.att_floats = (attn + 3) & ~3;
+    const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
+    if (smem > 200 * 1024) { qtc_set_error("fused step: %zu bytes of shared memory needed", smem); return -1; }
+    void *args[] = {&a};
+    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_THREADS), args, smem, c->stream));
+    c->launches++;
+    return 0;
+}
+
 /* One token through every layer + final norm.  b->x holds the input on entry and the post-final-norm
  * hidden on exit (ctx->tk_x semantics).  Position = *pos_ptr + pos_add. */
 int qtc_lm_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add) {
     const int H = lm->hidden, hd = lm->head_dim, qd = lm->heads * hd, kvd = lm->kv_heads * hd;
+    if (fused_ok(c, lm)) return fused_step(c, lm, b, pos_ptr, pos_add, NULL, 0, NULL, NULL);
     if (set_smem_attrs()) return -1;
     for (int l = 0; l < lm->layers; l++) {
         const LmLayerDev *w = &lm->layer[l];
@@ -172,6 +209,7 @@ int qtc_talker_forward_dev(qtc_ctx *c, const float *embed_dev) {
     const LmDev *lm = &c->talker;
     k_copy_f32<<<(lm->hidden + 255) / 256, 256, 0, c->stream>>>(c->tk.x, embed_dev, lm->hidden);
     LAUNCH_CHECK(c);
+    if (fused_ok(c, lm)) return fused_step(c, lm, &c->tk, &c->state->pos, 0, c->codec_head, lm->vocab, c->tk.logits, c->state);
     if (qtc_lm_step(c, lm, &c->tk, &c->state->pos, 0)) return -1;
     GemvSeg h = {c->codec_head, c->tk.logits, lm->vocab};
     if (qtc_gemv(c, &h, 1, c->tk.x, lm->hidden, EPI_STORE, NULL)) return -1;
@@ -220,9 +258,13 @@ int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code
         const int *idx = g == 1 ? first_code_ptr : codes_out_dev + (g - 1);
         if (qtc_embed_row(c, c->st_embed, table, idx, 0, H)) return -1;
         if (sub_project(c, c->st_embed)) return -1;
-        if (qtc_lm_step(c, lm, &c->st, g_zero_pos, g)) return -1;
-        GemvSeg hd = {c->sub_head[g - 1], c->st.logits, lm->vocab};
-        if (qtc_gemv(c, &hd, 1, c->st.x, lm->hidden, EPI_STORE, NULL)) return -1;
+        if (fused_ok(c, lm)) {
+            if (fused_step(c, lm, &c->st, g_zero_pos, g, c->sub_head[g - 1], lm->vocab, c->st.logits, NULL)) return -1;
+        } else {
+            if (qtc_lm_step(c, lm, &c->st, g_zero_pos, g)) return -1;
+            GemvSeg hd = {c->sub_head[g - 1], c->st.logits, lm->vocab};
+            if (qtc_gemv(c, &hd, 1, c->st.x, lm->hidden, EPI_STORE, NULL)) return -1;
+        }
         if (sub_sample(c, g, codes_out_dev, g == 1)) return -1;
     }
     return 0;
