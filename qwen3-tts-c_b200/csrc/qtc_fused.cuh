@@ -43,8 +43,30 @@ struct FusedArgs {
     GenState *st;                  /* talker: pos += 1 at the end (NULL for the sub-talker) */
     int xs_floats;                 /* size of the staged-vector region of shared memory */
     int att_floats;                /* attention scratch after it; the KV stage [2][64][hd] follows */
+    int flags;                     /* experiments (env QTC_FUSED_FLAGS) */
+    int ring_off;                  /* byte offset of the weight ring in dynamic shared memory (128-aligned) */
     long long *prof; int prof_layer; /* optional: clock64 stamps of one layer, 16 slots per CTA (debug / profiles) */
 };
+
+/* the 512 compute threads synchronise on named barrier 1; the producer warp (threads 512..543) never joins */
+#define NB_COMPUTE 1
+__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync %0, %1;" ::"n"(NB_COMPUTE), "n"(FUSED_THREADS) : "memory"); }
+__device__ __forceinline__ float csum(float v, float *red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_sum(v);
+    compute_sync();
+    if (lane == 0) red[w] = v;
+    compute_sync();
+    return warp_sum(lane < FUSED_WARPS ? red[lane] : 0.0f);
+}
+__device__ __forceinline__ float cmax(float v, float *red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_max(v);
+    compute_sync();
+    if (lane == 0) red[w] = v;
+    compute_sync();
+    return warp_max(lane < FUSED_WARPS ? red[lane] : -3.402823466e+38f);
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p) {
     unsigned long long v;
@@ -55,35 +77,36 @@ __device__ __forceinline__ void prefetch_l2_bulk(const void *p, unsigned bytes) 
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
 
-/* all CTAs of the grid; `target` lives in thread 0 */
+/* Grid barrier on a monotonic L2 counter.  Arrival is a release-reduction (orders this CTA's earlier writes,
+ * which bar.sync made visible to thread 0, without a full fence and without waiting for loads in flight);
+ * the wait is an acquire-load spin.  `target` lives in thread 0. */
+__device__ __forceinline__ void red_release_inc(unsigned long long *p) {
+    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(1ULL) : "memory");
+}
 __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned long long &target, unsigned nb) {
-    __syncthreads();
+    compute_sync();
     if (threadIdx.x == 0) {
         target += nb;
-        __threadfence();
-        const unsigned long long old = atomicAdd(bar, 1ULL);
-        if (old + 1 < target) while (ld_acquire_u64(bar) < target) { }
-        __threadfence();
+        red_release_inc(bar);
+        while (ld_acquire_u64(bar) < target) { }
     }
-    __syncthreads();
+    compute_sync();
 }
 
-/* the same barrier in two halves, so that work that needs no result of this phase (L2 prefetch of later
- * phases) is issued after the CTA has announced its arrival and while the others are still coming */
+/* the same barrier in two halves: loads that need no result of this phase (the next phase's first weight
+ * trip) are issued after the CTA has announced its arrival and fly while the others are still coming */
 __device__ __forceinline__ void barrier_arrive(unsigned long long *bar, unsigned long long &target, unsigned nb) {
-    __syncthreads();
+    compute_sync();
     if (threadIdx.x == 0) {
         target += nb;
-        __threadfence();
-        atomicAdd(bar, 1ULL);
+        red_release_inc(bar);
     }
 }
 __device__ __forceinline__ void barrier_wait(unsigned long long *bar, const unsigned long long &target) {
     if (threadIdx.x == 0) {
         while (ld_acquire_u64(bar) < target) { }
-        __threadfence();
     }
-    __syncthreads();
+    compute_sync();
 }
 
 __device__ __forceinline__ void row_range(int rows, int cta, int ncta, int &r0, int &r1) {
@@ -95,7 +118,7 @@ __device__ __forceinline__ void row_range(int rows, int cta, int ncta, int &r0, 
 __device__ __forceinline__ void stage_vec(float *xs, const float *src, int n) {
     for (int i = threadIdx.x * 4; i < n; i += FUSED_THREADS * 4)
         *reinterpret_cast<float4 *>(xs + i) = __ldcg(reinterpret_cast<const float4 *>(src + i));
-    __syncthreads();
+    compute_sync();
 }
 
 /* xs = rmsnorm(src) * w, computed by every CTA for itself */
@@ -109,11 +132,11 @@ __device__ __forceinline__ void stage_rmsnorm(float *xs, const float *src, const
         float ss = v0.x * v0.x;
         ss = fmaf(v0.y, v0.y, ss); ss = fmaf(v0.z, v0.z, ss); ss = fmaf(v0.w, v0.w, ss);
         ss = fmaf(v1.x, v1.x, ss); ss = fmaf(v1.y, v1.y, ss); ss = fmaf(v1.z, v1.z, ss); ss = fmaf(v1.w, v1.w, ss);
-        ss = block_sum(ss, red);
+        ss = csum(ss, red);
         const float inv = 1.0f / sqrtf(ss / (float)n + eps);
         if (i0 < n) *reinterpret_cast<float4 *>(xs + i0) = make_float4(v0.x * inv * w0.x, v0.y * inv * w0.y, v0.z * inv * w0.z, v0.w * inv * w0.w);
         if (i1 < n) *reinterpret_cast<float4 *>(xs + i1) = make_float4(v1.x * inv * w1.x, v1.y * inv * w1.y, v1.z * inv * w1.z, v1.w * inv * w1.w);
-        __syncthreads();
+        compute_sync();
         return;
     }
     float ss = 0.0f;
@@ -122,10 +145,10 @@ __device__ __forceinline__ void stage_rmsnorm(float *xs, const float *src, const
         *reinterpret_cast<float4 *>(xs + i) = v;
         ss = fmaf(v.x, v.x, ss); ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
     }
-    ss = block_sum(ss, red);
+    ss = csum(ss, red);
     const float inv = 1.0f / sqrtf(ss / (float)n + eps);
     for (int i = threadIdx.x; i < n; i += FUSED_THREADS) xs[i] = xs[i] * inv * w[i];
-    __syncthreads();
+    compute_sync();
 }
 
 __device__ __forceinline__ float dot8f(const uint4 w, const float4 x0, const float4 x1, float acc) {
@@ -226,6 +249,7 @@ __device__ __forceinline__ bool phase_seg(const FusedArgs &a, const LmDev &lm, i
 }
 __device__ __forceinline__ void prefetch_phase(const FusedArgs &a, const LmDev &lm, int p, int cta, int ncta) {
     Seg3 s; int cols;
+    if (a.flags & 1) return;
     if (phase_seg(a, lm, p >> 2, p & 3, s, cols)) prefetch_seg(s, cols, cta, ncta);
 }
 

@@ -19,7 +19,7 @@ __device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, i
     const int n = pos + 1;
     p.S = (n + 31) / 32;
     if (p.S > FUSED_MAX_SPLIT) p.S = FUSED_MAX_SPLIT;
-    while (p.S > 1 && lm.heads * p.S > ncta) p.S--;
+    while (p.S > 1 && (lm.heads * p.S > ncta || lm.heads * p.S * (lm.head_dim + 4) > 2 * ATT_STAGE_MAX * lm.head_dim)) p.S--;
     p.active = cta < lm.heads * p.S;
     p.h = p.active ? cta / p.S : 0;
     p.sp = cta - p.h * p.S;
@@ -79,7 +79,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
             dst[i + half] = xb * cs[i + half] + xa * sn[i + half];
         }
     }
-    __syncthreads();
+    compute_sync();
     if (p.sp == 0 && h % rep == 0)
         for (int i = tid; i < hd; i += FUSED_THREADS) { kc[(size_t)pos * kvd + g * hd + i] = ks[i]; vc[(size_t)pos * kvd + g * hd + i] = __ldcg(vr + i); }
 
@@ -117,13 +117,13 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
             if (lane == 0) sc[t - t0] = d * scale;
         }
     }
-    __syncthreads();
+    compute_sync();
     float mx = -3.402823466e+38f;
     for (int t = tid; t < t1 - t0; t += FUSED_THREADS) mx = fmaxf(mx, sc[t]);
-    mx = block_max(mx, red);
+    mx = cmax(mx, red);
     float tot = 0.0f;
     for (int t = tid; t < t1 - t0; t += FUSED_THREADS) { const float e = __expf(sc[t] - mx); sc[t] = e; tot += e; }
-    tot = block_sum(tot, red);
+    tot = csum(tot, red);
     /* weighted V: thread groups of hd lanes take positions round-robin, then fold the groups */
     const int grp = tid / hd, dim = tid - grp * hd;
     if (grp < ngrp) {
@@ -144,130 +144,39 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
         }
         op[grp * hd + dim] = o;
     }
-    __syncthreads();
-    float *mine = a.part + ((size_t)h * FUSED_MAX_SPLIT + p.sp) * (hd + 2);
-    if (tid < hd) { float o = 0.0f; for (int k = 0; k < ngrp; k++) o += op[k * hd + tid]; mine[2 + tid] = o; }
+    compute_sync();
+    /* partial record: [max, sum, -, -, out[hd]]; records of one head are contiguous and 16-byte aligned */
+    float *mine = a.part + ((size_t)h * p.S + p.sp) * (hd + 4);
+    if (tid < hd) { float o = 0.0f; for (int k = 0; k < ngrp; k++) o += op[k * hd + tid]; mine[4 + tid] = o; }
     if (tid == 0) { mine[0] = mx; mine[1] = tot; }
 }
 
-/* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector */
-__device__ __forceinline__ void stage_attention_out(float *xs, float *scr, const FusedArgs &a, const LmDev &lm, int S) {
-    const int hd = lm.head_dim, heads = lm.heads, qd = heads * hd, tid = threadIdx.x;
-    float *mb = scr, *lb = scr + heads * FUSED_MAX_SPLIT, *fac = lb + heads * FUSED_MAX_SPLIT;
-    /* every load of the phase is independent of every other: issue them all, then fold */
-    float v[4][FUSED_MAX_SPLIT];
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-        const int i = tid + r * FUSED_THREADS, h = i / hd, d = i - h * hd;
-#pragma unroll
-        for (int k = 0; k < FUSED_MAX_SPLIT; k++)
-            v[r][k] = (i < qd && k < S) ? __ldcg(a.part + ((size_t)h * FUSED_MAX_SPLIT + k) * (hd + 2) + 2 + d) : 0.0f;
+/* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector.
+ * The heads*S records (contiguous in HBM/L2) are copied into `land` (the KV stage, idle in this phase) with
+ * cp.async - one round trip, no registers tied up - and folded from shared memory. */
+__device__ __forceinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
+    const int hd = lm.head_dim, heads = lm.heads, qd = heads * hd, tid = threadIdx.x, rec = hd + 4;
+    const int n16 = heads * S * rec / 4;
+    for (int i = tid; i < n16; i += FUSED_THREADS) {
+        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(land + i * 4);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(a.part + i * 4));
     }
-    for (int idx = tid; idx < heads * S; idx += FUSED_THREADS) {
-        const int h = idx / S, k = idx - h * S;
-        const float *pp = a.part + ((size_t)h * FUSED_MAX_SPLIT + k) * (hd + 2);
-        mb[h * FUSED_MAX_SPLIT + k] = __ldcg(pp);
-        lb[h * FUSED_MAX_SPLIT + k] = __ldcg(pp + 1);
-    }
-    __syncthreads();
+    asm volatile("cp.async.commit_group;");
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    compute_sync();
+    float *fac = scr;
     for (int h = tid; h < heads; h += FUSED_THREADS) {
         float M = -3.402823466e+38f, L = 0.0f;
-        for (int k = 0; k < S; k++) M = fmaxf(M, mb[h * FUSED_MAX_SPLIT + k]);
-        for (int k = 0; k < S; k++) L = fmaf(lb[h * FUSED_MAX_SPLIT + k], __expf(mb[h * FUSED_MAX_SPLIT + k] - M), L);
-        for (int k = 0; k < S; k++) fac[h * FUSED_MAX_SPLIT + k] = __expf(mb[h * FUSED_MAX_SPLIT + k] - M) / L;
+        for (int k = 0; k < S; k++) M = fmaxf(M, land[(h * S + k) * rec]);
+        for (int k = 0; k < S; k++) L = fmaf(land[(h * S + k) * rec + 1], __expf(land[(h * S + k) * rec] - M), L);
+        for (int k = 0; k < S; k++) fac[h * FUSED_MAX_SPLIT + k] = __expf(land[(h * S + k) * rec] - M) / L;
     }
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-        const int i = tid + r * FUSED_THREADS, h = i / hd;
-        if (i < qd) {
-            float acc = 0.0f;
-#pragma unroll
-            for (int k = 0; k < FUSED_MAX_SPLIT; k++) if (k < S) acc = fmaf(v[r][k], fac[h * FUSED_MAX_SPLIT + k], acc);
-            xs[i] = acc;
-        }
-    }
-    for (int i = tid + 4 * FUSED_THREADS; i < qd; i += FUSED_THREADS) {          /* qd > 2048: plain loop */
+    compute_sync();
+    for (int i = tid; i < qd; i += FUSED_THREADS) {
         const int h = i / hd, d = i - h * hd;
         float acc = 0.0f;
-        for (int k = 0; k < S; k++) acc = fmaf(__ldcg(a.part + ((size_t)h * FUSED_MAX_SPLIT + k) * (hd + 2) + 2 + d), fac[h * FUSED_MAX_SPLIT + k], acc);
+        for (int k = 0; k < S; k++) acc = fmaf(land[(h * S + k) * rec + 4 + d], fac[h * FUSED_MAX_SPLIT + k], acc);
         xs[i] = acc;
     }
-    __syncthreads();
-}
-
-/* dynamic smem: [xs_floats | attention scratch | KV stage 2*ATT_STAGE_MAX*hd] floats */
-__global__ void __launch_bounds__(FUSED_THREADS, 1) k_lm_fused(const FusedArgs a) {
-    extern __shared__ __align__(16) float sm[];
-    __shared__ float red[32];
-    const LmDev &lm = *a.lm;
-    const int cta = blockIdx.x, ncta = gridDim.x, tid = threadIdx.x;
-    const int H = lm.hidden, I = lm.inter, L = lm.layers;
-    const int pos = *a.pos_ptr + a.pos_add;
-    float *att_sm = sm + a.xs_floats, *kvs = att_sm + a.att_floats;
-    const AttPlan plan = att_plan(lm, pos, cta, ncta);
-    unsigned long long target = 0;
-    if (tid == 0) { const unsigned long long v = ld_acquire_u64(a.bar); target = v - v % (unsigned long long)ncta; }
-    prefetch_phase(a, lm, 0, cta, ncta);
-    prefetch_phase(a, lm, 1, cta, ncta);
-    Seg3 s; int cols;
-#define PROF(i) do { if (a.prof && tid == 0 && l == a.prof_layer) a.prof[cta * 16 + (i)] = clock64(); } while (0)
-    for (int l = 0; l < L; l++) {
-        const LmLayerDev &w = lm.layer[l];
-        /* P1: RMSNorm -> Q,K,V */
-        PROF(0);
-        stage_rmsnorm(sm, a.x, w.in_norm, H, lm.eps, red);
-        PROF(1);
-        phase_seg(a, lm, l, 0, s, cols);
-        cta_gemv(s, cols, sm, NULL, cta, ncta);
-        att_stage_issue(a, lm, plan, l, pos, kvs);
-        PROF(2);
-        barrier_arrive(a.bar, target, ncta);
-        prefetch_phase(a, lm, l * 4 + 2, cta, ncta);          /* issued while the barrier spins */
-        barrier_wait(a.bar, target);
-        PROF(3);
-        /* P2: attention partials */
-        cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
-        PROF(4);
-        barrier_arrive(a.bar, target, ncta);
-        prefetch_phase(a, lm, l * 4 + 3, cta, ncta);
-        barrier_wait(a.bar, target);
-        PROF(5);
-        /* P3: combine partials -> O projection + residual */
-        stage_attention_out(sm, att_sm, a, lm, plan.S);
-        PROF(15);
-        phase_seg(a, lm, l, 1, s, cols);
-        cta_gemv(s, cols, sm, a.x, cta, ncta);
-        PROF(6);
-        barrier_arrive(a.bar, target, ncta);
-        prefetch_phase(a, lm, l * 4 + 4, cta, ncta);
-        barrier_wait(a.bar, target);
-        PROF(7);
-        /* P4: RMSNorm -> gate/up -> SwiGLU */
-        stage_rmsnorm(sm, a.x, w.post_norm, H, lm.eps, red);
-        PROF(8);
-        cta_swiglu(w.gate, w.up, a.g, I, H, sm, cta, ncta);
-        PROF(9);
-        barrier_arrive(a.bar, target, ncta);
-        prefetch_phase(a, lm, l * 4 + 5, cta, ncta);
-        barrier_wait(a.bar, target);
-        PROF(10);
-        /* P5: down projection + residual */
-        stage_vec(sm, a.g, I);
-        PROF(11);
-        phase_seg(a, lm, l, 3, s, cols);
-        cta_gemv(s, cols, sm, a.x, cta, ncta);
-        PROF(12);
-        grid_barrier(a.bar, target, ncta);
-        PROF(13);
-    }
-#undef PROF
-    /* final norm (every CTA, into shared memory), then x is overwritten in place with the normed hidden */
-    stage_rmsnorm(sm, a.x, lm.final_norm, H, lm.eps, red);
-    grid_barrier(a.bar, target, ncta);
-    if (cta == 0) {
-        for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = sm[i];
-        if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
-    }
-    if (phase_seg(a, lm, L, 0, s, cols)) cta_gemv(s, cols, sm, NULL, cta, ncta);
+    compute_sync();
 }

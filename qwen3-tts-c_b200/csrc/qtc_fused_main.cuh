@@ -1,0 +1,197 @@
+/*
+ * qtc_fused_main.cuh - k_lm_fused: one decoder-stack step as one persistent cooperative kernel,
+ * 148 CTAs x 16 warps.  See qtc_fused.cuh (barriers, staging, row split) and qtc_fused_kernel.cuh (attention).
+ *
+ * Weights do not depend on activations, so the first "trip" of every GEMV phase - each warp's first two
+ * rows, eight 128-bit loads per lane per row, 64 registers - is issued right after the CTA ARRIVES at the
+ * grid barrier that precedes the phase and is consumed after the barrier and the input staging: one DRAM
+ * round trip per phase moves off the critical path.  (A TMA-bulk shared-memory ring and an L2 bulk prefetch
+ * two phases ahead were both measured slower on B200 at batch 1: profiles/README.md.)
+ *
+ * dynamic shared memory: [ xs | attention scratch | KV stage 2 x 64 x hd ]
+ */
+#pragma once
+#include "qtc_fused_kernel.cuh"
+
+#define FUSED_BLOCK FUSED_THREADS
+
+#define PFJ 4                      /* 16-byte pieces per lane per row held across the barrier */
+struct WTrip { uint4 a[PFJ], b[PFJ]; };
+
+/* rows (ra, rb) of `cols` bf16: lane's pieces lane+32j, j<8 */
+__device__ __forceinline__ void trip_issue(WTrip &t, const uint16_t *ra, const uint16_t *rb, int cols) {
+    const int lane = threadIdx.x & 31, n8 = cols >> 3;
+    const uint4 *w0 = reinterpret_cast<const uint4 *>(ra), *w1 = reinterpret_cast<const uint4 *>(rb);
+#pragma unroll
+    for (int j = 0; j < PFJ; j++) {
+        const int p = lane + 32 * j;
+        if (p < n8) { t.a[j] = ldg_stream(w0 + p); t.b[j] = ldg_stream(w1 + p); }
+    }
+}
+/* finish the two dot products: the prefetched pieces, then (cols > 2048) the rest of the rows */
+__device__ __forceinline__ void trip_finish(const WTrip &t, const uint16_t *ra, const uint16_t *rb, const float *xs, int cols, float &oa, float &ob) {
+    const int lane = threadIdx.x & 31, n8 = cols >> 3;
+    const float4 *x4 = reinterpret_cast<const float4 *>(xs);
+    float a = 0.0f, b = 0.0f;
+#pragma unroll
+    for (int j = 0; j < PFJ; j++) {
+        const int p = lane + 32 * j;
+        if (p < n8) { a = dot8f(t.a[j], x4[2 * p], x4[2 * p + 1], a); b = dot8f(t.b[j], x4[2 * p], x4[2 * p + 1], b); }
+    }
+    if (n8 > 32 * PFJ) {
+        const uint4 *w0 = reinterpret_cast<const uint4 *>(ra), *w1 = reinterpret_cast<const uint4 *>(rb);
+        int i = lane + 32 * PFJ;
+        for (; i + 96 < n8; i += 128) {
+            const uint4 a0 = ldg_stream(w0 + i), a1 = ldg_stream(w0 + i + 32), a2 = ldg_stream(w0 + i + 64), a3 = ldg_stream(w0 + i + 96);
+            const uint4 b0 = ldg_stream(w1 + i), b1 = ldg_stream(w1 + i + 32), b2 = ldg_stream(w1 + i + 64), b3 = ldg_stream(w1 + i + 96);
+            a = dot8f(a0, x4[2 * i], x4[2 * i + 1], a);           b = dot8f(b0, x4[2 * i], x4[2 * i + 1], b);
+            a = dot8f(a1, x4[2 * i + 64], x4[2 * i + 65], a);     b = dot8f(b1, x4[2 * i + 64], x4[2 * i + 65], b);
+            a = dot8f(a2, x4[2 * i + 128], x4[2 * i + 129], a);   b = dot8f(b2, x4[2 * i + 128], x4[2 * i + 129], b);
+            a = dot8f(a3, x4[2 * i + 192], x4[2 * i + 193], a);   b = dot8f(b3, x4[2 * i + 192], x4[2 * i + 193], b);
+        }
+        for (; i < n8; i += 32) {
+            const uint4 a0 = ldg_stream(w0 + i), b0 = ldg_stream(w1 + i);
+            a = dot8f(a0, x4[2 * i], x4[2 * i + 1], a);
+            b = dot8f(b0, x4[2 * i], x4[2 * i + 1], b);
+        }
+    }
+    oa = warp_sum(a);
+    ob = warp_sum(b);
+}
+
+/* the row pair a warp starts a plain phase with (both rows valid or rb == ra) */
+__device__ __forceinline__ bool first_pair(const Seg3 &s, int cols, int cta, int ncta, int &r, int &rb, int &r1) {
+    const int total = s.rows[0] + (s.n > 1 ? s.rows[1] : 0) + (s.n > 2 ? s.rows[2] : 0);
+    int r0;
+    row_range(total, cta, ncta, r0, r1);
+    r = r0 + (threadIdx.x >> 5);
+    rb = r + FUSED_WARPS < r1 ? r + FUSED_WARPS : r;
+    return r < r1;
+}
+__device__ __forceinline__ void gemv_prefetch(WTrip &t, const Seg3 &s, int cols, int cta, int ncta) {
+    int r, rb, r1;
+    if (!first_pair(s, cols, cta, ncta, r, rb, r1)) return;
+    float *d0, *d1;
+    trip_issue(t, seg_row(s, r, cols, d0), seg_row(s, rb, cols, d1), cols);
+}
+__device__ __forceinline__ void gemv_run(const WTrip &t, const Seg3 &s, int cols, const float *xs, const float *resid, int cta, int ncta) {
+    int r, rb, r1;
+    if (!first_pair(s, cols, cta, ncta, r, rb, r1)) return;
+    const int lane = threadIdx.x & 31;
+    float *da, *db;
+    const uint16_t *pa = seg_row(s, r, cols, da), *pb = seg_row(s, rb, cols, db);
+    float va, vb;
+    trip_finish(t, pa, pb, xs, cols, va, vb);
+    if (lane == 0) {
+        *da = resid ? __ldcg(resid + r) + va : va;
+        if (rb != r) *db = resid ? __ldcg(resid + rb) + vb : vb;
+    }
+    for (r += 2 * FUSED_WARPS; r < r1; r += 2 * FUSED_WARPS) {
+        rb = r + FUSED_WARPS < r1 ? r + FUSED_WARPS : r;
+        pa = seg_row(s, r, cols, da); pb = seg_row(s, rb, cols, db);
+        warp_dot2(pa, pb, xs, cols, va, vb);
+        if (lane == 0) {
+            *da = resid ? __ldcg(resid + r) + va : va;
+            if (rb != r) *db = resid ? __ldcg(resid + rb) + vb : vb;
+        }
+    }
+}
+/* gate/up: the pair is (gate row u, up row u) */
+__device__ __forceinline__ void swiglu_prefetch(WTrip &t, const uint16_t *gate, const uint16_t *up, int inter, int cols, int cta, int ncta) {
+    int u0, u1;
+    row_range(inter, cta, ncta, u0, u1);
+    const int u = u0 + (threadIdx.x >> 5);
+    if (u < u1) trip_issue(t, gate + (size_t)u * cols, up + (size_t)u * cols, cols);
+}
+__device__ __forceinline__ void swiglu_run(const WTrip &t, const uint16_t *gate, const uint16_t *up, float *g, int inter, int cols,
+                                           const float *xs, int cta, int ncta) {
+    int u0, u1;
+    row_range(inter, cta, ncta, u0, u1);
+    const int lane = threadIdx.x & 31;
+    int u = u0 + (threadIdx.x >> 5);
+    if (u >= u1) return;
+    float va, vb;
+    trip_finish(t, gate + (size_t)u * cols, up + (size_t)u * cols, xs, cols, va, vb);
+    if (lane == 0) g[u] = swiglu_act<QTC_FAST>(va, vb);
+    for (u += FUSED_WARPS; u < u1; u += FUSED_WARPS) {
+        warp_dot2(gate + (size_t)u * cols, up + (size_t)u * cols, xs, cols, va, vb);
+        if (lane == 0) g[u] = swiglu_act<QTC_FAST>(va, vb);
+    }
+}
+
+__global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a) {
+    extern __shared__ __align__(128) float fused_smem[];
+    float *sm = fused_smem;
+    __shared__ float red[32];
+    const LmDev &lm = *a.lm;
+    const int cta = blockIdx.x, ncta = gridDim.x, tid = threadIdx.x;
+    const int H = lm.hidden, I = lm.inter, L = lm.layers;
+    float *att_sm = sm + a.xs_floats, *kvs = att_sm + a.att_floats;
+    const int pos = *a.pos_ptr + a.pos_add;
+    const AttPlan plan = att_plan(lm, pos, cta, ncta);
+    unsigned long long target = 0;
+    if (tid == 0) { const unsigned long long v = ld_acquire_u64(a.bar); target = v - v % (unsigned long long)ncta; }
+    Seg3 s; int cols;
+    WTrip tp;
+    phase_seg(a, lm, 0, 0, s, cols);
+    gemv_prefetch(tp, s, cols, cta, ncta);
+#define PROF(i) do { if (a.prof && tid == 0 && l == a.prof_layer) a.prof[cta * 32 + (i)] = clock64(); } while (0)
+    for (int l = 0; l < L; l++) {
+        const LmLayerDev &w = lm.layer[l];
+        /* P1: RMSNorm -> Q,K,V (first trip already in registers) */
+        PROF(0);
+        stage_rmsnorm(sm, a.x, w.in_norm, H, lm.eps, red);
+        PROF(1);
+        phase_seg(a, lm, l, 0, s, cols);
+        gemv_run(tp, s, cols, sm, NULL, cta, ncta);
+        att_stage_issue(a, lm, plan, l, pos, kvs);
+        PROF(2);
+        grid_barrier(a.bar, target, ncta);
+        PROF(3);
+        /* P2: attention partials */
+        cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
+        PROF(4);
+        barrier_arrive(a.bar, target, ncta);
+        phase_seg(a, lm, l, 1, s, cols);
+        gemv_prefetch(tp, s, cols, cta, ncta);
+        barrier_wait(a.bar, target);
+        PROF(5);
+        /* P3: combine partials -> O projection + residual */
+        stage_attention_out(sm, att_sm, kvs, a, lm, plan.S);
+        PROF(15);
+        gemv_run(tp, s, cols, sm, a.x, cta, ncta);
+        PROF(6);
+        barrier_arrive(a.bar, target, ncta);
+        swiglu_prefetch(tp, w.gate, w.up, I, H, cta, ncta);
+        barrier_wait(a.bar, target);
+        PROF(7);
+        /* P4: RMSNorm -> gate/up -> SwiGLU */
+        stage_rmsnorm(sm, a.x, w.post_norm, H, lm.eps, red);
+        PROF(8);
+        swiglu_run(tp, w.gate, w.up, a.g, I, H, sm, cta, ncta);
+        PROF(9);
+        barrier_arrive(a.bar, target, ncta);
+        phase_seg(a, lm, l, 3, s, cols);
+        gemv_prefetch(tp, s, cols, cta, ncta);
+        barrier_wait(a.bar, target);
+        PROF(10);
+        /* P5: down projection + residual */
+        stage_vec(sm, a.g, I);
+        PROF(11);
+        gemv_run(tp, s, cols, sm, a.x, cta, ncta);
+        PROF(12);
+        barrier_arrive(a.bar, target, ncta);
+        if (phase_seg(a, lm, l + 1, 0, s, cols)) gemv_prefetch(tp, s, cols, cta, ncta);     /* next layer's QKV, or the head */
+        barrier_wait(a.bar, target);
+        PROF(13);
+    }
+#undef PROF
+    /* final norm (every CTA, into shared memory), then x is overwritten in place with the normed hidden */
+    stage_rmsnorm(sm, a.x, lm.final_norm, H, lm.eps, red);
+    grid_barrier(a.bar, target, ncta);
+    if (cta == 0) {
+        for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = sm[i];
+        if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
+    }
+    if (phase_seg(a, lm, L, 0, s, cols)) gemv_run(tp, s, cols, sm, NULL, cta, ncta);
+}

@@ -237,7 +237,7 @@ extern "C" double qwen_tts_cuda_bench_talker_step(qtc_ctx_t *c, int pos, int ite
  * (slot meaning: qtc_fused_kernel.cuh PROF(i)); out receives num_sms*16 values, returns num_sms */
 extern "C" int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *c, int pos, int layer, long long *out) {
     if (!c || !out || c->talker.layers <= 0) return -1;
-    const size_t n = (size_t)c->num_sms * 16;
+    const size_t n = (size_t)c->num_sms * 32;
     if (!c->prof) { c->prof = (long long *)qtc_dmalloc(c, n * 8); if (!c->prof) return -1; }
     cudaMemsetAsync(c->prof, 0, n * 8, c->stream);
     c->prof_layer = layer;

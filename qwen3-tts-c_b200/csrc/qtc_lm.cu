@@ -7,7 +7,7 @@
  * reads positions / tokens from device memory, so every sequence here can be
  * captured into a CUDA graph and replayed.
  */
-#include "qtc_fused_kernel.cuh"
+#include "qtc_fused_main.cuh"
 #include "qtc_gemv.cuh"
 #include "qtc_internal.h"
 #include "qtc_lm_kernels.cuh"
@@ -132,15 +132,19 @@ int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
 }
 
 /* mode 1: the whole step (+ optional head GEMV, + pos bump) as one persistent cooperative kernel */
-static int g_fused_attr = 0;
+static int g_fused_attr = 0, g_fused_max_smem = 0;
 static bool fused_ok(const qtc_ctx *c, const LmDev *lm) {
     return c->mode == 1 && c->arith == QTC_FAST && lm->head_dim <= FUSED_THREADS && lm->head_dim % 2 == 0 &&
-           lm->hidden % 8 == 0 && lm->inter % 8 == 0 && (lm->heads * lm->head_dim) % 8 == 0 && lm->heads <= c->num_sms;
+           lm->hidden % 8 == 0 && lm->inter % 8 == 0 && (lm->heads * lm->head_dim) % 8 == 0 && lm->heads <= c->num_sms &&
+           lm->heads * (lm->head_dim + 4) <= 2 * ATT_STAGE_MAX * lm->head_dim;
 }
 static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
                       const uint16_t *head_w, int head_rows, float *logits, GenState *st) {
     if (!g_fused_attr) {
-        QTC_CUDA(cudaFuncSetAttribute(k_lm_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        cudaFuncAttributes fa;
+        QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_fused));
+        g_fused_max_smem = 227 * 1024 - (int)fa.sharedSizeBytes;         /* opt-in limit includes the static part */
+        QTC_CUDA(cudaFuncSetAttribute(k_lm_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, g_fused_max_smem));
         g_fused_attr = 1;
     }
     FusedArgs a;
@@ -152,16 +156,20 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     a.head_w = head_w; a.head_rows = head_rows; a.logits = logits;
     a.bar = c->bar; a.head_cnt = c->head_cnt; a.part = c->attn_part; a.st = st;
     a.prof = lm == &c->talker ? c->prof : NULL; a.prof_layer = c->prof_layer;
+    { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
     const int qd = lm->heads * lm->head_dim;
     int vec = lm->hidden > lm->inter ? lm->hidden : lm->inter;
     if (qd > vec) vec = qd;
-    const int attn = 2 * lm->head_dim + FUSED_THREADS + (b->kv_max > 64 ? b->kv_max : 64) + 64;
+    /* score buffer: a staged chunk (<= 64) or, for long contexts, ceil(n / splits) positions */
+    int sc = (b->kv_max + c->num_sms / lm->heads - 1) / (c->num_sms / lm->heads > 0 ? c->num_sms / lm->heads : 1);
+    if (sc < 64) sc = 64;
+    const int attn = 2 * lm->head_dim + FUSED_THREADS + sc + 64 + 3 * lm->heads * FUSED_MAX_SPLIT;
     a.xs_floats = (vec + 3) & ~3;
     a.att_floats = (attn + 3) & ~3;
     const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
-    if (smem > 200 * 1024) { qtc_set_error("fused step: %zu bytes of shared memory needed", smem); return -1; }
+    if (smem > (size_t)g_fused_max_smem) { qtc_set_error("fused step: %zu bytes of shared memory needed, %d available", smem, g_fused_max_smem); return -1; }
     void *args[] = {&a};
-    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_THREADS), args, smem, c->stream));
+    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
     c->launches++;
     return 0;
 }

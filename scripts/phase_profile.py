@@ -27,10 +27,10 @@ def main():
     assert ctx
     cuda.qwen_tts_cuda_set_mode(ctx, 1)
     cuda.qwen_tts_cuda_debug_phase_clocks.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_longlong)]
-    out = np.zeros(148 * 16 * 2, dtype=np.int64)
+    out = np.zeros(148 * 32 * 2, dtype=np.int64)
     n = cuda.qwen_tts_cuda_debug_phase_clocks(ctx, pos, layer, out.ctypes.data_as(C.POINTER(C.c_longlong)))
     assert n > 0
-    raw = out[: n * 16].reshape(n, 16).astype(np.float64)
+    raw = out[: n * 32].reshape(n, 32).astype(np.float64)
     for nm, a, b in (("prefetch issue (P1)", 0, 14), ("prefetch+stage (P3)", 5, 15)):
         dd = (raw[:, b] - raw[:, a]) / 1.965e3
         print(f"  [{nm}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
