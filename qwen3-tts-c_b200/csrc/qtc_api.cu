@@ -127,7 +127,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     qtc_ctx *c = new qtc_ctx();
     c->host = *desc;
     c->H = desc->talker.hidden; c->G = desc->num_code_groups; c->max_batch = max_batch > 0 ? max_batch : 1;
-    c->mode = 0; c->arith = 0; c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
+    c->mode = 1; c->arith = 0; c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
     c->codec = NULL; c->codes = NULL; c->trailing = NULL; c->prefill = NULL; c->codes_cap = c->trailing_cap = c->prefill_cap = 0;
     memset(&c->tk, 0, sizeof(c->tk)); memset(&c->st, 0, sizeof(c->st)); memset(&c->perf, 0, sizeof(c->perf));
     memset(&c->talker, 0, sizeof(c->talker)); memset(&c->sub, 0, sizeof(c->sub));

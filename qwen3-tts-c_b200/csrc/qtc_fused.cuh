@@ -48,6 +48,25 @@ struct FusedArgs {
     long long *prof; int prof_layer; /* optional: clock64 stamps of one layer, 16 slots per CTA (debug / profiles) */
 };
 
+/* The sub-talker's whole code-group loop (qwen_tts_subtalker_generate, c/qwen_tts_talker.c:539-736) as a
+ * program for the same kernel: G stack steps, each preceded by an embedding gather + input projection and
+ * followed (g >= 1) by its lm_head and an in-kernel sample.  G == 0: a single plain step (talker). */
+struct SubProg {
+    int G;                                  /* num_code_groups, 0 = not a sub-talker launch */
+    int Hin;                                /* talker hidden: width of the gathered embedding rows */
+    const float *hidden;                    /* talker hidden state [Hin] (position 0 input) */
+    const uint16_t *emb0;                   /* talker codec embedding (input of position 1) */
+    const uint16_t *emb[QTC_MAX_GROUPS - 1];/* sub-talker embeddings (input of position g uses emb[g-2]) */
+    const uint16_t *in_w; const float *in_b;/* small_to_mtp_projection [h, Hin] (+bias) or NULL: copy / zero-pad */
+    const uint16_t *heads[QTC_MAX_GROUPS - 1];
+    int vocab;
+    int *codes;                             /* [G] device: codes[0] = first code on entry, the rest on exit */
+    SampleCfg cfg;
+    uint32_t seed_bits;                     /* the RNG is re-seeded every frame (c/qwen_tts_talker.c:718) */
+    float *scratch_f; int *scratch_i;       /* slow-path sampler scratch */
+    float *vec;                             /* [Hin] cross-CTA scratch for the gathered / projected input */
+};
+
 /* the 512 compute threads synchronise on named barrier 1; the producer warp (threads 512..543) never joins */
 #define NB_COMPUTE 1
 __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync %0, %1;" ::"n"(NB_COMPUTE), "n"(FUSED_THREADS) : "memory"); }

@@ -69,14 +69,35 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
         const float *src = warp == 0 ? qr : kr, *nw = warp == 0 ? w.q_norm : w.k_norm;
         float *dst = warp == 0 ? qs : ks;
         float ss = 0.0f;
-        for (int i = lane; i < hd; i += 32) { const float v = __ldcg(src + i); dst[i] = v; ss = fmaf(v, v, ss); }
-        ss = warp_sum(ss);
-        const float inv = 1.0f / sqrtf(ss / (float)hd + lm.eps);
-        __syncwarp();
-        for (int i = lane; i < half; i += 32) {
-            const float xa = dst[i] * inv * nw[i], xb = dst[i + half] * inv * nw[i + half];
-            dst[i] = xa * cs[i] - xb * sn[i];
-            dst[i + half] = xb * cs[i + half] + xa * sn[i + half];
+        if (hd == 128) {
+            /* all twelve loads of a lane are independent: issue them before the reduction */
+            float xa[2], xb[2], wa[2], wb[2], ca[2], cb[2], sa[2], sb[2];
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int i = lane + 32 * j;
+                xa[j] = __ldcg(src + i); xb[j] = __ldcg(src + i + 64);
+                wa[j] = nw[i]; wb[j] = nw[i + 64]; ca[j] = cs[i]; cb[j] = cs[i + 64]; sa[j] = sn[i]; sb[j] = sn[i + 64];
+                ss = fmaf(xa[j], xa[j], ss); ss = fmaf(xb[j], xb[j], ss);
+            }
+            ss = warp_sum(ss);
+            const float inv = 1.0f / sqrtf(ss / (float)hd + lm.eps);
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int i = lane + 32 * j;
+                const float ya = xa[j] * inv * wa[j], yb = xb[j] * inv * wb[j];
+                dst[i] = ya * ca[j] - yb * sa[j];
+                dst[i + 64] = yb * cb[j] + ya * sb[j];
+            }
+        } else {
+            for (int i = lane; i < hd; i += 32) { const float v = __ldcg(src + i); dst[i] = v; ss = fmaf(v, v, ss); }
+            ss = warp_sum(ss);
+            const float inv = 1.0f / sqrtf(ss / (float)hd + lm.eps);
+            __syncwarp();
+            for (int i = lane; i < half; i += 32) {
+                const float xa = dst[i] * inv * nw[i], xb = dst[i + half] * inv * nw[i + half];
+                dst[i] = xa * cs[i] - xb * sn[i];
+                dst[i + half] = xb * cs[i + half] + xa * sn[i + half];
+            }
         }
     }
     compute_sync();
@@ -118,12 +139,20 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
         }
     }
     compute_sync();
-    float mx = -3.402823466e+38f;
-    for (int t = tid; t < t1 - t0; t += FUSED_THREADS) mx = fmaxf(mx, sc[t]);
-    mx = cmax(mx, red);
-    float tot = 0.0f;
-    for (int t = tid; t < t1 - t0; t += FUSED_THREADS) { const float e = __expf(sc[t] - mx); sc[t] = e; tot += e; }
-    tot = csum(tot, red);
+    float mx = -3.402823466e+38f, tot = 0.0f;
+    const bool small = t1 - t0 <= 64;
+    if (small) {
+        /* <= 64 scores: every warp folds them for itself with shuffles - no block barriers on the critical path */
+        const int n0 = t1 - t0;
+        const float v0 = lane < n0 ? sc[lane] : -3.402823466e+38f, v1 = lane + 32 < n0 ? sc[lane + 32] : -3.402823466e+38f;
+        mx = warp_max(fmaxf(v0, v1));
+        tot = warp_sum((lane < n0 ? __expf(v0 - mx) : 0.0f) + (lane + 32 < n0 ? __expf(v1 - mx) : 0.0f));
+    } else {
+        for (int t = tid; t < t1 - t0; t += FUSED_THREADS) mx = fmaxf(mx, sc[t]);
+        mx = cmax(mx, red);
+        for (int t = tid; t < t1 - t0; t += FUSED_THREADS) { const float e = __expf(sc[t] - mx); sc[t] = e; tot += e; }
+        tot = csum(tot, red);
+    }
     /* weighted V: thread groups of hd lanes take positions round-robin, then fold the groups */
     const int grp = tid / hd, dim = tid - grp * hd;
     if (grp < ngrp) {
@@ -139,12 +168,16 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
 #pragma unroll
             for (int j = 0; j < 8; j++) {
                 const int t = tb + j * ngrp;
-                if (t < t1) o = fmaf(sc[t - t0], v[j], o);
+                if (t < t1) o = fmaf(small ? __expf(sc[t - t0] - mx) : sc[t - t0], v[j], o);
             }
         }
         op[grp * hd + dim] = o;
     }
     compute_sync();
+    if (p.S == 1) {                          /* no split: the head's output is final */
+        if (tid < hd) { float o = 0.0f; for (int k = 0; k < ngrp; k++) o += op[k * hd + tid]; a.att[h * hd + tid] = o / tot; }
+        return;
+    }
     /* partial record: [max, sum, -, -, out[hd]]; records of one head are contiguous and 16-byte aligned */
     float *mine = a.part + ((size_t)h * p.S + p.sp) * (hd + 4);
     if (tid < hd) { float o = 0.0f; for (int k = 0; k < ngrp; k++) o += op[k * hd + tid]; mine[4 + tid] = o; }

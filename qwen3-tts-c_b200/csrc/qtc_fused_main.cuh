@@ -81,18 +81,21 @@ __device__ __forceinline__ void gemv_run(const WTrip &t, const Seg3 &s, int cols
     float *da, *db;
     const uint16_t *pa = seg_row(s, r, cols, da), *pb = seg_row(s, rb, cols, db);
     float va, vb;
+    /* the residual values are requested BEFORE the dot products: their L2 round trip hides behind the weights */
+    float ea = resid ? __ldcg(resid + r) : 0.0f, eb = resid ? __ldcg(resid + rb) : 0.0f;
     trip_finish(t, pa, pb, xs, cols, va, vb);
     if (lane == 0) {
-        *da = resid ? __ldcg(resid + r) + va : va;
-        if (rb != r) *db = resid ? __ldcg(resid + rb) + vb : vb;
+        *da = ea + va;
+        if (rb != r) *db = eb + vb;
     }
     for (r += 2 * FUSED_WARPS; r < r1; r += 2 * FUSED_WARPS) {
         rb = r + FUSED_WARPS < r1 ? r + FUSED_WARPS : r;
         pa = seg_row(s, r, cols, da); pb = seg_row(s, rb, cols, db);
+        ea = resid ? __ldcg(resid + r) : 0.0f; eb = resid ? __ldcg(resid + rb) : 0.0f;
         warp_dot2(pa, pb, xs, cols, va, vb);
         if (lane == 0) {
-            *da = resid ? __ldcg(resid + r) + va : va;
-            if (rb != r) *db = resid ? __ldcg(resid + rb) + vb : vb;
+            *da = ea + va;
+            if (rb != r) *db = eb + vb;
         }
     }
 }
@@ -119,79 +122,126 @@ __device__ __forceinline__ void swiglu_run(const WTrip &t, const uint16_t *gate,
     }
 }
 
-__global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a) {
+#include "qtc_sample.cuh"
+
+/* k_lm_fused(a0, sp): sp.G == 0 -> one stack step (talker: + codec head + KV length);
+ *                     sp.G  > 0 -> the sub-talker's G steps with gathers, heads and sampling inside. */
+__global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0, const SubProg sp) {
     extern __shared__ __align__(128) float fused_smem[];
     float *sm = fused_smem;
     __shared__ float red[32];
+    __shared__ SampleSmem S_samp;
+    __shared__ int s_codes[QTC_MAX_GROUPS];
+    __shared__ uint32_t s_rng;
+    FusedArgs a = a0;
     const LmDev &lm = *a.lm;
     const int cta = blockIdx.x, ncta = gridDim.x, tid = threadIdx.x;
     const int H = lm.hidden, I = lm.inter, L = lm.layers;
     float *att_sm = sm + a.xs_floats, *kvs = att_sm + a.att_floats;
-    const int pos = *a.pos_ptr + a.pos_add;
-    const AttPlan plan = att_plan(lm, pos, cta, ncta);
+    const int pos_base = *a.pos_ptr + a.pos_add;
     unsigned long long target = 0;
     if (tid == 0) { const unsigned long long v = ld_acquire_u64(a.bar); target = v - v % (unsigned long long)ncta; }
+    const int nsteps = sp.G > 0 ? sp.G : 1;
+    if (sp.G > 0 && tid == 0) s_codes[0] = sp.codes[0];
     Seg3 s; int cols;
     WTrip tp;
-    phase_seg(a, lm, 0, 0, s, cols);
-    gemv_prefetch(tp, s, cols, cta, ncta);
+    if (sp.G == 0) { phase_seg(a, lm, 0, 0, s, cols); gemv_prefetch(tp, s, cols, cta, ncta); }
+
+    for (int g = 0; g < nsteps; g++) {
+        const int pos = pos_base + g;
+        const AttPlan plan = att_plan(lm, pos, cta, ncta);
+        if (sp.G > 0) {
+            /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x */
+            compute_sync();
+            if (g == 0) stage_vec(sm, sp.hidden, sp.Hin);
+            else {
+                const uint16_t *row = (g == 1 ? sp.emb0 : sp.emb[g - 2]) + (size_t)s_codes[g - 1] * sp.Hin;
+                for (int i = tid; i < sp.Hin; i += FUSED_THREADS) sm[i] = bf16_to_f32(row[i]);
+                compute_sync();
+            }
+            if (sp.in_w) {
+                s.n = 1; s.w[0] = sp.in_w; s.out[0] = a.x; s.rows[0] = H; cols = sp.Hin;
+                cta_gemv(s, cols, sm, sp.in_b, cta, ncta);
+            } else if (cta == 0) {
+                for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = i < sp.Hin ? sm[i] : 0.0f;
+            }
+            a.head_w = g >= 1 ? sp.heads[g - 1] : NULL;
+            a.head_rows = sp.vocab;
+            barrier_arrive(a.bar, target, ncta);
+            phase_seg(a, lm, 0, 0, s, cols);
+            gemv_prefetch(tp, s, cols, cta, ncta);
+            barrier_wait(a.bar, target);
+        }
 #define PROF(i) do { if (a.prof && tid == 0 && l == a.prof_layer) a.prof[cta * 32 + (i)] = clock64(); } while (0)
-    for (int l = 0; l < L; l++) {
-        const LmLayerDev &w = lm.layer[l];
-        /* P1: RMSNorm -> Q,K,V (first trip already in registers) */
-        PROF(0);
-        stage_rmsnorm(sm, a.x, w.in_norm, H, lm.eps, red);
-        PROF(1);
-        phase_seg(a, lm, l, 0, s, cols);
-        gemv_run(tp, s, cols, sm, NULL, cta, ncta);
-        att_stage_issue(a, lm, plan, l, pos, kvs);
-        PROF(2);
-        grid_barrier(a.bar, target, ncta);
-        PROF(3);
-        /* P2: attention partials */
-        cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
-        PROF(4);
-        barrier_arrive(a.bar, target, ncta);
-        phase_seg(a, lm, l, 1, s, cols);
-        gemv_prefetch(tp, s, cols, cta, ncta);
-        barrier_wait(a.bar, target);
-        PROF(5);
-        /* P3: combine partials -> O projection + residual */
-        stage_attention_out(sm, att_sm, kvs, a, lm, plan.S);
-        PROF(15);
-        gemv_run(tp, s, cols, sm, a.x, cta, ncta);
-        PROF(6);
-        barrier_arrive(a.bar, target, ncta);
-        swiglu_prefetch(tp, w.gate, w.up, I, H, cta, ncta);
-        barrier_wait(a.bar, target);
-        PROF(7);
-        /* P4: RMSNorm -> gate/up -> SwiGLU */
-        stage_rmsnorm(sm, a.x, w.post_norm, H, lm.eps, red);
-        PROF(8);
-        swiglu_run(tp, w.gate, w.up, a.g, I, H, sm, cta, ncta);
-        PROF(9);
-        barrier_arrive(a.bar, target, ncta);
-        phase_seg(a, lm, l, 3, s, cols);
-        gemv_prefetch(tp, s, cols, cta, ncta);
-        barrier_wait(a.bar, target);
-        PROF(10);
-        /* P5: down projection + residual */
-        stage_vec(sm, a.g, I);
-        PROF(11);
-        gemv_run(tp, s, cols, sm, a.x, cta, ncta);
-        PROF(12);
-        barrier_arrive(a.bar, target, ncta);
-        if (phase_seg(a, lm, l + 1, 0, s, cols)) gemv_prefetch(tp, s, cols, cta, ncta);     /* next layer's QKV, or the head */
-        barrier_wait(a.bar, target);
-        PROF(13);
-    }
+        for (int l = 0; l < L; l++) {
+            const LmLayerDev &w = lm.layer[l];
+            /* P1: RMSNorm -> Q,K,V (first trip already in registers) */
+            PROF(0);
+            stage_rmsnorm(sm, a.x, w.in_norm, H, lm.eps, red);
+            PROF(1);
+            phase_seg(a, lm, l, 0, s, cols);
+            gemv_run(tp, s, cols, sm, NULL, cta, ncta);
+            att_stage_issue(a, lm, plan, l, pos, kvs);
+            PROF(2);
+            grid_barrier(a.bar, target, ncta);
+            PROF(3);
+            /* P2: attention partials */
+            cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
+            PROF(4);
+            barrier_arrive(a.bar, target, ncta);
+            phase_seg(a, lm, l, 1, s, cols);
+            gemv_prefetch(tp, s, cols, cta, ncta);
+            barrier_wait(a.bar, target);
+            PROF(5);
+            /* P3: combine partials -> O projection + residual */
+            if (plan.S == 1) stage_vec(sm, a.att, lm.heads * lm.head_dim);
+            else stage_attention_out(sm, att_sm, kvs, a, lm, plan.S);
+            PROF(15);
+            gemv_run(tp, s, cols, sm, a.x, cta, ncta);
+            PROF(6);
+            barrier_arrive(a.bar, target, ncta);
+            swiglu_prefetch(tp, w.gate, w.up, I, H, cta, ncta);
+            barrier_wait(a.bar, target);
+            PROF(7);
+            /* P4: RMSNorm -> gate/up -> SwiGLU */
+            stage_rmsnorm(sm, a.x, w.post_norm, H, lm.eps, red);
+            PROF(8);
+            swiglu_run(tp, w.gate, w.up, a.g, I, H, sm, cta, ncta);
+            PROF(9);
+            barrier_arrive(a.bar, target, ncta);
+            phase_seg(a, lm, l, 3, s, cols);
+            gemv_prefetch(tp, s, cols, cta, ncta);
+            barrier_wait(a.bar, target);
+            PROF(10);
+            /* P5: down projection + residual */
+            stage_vec(sm, a.g, I);
+            PROF(11);
+            gemv_run(tp, s, cols, sm, a.x, cta, ncta);
+            PROF(12);
+            barrier_arrive(a.bar, target, ncta);
+            if (phase_seg(a, lm, l + 1, 0, s, cols)) gemv_prefetch(tp, s, cols, cta, ncta);   /* next layer's QKV, or the head */
+            barrier_wait(a.bar, target);
+            PROF(13);
+        }
 #undef PROF
-    /* final norm (every CTA, into shared memory), then x is overwritten in place with the normed hidden */
-    stage_rmsnorm(sm, a.x, lm.final_norm, H, lm.eps, red);
-    grid_barrier(a.bar, target, ncta);
-    if (cta == 0) {
-        for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = sm[i];
-        if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
+        /* final norm (every CTA, into shared memory), then x is overwritten in place with the normed hidden */
+        stage_rmsnorm(sm, a.x, lm.final_norm, H, lm.eps, red);
+        grid_barrier(a.bar, target, ncta);
+        if (cta == 0 && sp.G == 0) {          /* (inside the sub-talker loop nobody reads the hidden state back) */
+            for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = sm[i];
+            if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
+        }
+        if (phase_seg(a, lm, L, 0, s, cols)) gemv_run(tp, s, cols, sm, NULL, cta, ncta);
+        if (sp.G > 0 && g >= 1) {
+            /* every CTA samples for itself from the same logits: same code everywhere, no broadcast needed */
+            grid_barrier(a.bar, target, ncta);
+            const int V = sp.vocab;
+            float *lg = sm, *vv = sm + V;
+            for (int i = tid; i < V; i += FUSED_THREADS) lg[i] = __ldcg(a.logits + i);
+            if (g == 1 && tid == 0) s_rng = sp.seed_bits;
+            __syncthreads();
+            const int tok = block_sample(lg, vv, V, sp.cfg.top_k, sp.cfg.top_p, sp.cfg.temperature, &s_rng, S_samp, sp.scratch_f, sp.scratch_i);
+            if (tid == 0) { s_codes[g] = tok; if (cta == 0) sp.codes[g] = tok; }
+        }
     }
-    if (phase_seg(a, lm, L, 0, s, cols)) gemv_run(tp, s, cols, sm, NULL, cta, ncta);
 }

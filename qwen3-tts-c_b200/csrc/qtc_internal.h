@@ -110,6 +110,7 @@ struct qtc_ctx {
     unsigned *head_cnt;           /* [heads] */
     float *attn_part;             /* [heads, 8, head_dim + 2] */
     int num_sms;
+    int prof_sub;                      /* 1: stamp the sub-talker's steps instead of the talker's */
     long long *prof; int prof_layer;   /* optional per-phase clock stamps of the fused kernel (debug) */
     int *sample_scratch;          /* slow-path sampler scratch */
     float *sample_scratch_f;

@@ -241,7 +241,9 @@ extern "C" int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *c, int pos, int layer
     if (!c->prof) { c->prof = (long long *)qtc_dmalloc(c, n * 8); if (!c->prof) return -1; }
     cudaMemsetAsync(c->prof, 0, n * 8, c->stream);
     c->prof_layer = layer;
-    if (qwen_tts_cuda_bench_talker_step(c, pos, 2, 1) < 0) return -1;
+    c->prof_sub = pos < 0;            /* pos < 0: profile the sub-talker frame (last code group wins) */
+    if ((pos < 0 ? qwen_tts_cuda_bench_subtalker(c, 2, 1) : qwen_tts_cuda_bench_talker_step(c, pos, 2, 1)) < 0) return -1;
+    c->prof_sub = 0;
     QTC_CUDA(cudaMemcpy(out, c->prof, n * 8, cudaMemcpyDeviceToHost));
     c->prof_layer = -1;
     return c->num_sms;

@@ -139,7 +139,7 @@ static bool fused_ok(const qtc_ctx *c, const LmDev *lm) {
            lm->heads * (lm->head_dim + 4) <= 2 * ATT_STAGE_MAX * lm->head_dim;
 }
 static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
-                      const uint16_t *head_w, int head_rows, float *logits, GenState *st) {
+                      const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog = NULL) {
     if (!g_fused_attr) {
         cudaFuncAttributes fa;
         QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_fused));
@@ -155,11 +155,18 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     a.pos_ptr = pos_ptr; a.pos_add = pos_add;
     a.head_w = head_w; a.head_rows = head_rows; a.logits = logits;
     a.bar = c->bar; a.head_cnt = c->head_cnt; a.part = c->attn_part; a.st = st;
-    a.prof = lm == &c->talker ? c->prof : NULL; a.prof_layer = c->prof_layer;
+    a.prof = (c->prof_sub ? lm == &c->sub : lm == &c->talker) ? c->prof : NULL; a.prof_layer = c->prof_layer;
     { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
     const int qd = lm->heads * lm->head_dim;
     int vec = lm->hidden > lm->inter ? lm->hidden : lm->inter;
     if (qd > vec) vec = qd;
+    SubProg sp;
+    memset(&sp, 0, sizeof(sp));
+    if (prog) {
+        sp = *prog;
+        if (2 * sp.vocab > vec) vec = 2 * sp.vocab;       /* the in-kernel sampler works in the staged-vector region */
+        if (sp.Hin > vec) vec = sp.Hin;
+    }
     /* score buffer: a staged chunk (<= 64) or, for long contexts, ceil(n / splits) positions */
     int sc = (b->kv_max + c->num_sms / lm->heads - 1) / (c->num_sms / lm->heads > 0 ? c->num_sms / lm->heads : 1);
     if (sc < 64) sc = 64;
@@ -168,7 +175,7 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     a.att_floats = (attn + 3) & ~3;
     const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
     if (smem > (size_t)g_fused_max_smem) { qtc_set_error("fused step: %zu bytes of shared memory needed, %d available", smem, g_fused_max_smem); return -1; }
-    void *args[] = {&a};
+    void *args[] = {&a, &sp};
     QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
     c->launches++;
     return 0;
@@ -254,10 +261,29 @@ static int sub_sample(qtc_ctx *c, int g, int *codes_out_dev, int reseed) {
 }
 
 
+/* the parallel sampler paths only (greedy, or top-k <= 1024 with top_p >= 1): the slow path uses one global scratch */
+static bool sampler_fusable(const qtc_ctx *c) {
+    const int k = c->params.subtalker_top_k;
+    return c->params.subtalker_top_p >= 1.0f && k > 0 && k < c->sub.vocab && k <= SAMPLE_MAX_K;
+}
+
 /* qwen_tts_subtalker_generate on device.  first_code_ptr: device int (codes_out_dev[0] already holds it). */
 int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code_ptr, int *codes_out_dev) {
     const LmDev *lm = &c->sub;
     const int G = c->G, H = c->H;
+    if (fused_ok(c, lm) && sampler_fusable(c) && first_code_ptr == codes_out_dev && H % 4 == 0) {
+        /* mode 1: the whole 15-codebook loop is ONE persistent kernel launch */
+        SubProg sp;
+        memset(&sp, 0, sizeof(sp));
+        sp.G = G; sp.Hin = H; sp.hidden = hidden_dev; sp.emb0 = c->codec_embedding;
+        for (int g = 0; g < G - 1; g++) { sp.emb[g] = c->sub_emb[g]; sp.heads[g] = c->sub_head[g]; }
+        sp.in_w = c->sub_in_w; sp.in_b = c->sub_in_b; sp.vocab = lm->vocab; sp.codes = codes_out_dev;
+        sp.cfg.vocab = lm->vocab; sp.cfg.top_k = c->params.subtalker_top_k; sp.cfg.top_p = c->params.subtalker_top_p;
+        sp.cfg.temperature = c->params.subtalker_temperature; sp.cfg.suppress_from = -1; sp.cfg.eos_id = -1; sp.cfg.rep_penalty = 1.0f;
+        { float f = (float)c->params.sample_seed; memcpy(&sp.seed_bits, &f, 4); }
+        sp.scratch_f = c->sample_scratch_f; sp.scratch_i = c->sample_scratch; sp.vec = c->st_embed;
+        return fused_step(c, lm, &c->st, c->zero_pos, 0, NULL, lm->vocab, c->st.logits, NULL, &sp);
+    }
     const int *g_zero_pos = c->zero_pos;          /* device int 0: the sub-talker's position base */
     if (sub_project(c, hidden_dev)) return -1;                                 /* pos 0: no logits */
     if (qtc_lm_step(c, lm, &c->st, g_zero_pos, 0)) return -1;

@@ -43,14 +43,38 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
     const int tid = threadIdx.x;
     if (temperature <= 0.0f) temperature = 1e-5f;
     __syncthreads();
+    if (top_p >= 1.0f && top_k == 1 && V > 1) {
+        /* greedy: the list holds one entry - the first strict maximum above -FLT_MAX; its probability is
+         * expf(0) = 1, the walk always lands on it, and the RNG still advances once (:451-474) */
+        float bv = -3.402823466e+38f; int bi = -1;
+        for (int i = tid; i < V; i += blockDim.x) { const float v = __fdiv_rn(lg[i], temperature); if (v > bv) { bv = v; bi = i; } }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (oi >= 0 && (ov > bv || (ov == bv && (bi < 0 || oi < bi)))) { bv = ov; bi = oi; }
+        }
+        if ((tid & 31) == 0) { S.sel_v[tid >> 5] = bv; S.sel_i[tid >> 5] = bi; }
+        __syncthreads();
+        if (tid == 0) {
+            const int nw = (blockDim.x + 31) >> 5;
+            for (int w = 1; w < nw; w++) {
+                const float ov = S.sel_v[w]; const int oi = S.sel_i[w];
+                if (oi >= 0 && (ov > bv || (ov == bv && (bi < 0 || oi < bi)))) { bv = ov; bi = oi; }
+            }
+            if (bi >= 0) { uint32_t st = *rng; (void)rng_next(&st); *rng = st; }
+            S.pick = bi >= 0 ? bi : 0;
+        }
+        __syncthreads();
+        return S.pick;
+    }
     if (top_p >= 1.0f && top_k > 0 && top_k < V && top_k <= SAMPLE_MAX_K) {
-        for (int i = tid; i < V; i += SAMPLE_THREADS) vv[i] = __fdiv_rn(lg[i], temperature);
+        for (int i = tid; i < V; i += blockDim.x) vv[i] = __fdiv_rn(lg[i], temperature);
         if (tid == 0) { S.prefix = 0; S.nsel = 0; S.pick = 0; }
         __syncthreads();
         /* candidates: v > -FLT_MAX (the list is initialised with -FLT_MAX and admits only strictly greater) */
         const uint32_t floor_key = f32_order_key(-3.402823466e+38f);
         uint32_t nvalid = 0;
-        for (int i = tid; i < V; i += SAMPLE_THREADS) nvalid += f32_order_key(vv[i]) > floor_key && vv[i] == vv[i];
+        for (int i = tid; i < V; i += blockDim.x) nvalid += f32_order_key(vv[i]) > floor_key && vv[i] == vv[i];
         nvalid = (uint32_t)(block_sum((float)nvalid, S.red) + 0.5f);
         const uint32_t kk = nvalid < (uint32_t)top_k ? nvalid : (uint32_t)top_k;
         if (kk == 0) return 0;                    /* sum == 0 branch: idx[0] < 0 -> token 0, RNG untouched */
@@ -58,10 +82,10 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
         __syncthreads();
         /* radix select of the kk-th largest key, 8 bits per pass from the top */
         for (int shift = 24; shift >= 0; shift -= 8) {
-            for (int i = tid; i < 256; i += SAMPLE_THREADS) S.hist[i] = 0;
+            for (int i = tid; i < 256; i += blockDim.x) S.hist[i] = 0;
             __syncthreads();
             const uint32_t prefix = S.prefix, himask = shift == 24 ? 0u : (0xffffffffu << (shift + 8));
-            for (int i = tid; i < V; i += SAMPLE_THREADS) {
+            for (int i = tid; i < V; i += blockDim.x) {
                 const uint32_t key = f32_order_key(vv[i]);
                 if (key > floor_key && vv[i] == vv[i] && (key & himask) == prefix) atomicAdd(&S.hist[(key >> shift) & 255u], 1u);
             }
@@ -90,7 +114,7 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
         }
         const uint32_t tkey = S.prefix, need_eq = S.remaining, eq_total = S.eq_total;
         /* admit keys above the threshold, and ties at the threshold in index order */
-        for (int i = tid; i < V; i += SAMPLE_THREADS) {
+        for (int i = tid; i < V; i += blockDim.x) {
             const uint32_t key = f32_order_key(vv[i]);
             if (vv[i] == vv[i] && key > tkey) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
             else if (key == tkey && eq_total == need_eq) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
@@ -108,7 +132,7 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
         }
         __syncthreads();
         /* rank by (value desc, index asc) */
-        for (uint32_t j = tid; j < kk; j += SAMPLE_THREADS) {
+        for (uint32_t j = tid; j < kk; j += blockDim.x) {
             const float v = S.sel_v[j]; const int id = S.sel_i[j];
             uint32_t r = 0;
             for (uint32_t m = 0; m < kk; m++) r += (S.sel_v[m] > v) || (S.sel_v[m] == v && S.sel_i[m] < id);
@@ -116,7 +140,7 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
         }
         __syncthreads();
         const float mx = S.ord_v[0];
-        for (uint32_t j = tid; j < kk; j += SAMPLE_THREADS) S.sel_v[j] = expf_libm(__fsub_rn(S.ord_v[j], mx));
+        for (uint32_t j = tid; j < kk; j += blockDim.x) S.sel_v[j] = expf_libm(__fsub_rn(S.ord_v[j], mx));
         __syncthreads();
         if (tid == 0) {
             float tot = 0.0f;
@@ -171,12 +195,12 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
     }
     /* ---- slow path, c/qwen_tts_kernels.c:486-557 ---- */
     float *p = scratch_f; int *ord = scratch_i;
-    for (int i = tid; i < V; i += SAMPLE_THREADS) p[i] = __fdiv_rn(lg[i], temperature);
+    for (int i = tid; i < V; i += blockDim.x) p[i] = __fdiv_rn(lg[i], temperature);
     __syncthreads();
     float mx = -3.402823466e+38f;
-    for (int i = tid; i < V; i += SAMPLE_THREADS) mx = fmaxf(mx, p[i]);
+    for (int i = tid; i < V; i += blockDim.x) mx = fmaxf(mx, p[i]);
     mx = block_max(mx, S.red);
-    for (int i = tid; i < V; i += SAMPLE_THREADS) p[i] = expf_libm(__fsub_rn(p[i], mx));
+    for (int i = tid; i < V; i += blockDim.x) p[i] = expf_libm(__fsub_rn(p[i], mx));
     __syncthreads();
     if (tid == 0) {
         float tot = 0.0f;
@@ -184,11 +208,11 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
         S.red[0] = __fdiv_rn(1.0f, tot);
     }
     __syncthreads();
-    { const float inv = S.red[0]; __syncthreads(); for (int i = tid; i < V; i += SAMPLE_THREADS) p[i] = __fmul_rn(p[i], inv); }
+    { const float inv = S.red[0]; __syncthreads(); for (int i = tid; i < V; i += blockDim.x) p[i] = __fmul_rn(p[i], inv); }
     __syncthreads();
     const bool use_k = top_k > 0 && top_k < V, use_p = top_p < 1.0f;
     if (use_k || use_p) {                               /* stable descending order == the insertion sort */
-        for (int i = tid; i < V; i += SAMPLE_THREADS) {
+        for (int i = tid; i < V; i += blockDim.x) {
             const float v = p[i];
             int r = 0;
             for (int m = 0; m < V; m++) r += (p[m] > v) || (p[m] == v && m < i);
@@ -199,7 +223,7 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
     if (use_k) {
         const float thr = p[ord[top_k - 1]];
         __syncthreads();
-        for (int i = tid; i < V; i += SAMPLE_THREADS) if (p[i] < thr) p[i] = 0.0f;
+        for (int i = tid; i < V; i += blockDim.x) if (p[i] < thr) p[i] = 0.0f;
         __syncthreads();
     }
     if (tid == 0) {
@@ -248,7 +272,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample(const SampleArgs a) {
     float *lg = dyn, *vv = dyn + V;
     if (a.role == 0 && a.st->done) return;
     if (a.reseed && tid == 0) *a.rng = a.seed_bits;
-    for (int i = tid; i < V; i += SAMPLE_THREADS) {
+    for (int i = tid; i < V; i += blockDim.x) {
         float l = a.logits[i];
         if (a.cfg.suppress_from >= 0 && i >= a.cfg.suppress_from && i != a.cfg.eos_id) l = -1e9f;
         if (a.hist_count && a.cfg.rep_penalty != 1.0f) {

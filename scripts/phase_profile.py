@@ -41,8 +41,12 @@ def main():
         print(f"  {name:16s} {d[:, i].min():7.2f} {np.median(d[:, i]):7.2f} {d[:, i].max():7.2f}")
     tot = (st[:, 13] - st[:, 0]) / 1.965e3
     print(f"  layer total      {tot.min():7.2f} {np.median(tot):7.2f} {tot.max():7.2f}")
-    step = cuda.qwen_tts_cuda_bench_talker_step(ctx, pos, 20, 1)
-    print(f"  talker step {step * 1e3:.1f} us, bytes {cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos) / 1e6:.1f} MB")
+    if pos >= 0:
+        step = cuda.qwen_tts_cuda_bench_talker_step(ctx, pos, 20, 1)
+        print(f"  talker step {step * 1e3:.1f} us, bytes {cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos) / 1e6:.1f} MB")
+    else:
+        fr = cuda.qwen_tts_cuda_bench_subtalker(ctx, 20, 1)
+        print(f"  sub-talker frame {fr * 1e3:.1f} us (16 steps), streamed bytes {cuda.qwen_tts_cuda_subtalker_frame_bytes(ctx) / 1e6:.1f} MB")
     cuda.qwen_tts_cuda_release(ctx)
 
 

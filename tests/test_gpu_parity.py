@@ -34,6 +34,7 @@ def snr_db(ref, got):
 def tiny_ctx(cuda, tiny):
     ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 1)
     assert ctx, cuda.qwen_tts_cuda_last_error()
+    assert cuda.qwen_tts_cuda_set_mode(ctx, 0) == 0      # this module: one kernel per op (mode 1 is tests/test_gpu_fused.py)
     yield ctx
     cuda.qwen_tts_cuda_release(ctx)
 
