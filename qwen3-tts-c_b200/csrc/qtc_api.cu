@@ -211,7 +211,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
 extern "C" void qwen_tts_cuda_set_params(qtc_ctx_t *c, const qtc_gen_params_t *p) { if (c && p) { c->params = *p; c->graph_key = -1; } }
 extern "C" void qwen_tts_cuda_get_perf(const qtc_ctx_t *c, qtc_perf_t *out) { if (c && out) { *out = c->perf; out->kernel_launches = c->launches; } }
 extern "C" int qwen_tts_cuda_set_mode(qtc_ctx_t *c, int mode) {
-    if (!c || mode < 0 || mode > 1) return -1;
+    if (!c || mode < 0 || mode > 2) return -1;
     c->mode = mode; c->graph_key = -1;
     return 0;
 }

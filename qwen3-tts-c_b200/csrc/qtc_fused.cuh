@@ -45,6 +45,9 @@ struct FusedArgs {
     int att_floats;                /* attention scratch after it; the KV stage [2][64][hd] follows */
     int flags;                     /* experiments (env QTC_FUSED_FLAGS) */
     int ring_off;                  /* byte offset of the weight ring in dynamic shared memory (128-aligned) */
+    int nst;                       /* ring stages (k_lm_ring) */
+    int att_cap;                   /* positions the shared-memory KV stage holds */
+    int kv_floats;                 /* size of the KV stage / sampler region */
     long long *prof; int prof_layer; /* optional: clock64 stamps of one layer, 16 slots per CTA (debug / profiles) */
 };
 
@@ -141,7 +144,7 @@ __device__ __forceinline__ void stage_vec(float *xs, const float *src, int n) {
 }
 
 /* xs = rmsnorm(src) * w, computed by every CTA for itself */
-__device__ __forceinline__ void stage_rmsnorm(float *xs, const float *src, const float *w, int n, float eps, float *red) {
+__device__ __noinline__ void stage_rmsnorm(float *xs, const float *src, const float *w, int n, float eps, float *red) {
     if (n <= FUSED_THREADS * 8) {
         /* one pass: values and norm weights stay in registers across the reduction */
         const int i0 = threadIdx.x * 4, i1 = i0 + FUSED_THREADS * 4;

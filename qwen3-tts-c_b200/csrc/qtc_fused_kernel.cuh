@@ -12,14 +12,15 @@
 
 #define ATT_STAGE_MAX 64          /* positions per CTA that fit the shared-memory KV stage */
 
-struct AttPlan { int S, h, sp, g, t0, t1, active, staged; };
+struct AttPlan { int S, h, sp, g, t0, t1, active, staged, cap; };
 
-__device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, int ncta) {
+__device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, int ncta, int cap = ATT_STAGE_MAX) {
     AttPlan p;
+    p.cap = cap;
     const int n = pos + 1;
     p.S = (n + 31) / 32;
     if (p.S > FUSED_MAX_SPLIT) p.S = FUSED_MAX_SPLIT;
-    while (p.S > 1 && (lm.heads * p.S > ncta || lm.heads * p.S * (lm.head_dim + 4) > 2 * ATT_STAGE_MAX * lm.head_dim)) p.S--;
+    while (p.S > 1 && (lm.heads * p.S > ncta || lm.heads * p.S * (lm.head_dim + 4) > 2 * cap * lm.head_dim)) p.S--;
     p.active = cta < lm.heads * p.S;
     p.h = p.active ? cta / p.S : 0;
     p.sp = cta - p.h * p.S;
@@ -28,7 +29,7 @@ __device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, i
     p.t0 = p.sp * chunk;
     p.t1 = p.t0 + chunk < n ? p.t0 + chunk : n;
     if (p.t1 < p.t0) p.t1 = p.t0;
-    p.staged = chunk <= ATT_STAGE_MAX && lm.head_dim % 4 == 0;
+    p.staged = chunk <= cap && lm.head_dim % 4 == 0;
     return p;
 }
 
@@ -41,7 +42,7 @@ __device__ __forceinline__ void att_stage_issue(const FusedArgs &a, const LmDev 
     for (int i = threadIdx.x; i < rows * q4 * 2; i += FUSED_THREADS) {
         const int which = i >= rows * q4, j = which ? i - rows * q4 : i, r = j / q4, c = j - r * q4;
         const float *src = (which ? vc : kc) + (size_t)(p.t0 + r) * kvd + c * 4;
-        float *dst = kvs + (size_t)which * ATT_STAGE_MAX * hd + r * hd + c * 4;
+        float *dst = kvs + (size_t)which * p.cap * hd + r * hd + c * 4;
         const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst);
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src));
     }
@@ -49,7 +50,7 @@ __device__ __forceinline__ void att_stage_issue(const FusedArgs &a, const LmDev 
 }
 
 /* per-head QK-RMSNorm + RoPE + KV append + partial attention over [t0,t1).  sm: scratch, kvs: staged K/V */
-__device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &lm, const AttPlan &p, int l, int pos, float *sm, float *kvs,
+__device__ __noinline__ void cta_attention(const FusedArgs &a, const LmDev &lm, const AttPlan &p, int l, int pos, float *sm, float *kvs,
                                               float *red) {
     asm volatile("cp.async.wait_all;");
     if (!p.active) return;
@@ -61,7 +62,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
     const float *qr = a.q + h * hd, *kr = a.kk + g * hd, *vr = a.vv + g * hd;
     const float *cs = a.cos + (size_t)pos * hd, *sn = a.sin + (size_t)pos * hd;
     float *kc = a.kc + (size_t)l * a.kv_max * kvd, *vc = a.vc + (size_t)l * a.kv_max * kvd;
-    const float *Ks = kvs, *Vs = kvs + (size_t)ATT_STAGE_MAX * hd;
+    const float *Ks = kvs, *Vs = kvs + (size_t)p.cap * hd;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     /* q and k of this token: norm over the head, rotate-half.  One warp each (hd <= 512), no block barrier */
@@ -187,7 +188,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
 /* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector.
  * The heads*S records (contiguous in HBM/L2) are copied into `land` (the KV stage, idle in this phase) with
  * cp.async - one round trip, no registers tied up - and folded from shared memory. */
-__device__ __forceinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
+__device__ __noinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
     const int hd = lm.head_dim, heads = lm.heads, qd = heads * hd, tid = threadIdx.x, rec = hd + 4;
     const int n16 = heads * S * rec / 4;
     for (int i = tid; i < n16; i += FUSED_THREADS) {

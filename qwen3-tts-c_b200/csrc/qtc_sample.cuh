@@ -38,25 +38,46 @@ struct SampleSmem {
 
 /* lg: logits in shared memory [V] (already suppressed / penalised).  Returns the pick in every thread.
  * scratch_f/scratch_i: global scratch of V entries each (slow path only). */
-__device__ int block_sample(const float *lg, float *vv, int V, int top_k, float top_p, float temperature,
+/* The sampler runs either as a whole CTA (NTF == 0: __syncthreads, blockDim.x threads) or as the first NTF
+ * threads of a larger CTA that synchronise on named barrier 1 (the fused kernels keep a producer warp apart). */
+#define SSYNC() do { if (NTF) asm volatile("bar.sync 1, %0;" ::"n"(NTF ? NTF : 32) : "memory"); else __syncthreads(); } while (0)
+template <int NTF> __device__ __forceinline__ float sblock_sum(float v, float *red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = ((NTF ? NTF : (int)blockDim.x) + 31) >> 5;
+    v = warp_sum(v);
+    SSYNC();
+    if (lane == 0) red[w] = v;
+    SSYNC();
+    return warp_sum(lane < nw ? red[lane] : 0.0f);
+}
+template <int NTF> __device__ __forceinline__ float sblock_max(float v, float *red) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = ((NTF ? NTF : (int)blockDim.x) + 31) >> 5;
+    v = warp_max(v);
+    SSYNC();
+    if (lane == 0) red[w] = v;
+    SSYNC();
+    return warp_max(lane < nw ? red[lane] : -3.402823466e+38f);
+}
+template <int NTF>
+__device__ __noinline__ int block_sample_t(const float *lg, float *vv, int V, int top_k, float top_p, float temperature,
                             uint32_t *rng, SampleSmem &S, float *scratch_f, int *scratch_i) {
     const int tid = threadIdx.x;
+    const int NT = NTF ? NTF : (int)blockDim.x;
     if (temperature <= 0.0f) temperature = 1e-5f;
-    __syncthreads();
+    SSYNC();
     if (top_p >= 1.0f && top_k == 1 && V > 1) {
         /* greedy: the list holds one entry - the first strict maximum above -FLT_MAX; its probability is
          * expf(0) = 1, the walk always lands on it, and the RNG still advances once (:451-474) */
         float bv = -3.402823466e+38f; int bi = -1;
-        for (int i = tid; i < V; i += blockDim.x) { const float v = __fdiv_rn(lg[i], temperature); if (v > bv) { bv = v; bi = i; } }
+        for (int i = tid; i < V; i += NT) { const float v = __fdiv_rn(lg[i], temperature); if (v > bv) { bv = v; bi = i; } }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (oi >= 0 && (ov > bv || (ov == bv && (bi < 0 || oi < bi)))) { bv = ov; bi = oi; }
         }
         if ((tid & 31) == 0) { S.sel_v[tid >> 5] = bv; S.sel_i[tid >> 5] = bi; }
-        __syncthreads();
+        SSYNC();
         if (tid == 0) {
-            const int nw = (blockDim.x + 31) >> 5;
+            const int nw = (NT + 31) >> 5;
             for (int w = 1; w < nw; w++) {
                 const float ov = S.sel_v[w]; const int oi = S.sel_i[w];
                 if (oi >= 0 && (ov > bv || (ov == bv && (bi < 0 || oi < bi)))) { bv = ov; bi = oi; }
@@ -64,32 +85,32 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
             if (bi >= 0) { uint32_t st = *rng; (void)rng_next(&st); *rng = st; }
             S.pick = bi >= 0 ? bi : 0;
         }
-        __syncthreads();
+        SSYNC();
         return S.pick;
     }
     if (top_p >= 1.0f && top_k > 0 && top_k < V && top_k <= SAMPLE_MAX_K) {
-        for (int i = tid; i < V; i += blockDim.x) vv[i] = __fdiv_rn(lg[i], temperature);
+        for (int i = tid; i < V; i += NT) vv[i] = __fdiv_rn(lg[i], temperature);
         if (tid == 0) { S.prefix = 0; S.nsel = 0; S.pick = 0; }
-        __syncthreads();
+        SSYNC();
         /* candidates: v > -FLT_MAX (the list is initialised with -FLT_MAX and admits only strictly greater) */
         const uint32_t floor_key = f32_order_key(-3.402823466e+38f);
         uint32_t nvalid = 0;
-        for (int i = tid; i < V; i += blockDim.x) nvalid += f32_order_key(vv[i]) > floor_key && vv[i] == vv[i];
-        nvalid = (uint32_t)(block_sum((float)nvalid, S.red) + 0.5f);
+        for (int i = tid; i < V; i += NT) nvalid += f32_order_key(vv[i]) > floor_key && vv[i] == vv[i];
+        nvalid = (uint32_t)(sblock_sum<NTF>((float)nvalid, S.red) + 0.5f);
         const uint32_t kk = nvalid < (uint32_t)top_k ? nvalid : (uint32_t)top_k;
         if (kk == 0) return 0;                    /* sum == 0 branch: idx[0] < 0 -> token 0, RNG untouched */
         if (tid == 0) S.remaining = kk;
-        __syncthreads();
+        SSYNC();
         /* radix select of the kk-th largest key, 8 bits per pass from the top */
         for (int shift = 24; shift >= 0; shift -= 8) {
-            for (int i = tid; i < 256; i += blockDim.x) S.hist[i] = 0;
-            __syncthreads();
+            for (int i = tid; i < 256; i += NT) S.hist[i] = 0;
+            SSYNC();
             const uint32_t prefix = S.prefix, himask = shift == 24 ? 0u : (0xffffffffu << (shift + 8));
-            for (int i = tid; i < V; i += blockDim.x) {
+            for (int i = tid; i < V; i += NT) {
                 const uint32_t key = f32_order_key(vv[i]);
                 if (key > floor_key && vv[i] == vv[i] && (key & himask) == prefix) atomicAdd(&S.hist[(key >> shift) & 255u], 1u);
             }
-            __syncthreads();
+            SSYNC();
             if (tid < 32) {                        /* suffix counts: lane l owns digits 8l..8l+7 */
                 uint32_t c[8], tot = 0;
 #pragma unroll
@@ -110,11 +131,11 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
                     above += c[j];
                 }
             }
-            __syncthreads();
+            SSYNC();
         }
         const uint32_t tkey = S.prefix, need_eq = S.remaining, eq_total = S.eq_total;
         /* admit keys above the threshold, and ties at the threshold in index order */
-        for (int i = tid; i < V; i += blockDim.x) {
+        for (int i = tid; i < V; i += NT) {
             const uint32_t key = f32_order_key(vv[i]);
             if (vv[i] == vv[i] && key > tkey) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
             else if (key == tkey && eq_total == need_eq) { const uint32_t s = atomicAdd(&S.nsel, 1u); S.sel_v[s] = vv[i]; S.sel_i[s] = i; }
@@ -130,18 +151,18 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
                 base += __popc(m);
             }
         }
-        __syncthreads();
+        SSYNC();
         /* rank by (value desc, index asc) */
-        for (uint32_t j = tid; j < kk; j += blockDim.x) {
+        for (uint32_t j = tid; j < kk; j += NT) {
             const float v = S.sel_v[j]; const int id = S.sel_i[j];
             uint32_t r = 0;
             for (uint32_t m = 0; m < kk; m++) r += (S.sel_v[m] > v) || (S.sel_v[m] == v && S.sel_i[m] < id);
             S.ord_v[r] = v; S.ord_i[r] = id;
         }
-        __syncthreads();
+        SSYNC();
         const float mx = S.ord_v[0];
-        for (uint32_t j = tid; j < kk; j += blockDim.x) S.sel_v[j] = expf_libm(__fsub_rn(S.ord_v[j], mx));
-        __syncthreads();
+        for (uint32_t j = tid; j < kk; j += NT) S.sel_v[j] = expf_libm(__fsub_rn(S.ord_v[j], mx));
+        SSYNC();
         if (tid == 0) {
             float tot = 0.0f;
             for (uint32_t j = 0; j < kk; j++) tot = __fadd_rn(tot, S.sel_v[j]);
@@ -157,7 +178,7 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
             }
             S.pick = pick;
         }
-        __syncthreads();
+        SSYNC();
         return S.pick;
     }
 
@@ -190,41 +211,41 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
             } else pick = idx[0] >= 0 ? idx[0] : 0;
             S.pick = pick;
         }
-        __syncthreads();
+        SSYNC();
         return S.pick;
     }
     /* ---- slow path, c/qwen_tts_kernels.c:486-557 ---- */
     float *p = scratch_f; int *ord = scratch_i;
-    for (int i = tid; i < V; i += blockDim.x) p[i] = __fdiv_rn(lg[i], temperature);
-    __syncthreads();
+    for (int i = tid; i < V; i += NT) p[i] = __fdiv_rn(lg[i], temperature);
+    SSYNC();
     float mx = -3.402823466e+38f;
-    for (int i = tid; i < V; i += blockDim.x) mx = fmaxf(mx, p[i]);
-    mx = block_max(mx, S.red);
-    for (int i = tid; i < V; i += blockDim.x) p[i] = expf_libm(__fsub_rn(p[i], mx));
-    __syncthreads();
+    for (int i = tid; i < V; i += NT) mx = fmaxf(mx, p[i]);
+    mx = sblock_max<NTF>(mx, S.red);
+    for (int i = tid; i < V; i += NT) p[i] = expf_libm(__fsub_rn(p[i], mx));
+    SSYNC();
     if (tid == 0) {
         float tot = 0.0f;
         for (int i = 0; i < V; i++) tot = __fadd_rn(tot, p[i]);
         S.red[0] = __fdiv_rn(1.0f, tot);
     }
-    __syncthreads();
-    { const float inv = S.red[0]; __syncthreads(); for (int i = tid; i < V; i += blockDim.x) p[i] = __fmul_rn(p[i], inv); }
-    __syncthreads();
+    SSYNC();
+    { const float inv = S.red[0]; SSYNC(); for (int i = tid; i < V; i += NT) p[i] = __fmul_rn(p[i], inv); }
+    SSYNC();
     const bool use_k = top_k > 0 && top_k < V, use_p = top_p < 1.0f;
     if (use_k || use_p) {                               /* stable descending order == the insertion sort */
-        for (int i = tid; i < V; i += blockDim.x) {
+        for (int i = tid; i < V; i += NT) {
             const float v = p[i];
             int r = 0;
             for (int m = 0; m < V; m++) r += (p[m] > v) || (p[m] == v && m < i);
             ord[r] = i;
         }
-        __syncthreads();
+        SSYNC();
     }
     if (use_k) {
         const float thr = p[ord[top_k - 1]];
-        __syncthreads();
-        for (int i = tid; i < V; i += blockDim.x) if (p[i] < thr) p[i] = 0.0f;
-        __syncthreads();
+        SSYNC();
+        for (int i = tid; i < V; i += NT) if (p[i] < thr) p[i] = 0.0f;
+        SSYNC();
     }
     if (tid == 0) {
         if (use_p) {
@@ -247,8 +268,13 @@ __device__ int block_sample(const float *lg, float *vv, int V, int top_k, float 
         }
         S.pick = pick;
     }
-    __syncthreads();
+    SSYNC();
     return S.pick;
+}
+#undef SSYNC
+__device__ __forceinline__ int block_sample(const float *lg, float *vv, int V, int top_k, float top_p, float temperature,
+                                            uint32_t *rng, SampleSmem &S, float *scratch_f, int *scratch_i) {
+    return block_sample_t<0>(lg, vv, V, top_k, top_p, temperature, rng, S, scratch_f, scratch_i);
 }
 
 struct SampleArgs {

@@ -25,15 +25,21 @@ def main():
     hm = B.HostModel(spec, main_t, {}, orc)
     ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
     assert ctx
-    cuda.qwen_tts_cuda_set_mode(ctx, 1)
+    cuda.qwen_tts_cuda_set_mode(ctx, int(os.environ.get("QTC_MODE", "2")))
     cuda.qwen_tts_cuda_debug_phase_clocks.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_longlong)]
     out = np.zeros(148 * 32 * 2, dtype=np.int64)
     n = cuda.qwen_tts_cuda_debug_phase_clocks(ctx, pos, layer, out.ctypes.data_as(C.POINTER(C.c_longlong)))
     assert n > 0
     raw = out[: n * 32].reshape(n, 32).astype(np.float64)
-    for nm, a, b in (("prefetch issue (P1)", 0, 14), ("prefetch+stage (P3)", 5, 15)):
+    for nm, a, b in (("qkv consume only", 1, 16), ("stage (P3)", 5, 15)):
         dd = (raw[:, b] - raw[:, a]) / 1.965e3
         print(f"  [{nm}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
+    if raw[:, 17].any():
+        names = {26: "before geom", 17: "consume entry", 18: "x slice loaded", 19: "quad0 loaded", 20: "quad0 mma done", 21: "quad0 released", 22: "chunk1 done",
+                 23: "chunk2 full", 24: "chunk2 done", 25: "loop end", 16: "after consume", 27: "PRODUCER at qkv", 28: "PRODUCER got slot"}
+        for k in (27, 28, 26, 17, 19, 20, 21, 25, 16):
+            dd = (raw[:, k] - raw[:, 1]) / 1.965e3
+            print(f"  [qkv +{names[k]:16s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
     st = raw[:, :14]
     d = np.diff(st, axis=1) / 1.965e3          # us at the 1965 MHz the bench runs at
     print(f"{preset} pos={pos} layer={layer}: per-phase microseconds over {n} CTAs (min / median / max)")

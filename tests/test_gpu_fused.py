@@ -1,5 +1,5 @@
-"""Mode 1 (one persistent cooperative kernel per decoder-stack step) against the same golden vectors
-and oracle as the per-op path.  Fast arithmetic: logits within 1e-2 relative (north_star), codes equal."""
+"""Modes 1 and 2 (one persistent cooperative kernel per decoder-stack step; mode 2 streams the weights through
+the shared-memory TMA ring) against the same golden vectors and oracle as the per-op path.  Fast arithmetic: logits within 1e-2 relative (north_star), codes equal."""
 import ctypes as C
 import os
 
@@ -13,11 +13,11 @@ from test_gpu_parity import GEN_CASES, GOLD, TOK, _generate, _stage_run, snr_db
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def fused_ctx(cuda, tiny):
+@pytest.fixture(scope="module", params=[1, 2], ids=["fused", "ring"])
+def fused_ctx(request, cuda, tiny):
     ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 1)
     assert ctx, cuda.qwen_tts_cuda_last_error()
-    assert cuda.qwen_tts_cuda_set_mode(ctx, 1) == 0
+    assert cuda.qwen_tts_cuda_set_mode(ctx, request.param) == 0
     yield ctx
     cuda.qwen_tts_cuda_release(ctx)
 
@@ -41,13 +41,14 @@ def test_fused_generate(cuda, fused_ctx, name, params, spk, lang):
     assert snr_db(want_pcm, pcm) >= 80.0
 
 
-def test_fused_long_context_splits(cuda, orc):
+@pytest.mark.parametrize("mode", [1, 2], ids=["fused", "ring"])
+def test_fused_long_context_splits(cuda, orc, mode):
     """KV length past 64 / 128 / ... positions exercises the split-KV attention and its combine step:
     teacher-forced talker steps on the `small` preset (16 Q / 8 KV heads of 128) against the oracle"""
     hm = get_model(orc, "small")
     H, V = hm.spec["talker"]["hidden"], hm.spec["talker"]["vocab"]
     ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
-    assert ctx and cuda.qwen_tts_cuda_set_mode(ctx, 1) == 0
+    assert ctx and cuda.qwen_tts_cuda_set_mode(ctx, mode) == 0
     s = orc.orc_create(hm.desc)
     rng = np.random.default_rng(0)
     n_pre, n_steps = 60, 150
