@@ -261,6 +261,8 @@ int qwen_tts_cuda_snake_beta(float *out, const float *x, const float *alpha, con
                              int channels, int length);
 int qwen_tts_cuda_matmul_f32(float *C, const float *A, const float *B, int M, int N, int K);
 int qwen_tts_cuda_matmul_bf16(float *C, const float *A, const uint16_t *B_bf16, int M, int N, int K);
+/* the batched path's projection kernel on its own (tcgen05 / TMEM / TMA): C[M,N] = bf16(A)[M,K] . W[N,K]^T, M <= 64, K % 64 == 0 */
+int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16_t *W_bf16, int M, int N, int K);
 
 /* ---- measurement hooks ------------------------------------------------------ */
 /* time `iters` talker decode steps at KV position `pos` with CUDA events on the

@@ -144,7 +144,7 @@ __device__ __forceinline__ void stage_vec(float *xs, const float *src, int n) {
 }
 
 /* xs = rmsnorm(src) * w, computed by every CTA for itself */
-__device__ __noinline__ void stage_rmsnorm(float *xs, const float *src, const float *w, int n, float eps, float *red) {
+__device__ __forceinline__ void stage_rmsnorm(float *xs, const float *src, const float *w, int n, float eps, float *red) {
     if (n <= FUSED_THREADS * 8) {
         /* one pass: values and norm weights stay in registers across the reduction */
         const int i0 = threadIdx.x * 4, i1 = i0 + FUSED_THREADS * 4;

@@ -50,7 +50,7 @@ __device__ __forceinline__ void att_stage_issue(const FusedArgs &a, const LmDev 
 }
 
 /* per-head QK-RMSNorm + RoPE + KV append + partial attention over [t0,t1).  sm: scratch, kvs: staged K/V */
-__device__ __noinline__ void cta_attention(const FusedArgs &a, const LmDev &lm, const AttPlan &p, int l, int pos, float *sm, float *kvs,
+__device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &lm, const AttPlan &p, int l, int pos, float *sm, float *kvs,
                                               float *red) {
     asm volatile("cp.async.wait_all;");
     if (!p.active) return;
@@ -188,7 +188,7 @@ __device__ __noinline__ void cta_attention(const FusedArgs &a, const LmDev &lm, 
 /* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector.
  * The heads*S records (contiguous in HBM/L2) are copied into `land` (the KV stage, idle in this phase) with
  * cp.async - one round trip, no registers tied up - and folded from shared memory. */
-__device__ __noinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
+__device__ __forceinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
     const int hd = lm.head_dim, heads = lm.heads, qd = heads * hd, tid = threadIdx.x, rec = hd + 4;
     const int n16 = heads * S * rec / 4;
     for (int i = tid; i < n16; i += FUSED_THREADS) {

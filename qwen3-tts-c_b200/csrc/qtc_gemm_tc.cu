@@ -1,0 +1,261 @@
+/*
+ * qtc_gemm_tc.cu - the batched (lock-step, B <= 64 utterances) projections of the talker / sub-talker
+ * as tcgen05 GEMMs:  Y[b, n] += sum_k X[b, k] * W[n, k]      (kernel_matvec_bf16, c/qwen_tts_kernels.c:95-149,
+ * once per utterance in the reference; here one pass over W serves the whole batch).
+ *
+ * Mapping (sm_100a): the bf16 weight matrix is the A operand - a CTA owns 128 weight rows (UMMA M = 128) and one
+ * K range (split-K so that tiles x splits ~ the 148 SMs: the op is weight-bandwidth bound at batch 64, every SM
+ * has to pull HBM); the activations, rounded to bf16, are the B operand (UMMA N = 64 = batch, K-major).  TMA
+ * (cp.async.bulk.tensor, SWIZZLE_128B) fills a 6-stage shared-memory pipeline of [128 x 64] + [64 x 64] tiles,
+ * one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (4 per stage), the fp32 accumulator [128 x 64]
+ * lives in TMEM (64 columns), four epilogue warps read it back with tcgen05.ld (32 lanes x 32 bit x 16) and add it
+ * to Y with fp32 reductions in L2 (red.global.add.f32) - Y is pre-loaded with zero, a bias or the residual stream,
+ * so split-K needs no second pass and "x += W.h" costs nothing extra.
+ *
+ * Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc/free), 2..5 epilogue (TMEM lane quarter = warp % 4).
+ */
+#include "qtc_internal.h"
+
+#include <cuda.h>
+#include <unordered_map>
+
+#define TC_BM 128           /* weight rows per CTA (UMMA M) */
+#define TC_BN 64            /* batch columns (UMMA N) */
+#define TC_BK 64            /* K per stage: 64 bf16 = one 128-byte swizzle row */
+#define TC_STAGES 6
+#define TC_A_BYTES (TC_BM * TC_BK * 2)
+#define TC_B_BYTES (TC_BN * TC_BK * 2)
+#define TC_STAGE_BYTES (TC_A_BYTES + TC_B_BYTES)
+#define TC_THREADS 192
+#define TC_SMEM (TC_STAGES * TC_STAGE_BYTES + 1024)
+
+__device__ __forceinline__ uint32_t tc_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tc_mbar_init(uint64_t *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tc_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_wait(uint64_t *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "TCW_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra TCD_%=;\n"
+        "bra TCW_%=;\n"
+        "TCD_%=:\n"
+        "}\n" ::"r"(tc_smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tc_tma_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(tc_smem_u32(dst)), "l"(map), "r"(tc_smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+/* K-major operand tile in SWIZZLE_128B layout: rows of 128 bytes, 8-row groups 1024 bytes apart */
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr & 0x3ffffu) >> 4);          /* start address, 16-byte units           [0,14)  */
+    d |= (uint64_t)(1024 >> 4) << 32;                 /* stride byte offset (8 rows x 128 B)    [32,46) */
+    d |= 1ull << 46;                                  /* descriptor version (sm_100)            [46,48) */
+    d |= 2ull << 61;                                  /* layout: SWIZZLE_128B                   [61,64) */
+    return d;
+}
+/* kind::f16 instruction descriptor: D f32, A/B bf16, both K-major, M = 128, N = 64 */
+__device__ __forceinline__ uint32_t tc_idesc() {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tc_smem_u32(bar)) : "memory");
+}
+
+/* grid (row tiles, K splits).  Y [batch, ldy] fp32, pre-initialised; rows >= N and batch columns >= nbatch are dropped */
+__global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapX,
+                                                            float *Y, int N, int ldy, int kb_per_split, int nbatch) {
+    extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
+    __shared__ __align__(8) uint64_t full[TC_STAGES], empty[TC_STAGES], acc_full;
+    __shared__ uint32_t tmem_base_s;
+    unsigned char *tiles = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row0 = blockIdx.x * TC_BM, kb0 = blockIdx.y * kb_per_split;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < TC_STAGES; i++) { tc_mbar_init(&full[i], 1); tc_mbar_init(&empty[i], 1); }
+        tc_mbar_init(&acc_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(&tmem_base_s)), "r"(TC_BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < kb_per_split; kb++) {
+                const int st = kb % TC_STAGES, ph = (kb / TC_STAGES) & 1;
+                tc_mbar_wait(&empty[st], ph ^ 1);
+                unsigned char *sa = tiles + (size_t)st * TC_STAGE_BYTES, *sb = sa + TC_A_BYTES;
+                tc_mbar_expect_tx(&full[st], TC_STAGE_BYTES);
+                tc_tma_2d(sa, &mapW, (kb0 + kb) * TC_BK, row0, &full[st]);
+                tc_tma_2d(sb, &mapX, (kb0 + kb) * TC_BK, 0, &full[st]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = tc_idesc();
+            for (int kb = 0; kb < kb_per_split; kb++) {
+                const int st = kb % TC_STAGES, ph = (kb / TC_STAGES) & 1;
+                tc_mbar_wait(&full[st], ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = tc_smem_u32(tiles + (size_t)st * TC_STAGE_BYTES), sb = sa + TC_A_BYTES;
+                const uint64_t ad = tc_smem_desc(sa), bd = tc_smem_desc(sb);
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; k++)          /* UMMA K = 16 bf16 = 32 bytes inside the swizzle row */
+                    tc_mma(tmem_d, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+                tc_commit(&empty[st]);                         /* frees the stage when these MMAs have read it */
+            }
+            tc_commit(&acc_full);
+        }
+    } else {
+        /* epilogue: warp w may touch TMEM lanes [32 (w % 4), +32); thread = one weight row, 64 batch columns */
+        const int q = warp & 3, row = row0 + q * 32 + lane;
+        tc_mbar_wait(&acc_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+        for (int c0 = 0; c0 < TC_BN; c0 += 16) {
+            uint32_t v[16];
+            const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                         : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (row < N) {
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+                    if (c0 + j < nbatch) atomicAdd(Y + (size_t)(c0 + j) * ldy + row, __uint_as_float(v[j]));
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TC_BN) : "memory");
+    }
+}
+
+/* ---- host side ---------------------------------------------------------------------------------------- */
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = NULL;
+static int get_encode() {
+    if (g_encode) return 0;
+    void *fn = NULL;
+    cudaDriverEntryPointQueryResult qr;
+    QTC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+    if (!fn || qr != cudaDriverEntryPointSuccess) { qtc_set_error("cuTensorMapEncodeTiled not available from the driver"); return -1; }
+    g_encode = (EncodeTiledFn)fn;
+    return 0;
+}
+/* bf16 [rows, cols] row-major -> boxes of [box_rows x 64 columns], 128-byte swizzle, zero fill out of bounds */
+static int make_map(CUtensorMap *m, const void *ptr, int rows, int cols, int box_rows) {
+    if (get_encode()) return -1;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows}, strides[1] = {(cuuint64_t)cols * 2};
+    const cuuint32_t box[2] = {TC_BK, (cuuint32_t)box_rows}, es[2] = {1, 1};
+    const CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void *)ptr, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { qtc_set_error("cuTensorMapEncodeTiled failed (%d) for a [%d, %d] bf16 matrix", (int)r, rows, cols); return -1; }
+    return 0;
+}
+
+struct MapKey { const void *p; int rows, cols, box; bool operator==(const MapKey &o) const { return p == o.p && rows == o.rows && cols == o.cols && box == o.box; } };
+struct MapHash { size_t operator()(const MapKey &k) const { return std::hash<const void *>()(k.p) ^ ((size_t)k.rows * 1315423911u) ^ ((size_t)k.cols << 20) ^ (size_t)k.box; } };
+static std::unordered_map<MapKey, CUtensorMap, MapHash> g_maps;
+static const CUtensorMap *cached_map(const void *ptr, int rows, int cols, int box) {
+    const MapKey k = {ptr, rows, cols, box};
+    auto it = g_maps.find(k);
+    if (it != g_maps.end()) return &it->second;
+    CUtensorMap m;
+    if (make_map(&m, ptr, rows, cols, box)) return NULL;
+    return &g_maps.emplace(k, m).first->second;
+}
+void qtc_gemm_tc_forget(const void *ptr) {          /* a buffer was freed: drop its maps */
+    for (auto it = g_maps.begin(); it != g_maps.end();) { if (it->first.p == ptr) it = g_maps.erase(it); else ++it; }
+}
+
+/* K split: the divisor of the k-block count that brings tiles x splits closest to the SM count without passing 2 waves */
+static int pick_splits(int tiles, int kblocks, int sms) {
+    int best = 1; double bs = 1e30;
+    for (int s = 1; s <= kblocks; s++) {
+        if (kblocks % s) continue;
+        const int ctas = tiles * s, waves = (ctas + sms - 1) / sms;
+        /* time ~ waves x (work per CTA + fixed pipeline fill of ~3 k-blocks) */
+        const double cost = waves * ((double)kblocks / s + 3.0);
+        if (cost < bs - 1e-9) { bs = cost; best = s; }
+    }
+    return best;
+}
+
+static int g_tc_attr = 0;
+/* Y[b, n] += sum_k X[b, k] W[n, k];  X: bf16 [TC_BN, K] on device (rows >= nbatch are zero or ignored), W: bf16 [N, K] */
+int qtc_gemm_tc(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K) {
+    if (K % TC_BK || nbatch < 1 || nbatch > TC_BN) { qtc_set_error("gemm_tc: K %% 64 != 0 or batch outside 1..64 (K=%d, batch=%d)", K, nbatch); return -1; }
+    if (!g_tc_attr) { QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM)); g_tc_attr = 1; }
+    const CUtensorMap *mw = cached_map(W, N, K, TC_BM), *mx = cached_map(X, TC_BN, K, TC_BN);
+    if (!mw || !mx) return -1;
+    const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = pick_splits(tiles, kblocks, c->num_sms);
+    k_gemm_tc<<<dim3(tiles, splits), TC_THREADS, TC_SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch);
+    c->launches++;
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { qtc_set_error("gemm_tc launch -> %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
+/* fp32 [rows, cols] -> bf16 (round to nearest even) [rows_pad, cols], rows >= rows zero filled */
+__global__ void k_to_bf16_rows(uint16_t *out, const float *in, int rows, int rows_pad, int cols) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, n = (size_t)rows_pad * cols;
+    if (i >= n) return;
+    const size_t r = i / cols;
+    uint32_t v = 0;
+    if (r < (size_t)rows) { const uint32_t u = __float_as_uint(in[i]); v = (u + 0x7fffu + ((u >> 16) & 1u)) >> 16; }
+    out[i] = (uint16_t)v;
+}
+
+/* test surface: C[M, N] = A[M, K] (fp32, rounded to bf16) . W[N, K]^T (bf16), host pointers, M <= 64 */
+extern "C" int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16_t *W, int M, int N, int K) {
+    if (!C || !A || !W || M < 1 || M > TC_BN || N < 1 || K < TC_BK || K % TC_BK) { qtc_set_error("gemm_bf16_tc: bad shape"); return -1; }
+    qtc_ctx tmp;                                   /* only stream / num_sms / launches are used */
+    memset((void *)&tmp, 0, offsetof(qtc_ctx, allocs));
+    int dev = 0;
+    QTC_CUDA(cudaGetDevice(&dev));
+    QTC_CUDA(cudaDeviceGetAttribute(&tmp.num_sms, cudaDevAttrMultiProcessorCount, dev));
+    float *dA = NULL, *dC = NULL; uint16_t *dW = NULL, *dX = NULL;
+    QTC_CUDA(cudaMalloc(&dA, (size_t)M * K * 4)); QTC_CUDA(cudaMalloc(&dC, (size_t)M * N * 4));
+    QTC_CUDA(cudaMalloc(&dW, (size_t)N * K * 2)); QTC_CUDA(cudaMalloc(&dX, (size_t)TC_BN * K * 2));
+    QTC_CUDA(cudaMemcpy(dA, A, (size_t)M * K * 4, cudaMemcpyHostToDevice));
+    QTC_CUDA(cudaMemcpy(dW, W, (size_t)N * K * 2, cudaMemcpyHostToDevice));
+    QTC_CUDA(cudaMemset(dC, 0, (size_t)M * N * 4));
+    const size_t n = (size_t)TC_BN * K;
+    k_to_bf16_rows<<<(unsigned)((n + 255) / 256), 256>>>(dX, dA, M, TC_BN, K);
+    int rc = qtc_gemm_tc(&tmp, dC, N, dX, dW, M, N, K);
+    if (rc == 0 && cudaDeviceSynchronize() != cudaSuccess) { qtc_set_error("gemm_bf16_tc: %s", cudaGetErrorString(cudaGetLastError())); rc = -1; }
+    if (rc == 0) QTC_CUDA(cudaMemcpy(C, dC, (size_t)M * N * 4, cudaMemcpyDeviceToHost));
+    qtc_gemm_tc_forget(dW); qtc_gemm_tc_forget(dX);
+    cudaFree(dA); cudaFree(dC); cudaFree(dW); cudaFree(dX);
+    return rc;
+}

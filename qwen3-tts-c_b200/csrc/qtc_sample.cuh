@@ -58,7 +58,7 @@ template <int NTF> __device__ __forceinline__ float sblock_max(float v, float *r
     return warp_max(lane < nw ? red[lane] : -3.402823466e+38f);
 }
 template <int NTF>
-__device__ __noinline__ int block_sample_t(const float *lg, float *vv, int V, int top_k, float top_p, float temperature,
+__device__ int block_sample_t(const float *lg, float *vv, int V, int top_k, float top_p, float temperature,
                             uint32_t *rng, SampleSmem &S, float *scratch_f, int *scratch_i) {
     const int tid = threadIdx.x;
     const int NT = NTF ? NTF : (int)blockDim.x;
