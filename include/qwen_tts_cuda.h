@@ -236,14 +236,25 @@ float *qwen_tts_cuda_generate(qtc_ctx_t *ctx, const char *text, const char *spea
                               int *out_codes, int max_codes, int *out_n_frames);
 
 /* ---- batched, request-sharded variant (BASELINE configs 4-5) ---------------
- * B independent utterances decoded in lock-step; utterance b uses seed
- * params.sample_seed + b.  token_ids is a ragged list: offsets[B+1].
- * out_codes [B, max_tokens, groups]; pcm_out (optional) [B, max_tokens*1920]. */
+ * batch <= 64 independent utterances decoded in lock-step on this GPU (more: call again, or shard over GPUs);
+ * projections are tcgen05 GEMMs (one pass over the weights per step for the whole batch).  Utterance b uses seed
+ * params.sample_seed + b.  token_ids is a ragged list: offsets[batch+1]; speaker_ids / language_ids are codec ids
+ * (qwen_tts_config_t.spk_id / codec_language_id values) or -1, or NULL.
+ * out_codes [batch, max_tokens, groups]; out_n_frames [batch] (optional); pcm_out (optional) [batch, max_tokens*1920]. */
 int  qwen_tts_cuda_generate_batch(qtc_ctx_t *ctx, int batch,
                                   const int *token_ids, const int *offsets,
                                   const int *speaker_ids, const int *language_ids,
                                   int *out_codes, int *out_n_frames,
                                   float *pcm_out, int max_tokens);
+/* activations of the batched GEMMs: 3 = exact split of every fp32 value into three bf16 pieces (default: results differ
+ * from the batch-1 fast path by summation order only), 1 = rounded to bf16 (logits within 1e-2 relative) */
+int  qwen_tts_cuda_set_batch_pieces(qtc_ctx_t *ctx, int pieces);
+/* stage API of the batched path (host buffers), the batched forms of c/qwen_tts.h:486-494 */
+int  qwen_tts_cuda_batch_reset(qtc_ctx_t *ctx, int batch, int kv_max);
+int  qwen_tts_cuda_batch_forward(qtc_ctx_t *ctx, int batch, const float *embeds /*[B,hidden]*/,
+                                 float *logits /*[B,vocab] or NULL*/, float *hidden /*[B,hidden] or NULL*/);
+int  qwen_tts_cuda_batch_subtalker(qtc_ctx_t *ctx, int batch, const float *hidden /*[B,hidden]*/,
+                                   const int *first_codes /*[B]*/, int *out_codes /*[B,groups]*/);
 
 /* ---- kernel-level test surface: signatures of c/qwen_tts_kernels.h:27-131 ---
  * host pointers in/out (one H2D/D2H per call: for parity tests, not for speed) */
@@ -261,8 +272,9 @@ int qwen_tts_cuda_snake_beta(float *out, const float *x, const float *alpha, con
                              int channels, int length);
 int qwen_tts_cuda_matmul_f32(float *C, const float *A, const float *B, int M, int N, int K);
 int qwen_tts_cuda_matmul_bf16(float *C, const float *A, const uint16_t *B_bf16, int M, int N, int K);
-/* the batched path's projection kernel on its own (tcgen05 / TMEM / TMA): C[M,N] = bf16(A)[M,K] . W[N,K]^T, M <= 64, K % 64 == 0 */
-int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16_t *W_bf16, int M, int N, int K);
+/* the batched path's projection kernel on its own (tcgen05 / TMEM / TMA): C[M,N] = A[M,K] . W[N,K]^T, M <= 64, K % 64 == 0.
+ * pieces = 1: A rounded to bf16; pieces = 3: A split exactly into three bf16 pieces (fp32-accurate result) */
+int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16_t *W_bf16, int M, int N, int K, int pieces);
 
 /* ---- measurement hooks ------------------------------------------------------ */
 /* time `iters` talker decode steps at KV position `pos` with CUDA events on the

@@ -1,0 +1,589 @@
+/*
+ * qtc_batch.cuh - lock-step decode of B <= 64 independent utterances on one GPU (BASELINE configs 4-5): the
+ * reference's frame loop (c/qwen_tts.c:1282-1373) with every per-utterance vector turned into a [B, .] matrix.
+ * Projections run as tcgen05 GEMMs (qtc_gemm_tc.cu: one pass over the bf16 weights serves the whole batch),
+ * everything else (RMSNorm, per-head QK-norm + RoPE + KV append + GQA attention, SwiGLU, gathers, sampling,
+ * next-input embedding) as small batched kernels with the utterance index in blockIdx.y.
+ *
+ * Activations enter the GEMMs as `pieces` bf16 pieces per value: 3 (default) splits every fp32 value exactly
+ * (hi + mid + lo), so the products are exact and the results differ from the batch-1 fast path only by fp32
+ * summation order - sampled codes then track the C path like batch 1 does; 1 rounds to bf16 (logits within 1e-2
+ * relative, BASELINE north_star), one third of the tensor work.
+ *
+ * Utterances advance together: prompts are right-aligned (utterance b starts `maxlen - len_b` steps late, its
+ * position is negative until then and every kernel skips it), every frame all B rows take one talker step and one
+ * 15-codebook sub-talker loop.  State per utterance (position, frame count, RNG, done flag) lives in HBM so that
+ * the frame is two CUDA graphs replayed by the host.
+ */
+/* (included at the end of qtc_lm.cu: it shares that translation unit's kernels - sampler, next-input embedding) */
+#pragma once
+
+#define BLAUNCH(c)                                                                  \
+    do {                                                                            \
+        (c)->launches++;                                                            \
+        cudaError_t e_ = cudaGetLastError();                                        \
+        if (e_ != cudaSuccess) { qtc_set_error("%s:%d launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return -1; } \
+    } while (0)
+
+#define BROWS 64            /* rows per activation piece in the GEMM staging buffer (TC_BN) */
+
+int qtc_gemm_tc(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K, int pieces);
+void qtc_gemm_tc_forget(const void *ptr);
+
+/* value -> `pieces` bf16 pieces at xb[(p*64 + b) * K + i] */
+__device__ __forceinline__ void store_pieces(uint16_t *xb, int b, int i, int K, int pieces, float v) {
+    for (int p = 0; p < pieces; p++) {
+        const uint32_t u = __float_as_uint(v), h = (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;
+        xb[((size_t)p * BROWS + b) * K + i] = (uint16_t)h;
+        v -= __uint_as_float(h << 16);
+    }
+}
+
+/* RMSNorm of row b of x [B, n] -> bf16 pieces (GEMM input), optionally the fp32 normed row too (out_f32 [B, n]);
+ * also clears zero_n floats of row b of `zero` (the next GEMM's output, which accumulates).  pos[b] < 0: inactive */
+__global__ void __launch_bounds__(256) k_b_norm(uint16_t *xb, float *out_f32, const float *x, const float *w, int n, float eps, int pieces,
+                                                float *zero, int zero_n, const int *pos) {
+    __shared__ float red[32];
+    const int b = blockIdx.x;
+    if (zero) for (int i = threadIdx.x; i < zero_n; i += blockDim.x) zero[(size_t)b * zero_n + i] = 0.0f;
+    const float *xi = x + (size_t)b * n;
+    float ss = 0.0f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) ss = fmaf(xi[i], xi[i], ss);
+    ss = block_sum(ss, red);
+    const float inv = 1.0f / sqrtf(ss / (float)n + eps);
+    const bool live = !pos || pos[b] >= 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float y = live ? xi[i] * inv * w[i] : 0.0f;
+        store_pieces(xb, b, i, n, pieces, y);
+        if (out_f32) out_f32[(size_t)b * n + i] = y;
+    }
+}
+
+/* fp32 rows [B, n] -> bf16 pieces; optionally clears the next GEMM's output rows */
+__global__ void k_b_pieces(uint16_t *xb, const float *src, int n, int pieces, float *zero, int zero_n) {
+    const int b = blockIdx.y;
+    if (zero) for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < zero_n; i += gridDim.x * blockDim.x) zero[(size_t)b * zero_n + i] = 0.0f;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) store_pieces(xb, b, i, n, pieces, src[(size_t)b * n + i]);
+}
+
+/* SwiGLU of gu [B, 2I] (gate | up) -> bf16 pieces [.., I] */
+__global__ void k_b_swiglu(uint16_t *xb, const float *gu, int I, int pieces) {
+    const int b = blockIdx.y;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < I; i += gridDim.x * blockDim.x) {
+        const float g = gu[(size_t)b * 2 * I + i], u = gu[(size_t)b * 2 * I + I + i];
+        store_pieces(xb, b, i, I, pieces, swiglu_act<QTC_FAST>(g, u));
+    }
+}
+
+struct BAttnArgs {
+    const float *qkv;              /* [B, qd + 2 kvd]: q | k | v of the new token */
+    const float *q_norm, *k_norm, *cos, *sin;
+    float *kc, *vc;                /* this layer's cache, utterance stride kv_stride floats: [B][..][kv_max, kvd] */
+    size_t kv_stride;
+    uint16_t *xb;                  /* out: attention output as bf16 pieces [.., qd] */
+    const int *pos; int pos_add;   /* position of utterance b = pos[b] + pos_add (pos == NULL: pos_add) */
+    int heads, kv_heads, hd, pieces;
+    float eps, scale;
+};
+/* talker_attention_single steps 3-6 (c/qwen_tts_talker.c:150-225) for utterance blockIdx.y, Q head blockIdx.x.
+ * dynamic smem: 2 hd + (pos + 1) floats */
+__global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
+    extern __shared__ __align__(16) float sm[];
+    __shared__ float red[32];
+    const int hd = a.hd, half = hd >> 1, b = blockIdx.y, h = blockIdx.x;
+    const int rep = a.heads / a.kv_heads, g = h / rep, kvd = a.kv_heads * hd, qd = a.heads * hd;
+    const int pos = (a.pos ? a.pos[b] : 0) + a.pos_add;
+    if (pos < 0) { for (int i = threadIdx.x; i < hd; i += blockDim.x) store_pieces(a.xb, b, h * hd + i, qd, a.pieces, 0.0f); return; }
+    float *qs = sm, *ks = sm + hd, *sc = sm + 2 * hd;
+    const float *row = a.qkv + (size_t)b * (qd + 2 * kvd), *qr = row + h * hd, *kr = row + qd + g * hd, *vr = row + qd + kvd + g * hd;
+    const float *cs = a.cos + (size_t)pos * hd, *sn = a.sin + (size_t)pos * hd;
+    float *kc = a.kc + (size_t)b * a.kv_stride, *vc = a.vc + (size_t)b * a.kv_stride;
+    float s1 = 0.0f, s2 = 0.0f;
+    for (int i = threadIdx.x; i < hd; i += blockDim.x) { s1 = fmaf(qr[i], qr[i], s1); s2 = fmaf(kr[i], kr[i], s2); }
+    s1 = block_sum(s1, red);
+    s2 = block_sum(s2, red);
+    const float qinv = 1.0f / sqrtf(s1 / (float)hd + a.eps), kinv = 1.0f / sqrtf(s2 / (float)hd + a.eps);
+    for (int i = threadIdx.x; i < hd; i += blockDim.x) { qs[i] = qr[i] * qinv * a.q_norm[i]; ks[i] = kr[i] * kinv * a.k_norm[i]; }
+    __syncthreads();
+    float rq0 = 0, rq1 = 0, rk0 = 0, rk1 = 0;
+    for (int i0 = threadIdx.x; i0 < half; i0 += blockDim.x) {          /* hd <= 256: one trip */
+        const float qa = qs[i0], qb = qs[i0 + half], ka = ks[i0], kb = ks[i0 + half];
+        rq0 = qa * cs[i0] - qb * sn[i0]; rq1 = qb * cs[i0 + half] + qa * sn[i0 + half];
+        rk0 = ka * cs[i0] - kb * sn[i0]; rk1 = kb * cs[i0 + half] + ka * sn[i0 + half];
+    }
+    __syncthreads();
+    if (threadIdx.x < half) { qs[threadIdx.x] = rq0; qs[threadIdx.x + half] = rq1; ks[threadIdx.x] = rk0; ks[threadIdx.x + half] = rk1; }
+    __syncthreads();
+    if (h % rep == 0)
+        for (int i = threadIdx.x; i < hd; i += blockDim.x) { kc[(size_t)pos * kvd + g * hd + i] = ks[i]; vc[(size_t)pos * kvd + g * hd + i] = vr[i]; }
+    const int n = pos + 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int t = warp; t < n; t += nw) {
+        const float *kt = t < pos ? kc + (size_t)t * kvd + g * hd : ks;
+        float d = 0.0f;
+        for (int i = lane; i < hd; i += 32) d = fmaf(qs[i], kt[i], d);
+        d = warp_sum(d);
+        if (lane == 0) sc[t] = d * a.scale;
+    }
+    __syncthreads();
+    float mx = -3.402823466e+38f;
+    for (int t = threadIdx.x; t < n; t += blockDim.x) mx = fmaxf(mx, sc[t]);
+    mx = block_max(mx, red);
+    float tot = 0.0f;
+    for (int t = threadIdx.x; t < n; t += blockDim.x) { const float e = __expf(sc[t] - mx); sc[t] = e; tot += e; }
+    tot = block_sum(tot, red);
+    const float inv = 1.0f / tot;
+    __syncthreads();
+    for (int i = threadIdx.x; i < hd; i += blockDim.x) {
+        float o = 0.0f, o1 = 0.0f;
+        const float *vcol = vc + g * hd + i;
+        int t = 0;
+        for (; t + 1 < pos; t += 2) { o = fmaf(sc[t], vcol[(size_t)t * kvd], o); o1 = fmaf(sc[t + 1], vcol[(size_t)(t + 1) * kvd], o1); }
+        for (; t < pos; t++) o = fmaf(sc[t], vcol[(size_t)t * kvd], o);
+        o = fmaf(sc[pos], vr[i], o + o1);
+        store_pieces(a.xb, b, h * hd + i, qd, a.pieces, o * inv);
+    }
+}
+
+/* ---- small batched helpers --------------------------------------------------------------------------- */
+/* x[b] = prefill[b][pos[b]] while the utterance is inside its prompt window (pos[b] >= 0), else 0 */
+__global__ void k_b_fill_prefill(float *x, const float *prefill, int rows_cap, const int *pos, int H) {
+    const int b = blockIdx.y, p = pos[b];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < H; i += gridDim.x * blockDim.x)
+        x[(size_t)b * H + i] = p >= 0 ? prefill[((size_t)b * rows_cap + p) * H + i] : 0.0f;
+}
+__global__ void k_b_copy_rows(float *dst, const float *src, int n) {
+    const int b = blockIdx.y;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[(size_t)b * n + i] = src[(size_t)b * n + i];
+}
+__global__ void k_b_pos_add(int *pos, int n, int add) { const int b = blockIdx.x * blockDim.x + threadIdx.x; if (b < n) pos[b] += add; }
+/* talker position of every utterance follows its GenState (captured graphs replay without host patching) */
+__global__ void k_b_bump_state_pos(GenState *st, int *pos, int n) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < n) { if (!st[b].done) st[b].pos += 1; pos[b] = st[b].pos; }
+}
+/* sub-talker input of code group g (ST_PROJECT_INPUT, c/qwen_tts_talker.c:693-726): the talker hidden state (g = 0) or the
+ * bf16 embedding row of the previous code -> fp32 rows [B, Hin] */
+__global__ void k_b_sub_input(float *out, const float *hidden, const uint16_t *table, const int *codes, int code_stride, int code_idx, int Hin) {
+    const int b = blockIdx.y;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Hin; i += gridDim.x * blockDim.x)
+        out[(size_t)b * Hin + i] = table ? bf16_to_f32(table[(size_t)codes[(size_t)b * code_stride + code_idx] * Hin + i]) : hidden[(size_t)b * Hin + i];
+}
+/* y[b, i] = bias[i] (or 0): initial value of a GEMM output that accumulates */
+__global__ void k_b_init_rows(float *y, const float *bias, int n) {
+    const int b = blockIdx.y;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) y[(size_t)b * n + i] = bias ? bias[i] : 0.0f;
+}
+__global__ void k_b_copy_pad_rows(float *dst, const float *src, int n_in, int n_out) {
+    const int b = blockIdx.y;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_out; i += gridDim.x * blockDim.x) dst[(size_t)b * n_out + i] = i < n_in ? src[(size_t)b * n_in + i] : 0.0f;
+}
+
+/* ---- device-resident batch state ----------------------------------------------------------------------- */
+struct BStack {                   /* one decoder stack's batched buffers */
+    float *x, *qkv, *gu, *logits; /* [B,H] [B,qd+2kvd] [B,2I] [B,vocab] */
+    float *kc, *vc;               /* [B][layers][kv_max][kvd] */
+    int kv_max;
+};
+struct BatchBuf {
+    int B;                        /* capacity (utterances) */
+    int pieces;
+    uint16_t *xb;                 /* GEMM input staging: [pieces*64, maxK] bf16 */
+    int maxK;
+    BStack tk, st;
+    float *hidden;                /* [B,H] post-final-norm talker hidden (ctx->tk_x of every utterance) */
+    float *sub_in;                /* [B,H] gathered sub-talker input */
+    int *pos;                     /* [B] talker position of the token in flight (negative: not started) */
+    GenState *state; GenState *state_host;
+    int *hist;                    /* [B, vocab] */
+    int *frame_codes;             /* [B, G] */
+    int *codes; int codes_cap;    /* [B, codes_cap, G] */
+    float *next_embed;            /* [B,H] */
+    float *prefill; int prefill_cap;   /* [B, prefill_cap, H] */
+    float *trailing; int trailing_cap; /* [B, trailing_cap, H] */
+    uint32_t *sub_rng;            /* [B] */
+    uint32_t *seeds;              /* [B] bit pattern of (float)(sample_seed + b): RNG seed of utterance b */
+    float *scratch_f; int *scratch_i;  /* slow-path sampler scratch [B, vocab] */
+    cudaGraphExec_t g_front, g_talker;
+    int graph_key, graph_B;
+    std::vector<void *> allocs;
+};
+
+static void *balloc(BatchBuf *bb, size_t bytes) {
+    void *p = NULL;
+    if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) { qtc_set_error("batch: cudaMalloc of %.1f MB failed", bytes / 1e6); return NULL; }
+    cudaMemset(p, 0, bytes ? bytes : 16);
+    bb->allocs.push_back(p);
+    return p;
+}
+void qtc_batch_release(qtc_ctx *c) {
+    BatchBuf *bb = c->bb;
+    if (!bb) return;
+    cudaStreamSynchronize(c->stream);
+    if (bb->g_front) cudaGraphExecDestroy(bb->g_front);
+    if (bb->g_talker) cudaGraphExecDestroy(bb->g_talker);
+    for (void *p : bb->allocs) { qtc_gemm_tc_forget(p); cudaFree(p); }
+    if (bb->state_host) cudaFreeHost(bb->state_host);
+    delete bb;
+    c->bb = NULL;
+}
+
+static int bstack_alloc(BatchBuf *bb, BStack *s, const LmDev *lm, int B, int kv_max) {
+    const size_t qd = (size_t)lm->heads * lm->head_dim, kvd = (size_t)lm->kv_heads * lm->head_dim;
+    s->x = (float *)balloc(bb, (size_t)B * lm->hidden * 4);
+    s->qkv = (float *)balloc(bb, (size_t)B * (qd + 2 * kvd) * 4);
+    s->gu = (float *)balloc(bb, (size_t)B * 2 * lm->inter * 4);
+    s->logits = (float *)balloc(bb, (size_t)B * lm->vocab * 4);
+    s->kc = (float *)balloc(bb, (size_t)B * lm->layers * kv_max * kvd * 4);
+    s->vc = (float *)balloc(bb, (size_t)B * lm->layers * kv_max * kvd * 4);
+    s->kv_max = kv_max;
+    return (s->x && s->qkv && s->gu && s->logits && s->kc && s->vc) ? 0 : -1;
+}
+
+/* (re)build the batch state for B utterances, kv_max talker positions, `frames` frames, prompt / trailing capacities */
+static int batch_ensure(qtc_ctx *c, int B, int kv_need, int frames, int pre_rows, int tr_rows) {
+    BatchBuf *bb = c->bb;
+    const int pieces = c->batch_pieces == 1 ? 1 : 3;
+    if (bb && bb->B >= B && bb->tk.kv_max >= kv_need && bb->codes_cap >= frames && bb->prefill_cap >= pre_rows && bb->trailing_cap >= tr_rows &&
+        bb->pieces == pieces) return 0;
+    qtc_batch_release(c);
+    bb = new BatchBuf();
+    bb->B = B; bb->pieces = pieces; bb->g_front = NULL; bb->g_talker = NULL; bb->graph_key = -1; bb->graph_B = 0; bb->state_host = NULL;
+    c->bb = bb;
+    const LmDev *tk = &c->talker, *st = &c->sub;
+    const int H = c->H, G = c->G;
+    int maxK = tk->hidden > tk->inter ? tk->hidden : tk->inter;
+    if (tk->heads * tk->head_dim > maxK) maxK = tk->heads * tk->head_dim;
+    if (st->inter > maxK) maxK = st->inter;
+    if (st->heads * st->head_dim > maxK) maxK = st->heads * st->head_dim;
+    bb->maxK = maxK;
+    const int kv_max = ((kv_need + 63) / 64) * 64;
+    bb->xb = (uint16_t *)balloc(bb, (size_t)pieces * BROWS * maxK * 2);
+    if (!bb->xb || bstack_alloc(bb, &bb->tk, tk, B, kv_max) || bstack_alloc(bb, &bb->st, st, B, G + 2)) return -1;
+    bb->hidden = (float *)balloc(bb, (size_t)B * H * 4);
+    bb->sub_in = (float *)balloc(bb, (size_t)B * H * 4);
+    bb->pos = (int *)balloc(bb, (size_t)B * 4);
+    bb->state = (GenState *)balloc(bb, (size_t)B * sizeof(GenState));
+    bb->hist = (int *)balloc(bb, (size_t)B * tk->vocab * 4);
+    bb->frame_codes = (int *)balloc(bb, (size_t)B * G * 4);
+    bb->codes_cap = frames + 8;
+    bb->codes = (int *)balloc(bb, (size_t)B * bb->codes_cap * G * 4);
+    bb->next_embed = (float *)balloc(bb, (size_t)B * H * 4);
+    bb->prefill_cap = pre_rows; bb->trailing_cap = tr_rows;
+    bb->prefill = (float *)balloc(bb, (size_t)B * pre_rows * H * 4);
+    bb->trailing = (float *)balloc(bb, (size_t)B * tr_rows * H * 4);
+    bb->sub_rng = (uint32_t *)balloc(bb, (size_t)B * 4);
+    bb->seeds = (uint32_t *)balloc(bb, (size_t)B * 4);
+    const int vmax = tk->vocab > st->vocab ? tk->vocab : st->vocab;
+    bb->scratch_f = (float *)balloc(bb, (size_t)B * vmax * 4);
+    bb->scratch_i = (int *)balloc(bb, (size_t)B * vmax * 4);
+    if (!bb->hidden || !bb->sub_in || !bb->pos || !bb->state || !bb->hist || !bb->frame_codes || !bb->codes || !bb->next_embed || !bb->prefill ||
+        !bb->trailing || !bb->sub_rng || !bb->seeds || !bb->scratch_f || !bb->scratch_i) return -1;
+    if (cudaMallocHost(&bb->state_host, (size_t)B * sizeof(GenState)) != cudaSuccess) { qtc_set_error("batch: pinned state"); return -1; }
+    /* RoPE tables of both stacks must cover the positions (they are shared with the batch-1 path) */
+    if (qtc_ensure_kv(c, &c->tk, &c->talker, kv_max) || qtc_ensure_kv(c, &c->st, &c->sub, G + 2)) return -1;
+    return 0;
+}
+
+/* ---- one decoder-stack step for the whole batch ------------------------------------------------------------
+ * s->x [B,H] holds the inputs on entry.  pos (device, per utterance, may be NULL) + pos_add = KV position.
+ * hidden_out (optional) receives the post-final-norm hidden rows; head_w (optional) -> s->logits [B, head_rows]. */
+static int b_lm_step(qtc_ctx *c, BatchBuf *bb, const LmDev *lm, BStack *s, const LmBuffers *rope, int B, const int *pos, int pos_add,
+                     float *hidden_out, const uint16_t *head_w, int head_rows) {
+    const int H = lm->hidden, I = lm->inter, hd = lm->head_dim, qd = lm->heads * hd, kvd = lm->kv_heads * hd, np = bb->pieces;
+    const int ldq = qd + 2 * kvd;
+    const size_t kv_stride = (size_t)lm->layers * s->kv_max * kvd;
+    for (int l = 0; l < lm->layers; l++) {
+        const LmLayerDev *w = &lm->layer[l];
+        k_b_norm<<<B, 256, 0, c->stream>>>(bb->xb, NULL, s->x, w->in_norm, H, lm->eps, np, s->qkv, ldq, pos);
+        BLAUNCH(c);
+        if (qtc_gemm_tc(c, s->qkv, ldq, bb->xb, w->wq, B, qd, H, np) || qtc_gemm_tc(c, s->qkv + qd, ldq, bb->xb, w->wk, B, kvd, H, np) ||
+            qtc_gemm_tc(c, s->qkv + qd + kvd, ldq, bb->xb, w->wv, B, kvd, H, np)) return -1;
+        BAttnArgs a;
+        a.qkv = s->qkv; a.q_norm = w->q_norm; a.k_norm = w->k_norm; a.cos = rope->cos; a.sin = rope->sin;
+        a.kc = s->kc + (size_t)l * s->kv_max * kvd; a.vc = s->vc + (size_t)l * s->kv_max * kvd; a.kv_stride = kv_stride;
+        a.xb = bb->xb; a.pos = pos; a.pos_add = pos_add; a.heads = lm->heads; a.kv_heads = lm->kv_heads; a.hd = hd; a.pieces = np;
+        a.eps = lm->eps; a.scale = 1.0f / sqrtf((float)hd);
+        k_b_attn<<<dim3(lm->heads, B), 128, (size_t)(2 * hd + s->kv_max + 32) * 4, c->stream>>>(a);
+        BLAUNCH(c);
+        if (qtc_gemm_tc(c, s->x, H, bb->xb, w->wo, B, H, qd, np)) return -1;                      /* x += Wo . att */
+        k_b_norm<<<B, 256, 0, c->stream>>>(bb->xb, NULL, s->x, w->post_norm, H, lm->eps, np, s->gu, 2 * I, pos);
+        BLAUNCH(c);
+        if (qtc_gemm_tc(c, s->gu, 2 * I, bb->xb, w->gate, B, I, H, np) || qtc_gemm_tc(c, s->gu + I, 2 * I, bb->xb, w->up, B, I, H, np)) return -1;
+        k_b_swiglu<<<dim3((I + 255) / 256, B), 256, 0, c->stream>>>(bb->xb, s->gu, I, np);
+        BLAUNCH(c);
+        if (qtc_gemm_tc(c, s->x, H, bb->xb, w->down, B, H, I, np)) return -1;                     /* x += Wdown . h */
+    }
+    k_b_norm<<<B, 256, 0, c->stream>>>(bb->xb, hidden_out, s->x, lm->final_norm, H, lm->eps, np, head_w ? s->logits : NULL, head_rows, pos);
+    BLAUNCH(c);
+    if (head_w && qtc_gemm_tc(c, s->logits, head_rows, bb->xb, head_w, B, head_rows, H, np)) return -1;
+    return 0;
+}
+
+/* qwen_tts_talker_forward for every utterance: embeds [B,H] (device) -> hidden, logits; positions advance */
+static int b_talker_forward(qtc_ctx *c, BatchBuf *bb, int B, const float *embeds_dev, int with_head) {
+    const int H = c->H;
+    k_b_copy_rows<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->tk.x, embeds_dev, H);
+    BLAUNCH(c);
+    if (b_lm_step(c, bb, &c->talker, &bb->tk, &c->tk, B, bb->pos, 0, bb->hidden, with_head ? c->codec_head : NULL, c->talker.vocab)) return -1;
+    k_b_pos_add<<<(B + 63) / 64, 64, 0, c->stream>>>(bb->pos, B, 1);
+    BLAUNCH(c);
+    return 0;
+}
+
+static void b_sub_sample_args(qtc_ctx *c, BatchBuf *bb, SampleArgs *a, int g, const uint32_t *seed_tab) {
+    memset(a, 0, sizeof(*a));
+    const int G = c->G, v = c->sub.vocab;
+    a->logits = bb->st.logits; a->bs_logits = v;
+    a->cfg.vocab = v; a->cfg.top_k = c->params.subtalker_top_k; a->cfg.top_p = c->params.subtalker_top_p;
+    a->cfg.temperature = c->params.subtalker_temperature; a->cfg.suppress_from = -1; a->cfg.eos_id = -1; a->cfg.rep_penalty = 1.0f;
+    a->rng = bb->sub_rng; a->bs_rng = 1; a->out_token = bb->frame_codes + g; a->bs_out = G; a->role = 1;
+    a->reseed = g == 1; a->seed_tab = seed_tab;
+    a->scratch_f = bb->scratch_f; a->scratch_i = bb->scratch_i; a->bs_scratch = c->talker.vocab > v ? c->talker.vocab : v;
+}
+
+/* qwen_tts_subtalker_generate (c/qwen_tts_talker.c:539-736) for every utterance: bb->hidden, bb->frame_codes[:,0] -> frame_codes[:,1..] */
+static int b_subtalker(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_tab) {
+    const LmDev *lm = &c->sub;
+    const int H = c->H, h = lm->hidden, G = c->G, np = bb->pieces;
+    if (set_smem_attrs()) return -1;
+    for (int g = 0; g < G; g++) {
+        const uint16_t *table = g == 0 ? NULL : (g == 1 ? c->codec_embedding : c->sub_emb[g - 2]);
+        k_b_sub_input<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->sub_in, bb->hidden, table, bb->frame_codes, G, g > 0 ? g - 1 : 0, H);
+        BLAUNCH(c);
+        if (c->sub_in_w) {
+            k_b_pieces<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->xb, bb->sub_in, H, np, NULL, 0);
+            BLAUNCH(c);
+            k_b_init_rows<<<dim3((h + 255) / 256, B), 256, 0, c->stream>>>(bb->st.x, c->sub_in_b, h);
+            BLAUNCH(c);
+            if (qtc_gemm_tc(c, bb->st.x, h, bb->xb, c->sub_in_w, B, h, H, np)) return -1;
+        } else {
+            k_b_copy_pad_rows<<<dim3((h + 255) / 256, B), 256, 0, c->stream>>>(bb->st.x, bb->sub_in, H < h ? H : h, h);
+            BLAUNCH(c);
+        }
+        if (b_lm_step(c, bb, lm, &bb->st, &c->st, B, NULL, g, NULL, g >= 1 ? c->sub_head[g - 1] : NULL, lm->vocab)) return -1;
+        if (g >= 1) {
+            SampleArgs a;
+            b_sub_sample_args(c, bb, &a, g, seed_tab);
+            k_sample<<<B, SAMPLE_THREADS, (size_t)a.cfg.vocab * 8, c->stream>>>(a);
+            BLAUNCH(c);
+        }
+    }
+    return 0;
+}
+
+/* c/qwen_tts.c:1302-1363 for every utterance: logits policy + sample, sub-talker, next-input embedding, frame counter */
+static int b_frame_front(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_tab) {
+    const LmDev *lm = &c->talker;
+    const int H = c->H, G = c->G;
+    SampleArgs a;
+    memset(&a, 0, sizeof(a));
+    a.logits = bb->tk.logits; a.bs_logits = lm->vocab;
+    a.cfg.vocab = lm->vocab; a.cfg.top_k = c->params.top_k; a.cfg.top_p = c->params.top_p; a.cfg.temperature = c->params.temperature;
+    a.cfg.suppress_from = lm->vocab - 1024; a.cfg.eos_id = c->host.codec_eos_id; a.cfg.rep_penalty = c->params.repetition_penalty;
+    a.rng = &bb->state->rng; a.bs_rng = (int)(sizeof(GenState) / 4);
+    a.hist_count = bb->hist; a.bs_hist = lm->vocab; a.st = bb->state; a.codes = bb->frame_codes; a.bs_codes = G; a.G = G; a.role = 0;
+    a.scratch_f = bb->scratch_f; a.scratch_i = bb->scratch_i; a.bs_scratch = lm->vocab > c->sub.vocab ? lm->vocab : c->sub.vocab;
+    if (set_smem_attrs()) return -1;
+    k_sample<<<B, SAMPLE_THREADS, (size_t)lm->vocab * 8, c->stream>>>(a);
+    BLAUNCH(c);
+    if (b_subtalker(c, bb, B, seed_tab)) return -1;
+    NextEmbedArgs n;
+    memset(&n, 0, sizeof(n));
+    n.out = bb->next_embed; n.codec_embedding = c->codec_embedding;
+    for (int g = 0; g < G - 1; g++) n.sub_emb[g] = c->sub_emb[g];
+    n.frame_codes = bb->frame_codes; n.bs_fc = G; n.all_codes = bb->codes; n.bs_codes = bb->codes_cap * G;
+    n.trailing = bb->trailing; n.bs_tr = bb->trailing_cap * H; n.tts_pad = c->tts_pad; n.st = bb->state; n.H = H; n.G = G;
+    k_next_embed<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(n);
+    BLAUNCH(c);
+    k_advance_step<<<B, 1, 0, c->stream>>>(bb->state);
+    BLAUNCH(c);
+    return 0;
+}
+
+/* ---- frame loop as two CUDA graphs ------------------------------------------------------------------------ */
+static int b_params_key(const qtc_ctx *c, int B) {
+    uint32_t h = 2166136261u;
+    const unsigned char *p = (const unsigned char *)&c->params;
+    for (size_t i = 0; i < sizeof(c->params); i++) h = (h ^ p[i]) * 16777619u;
+    h = (h ^ (uint32_t)B) * 16777619u;
+    return (int)(h & 0x7fffffff);
+}
+static int b_capture(qtc_ctx *c, cudaGraphExec_t *out, int which, int B, long long *nlaunch) {
+    BatchBuf *bb = c->bb;
+    cudaGraph_t g = NULL;
+    QTC_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    const long long before = c->launches;
+    const int rc = which == 0 ? b_frame_front(c, bb, B, bb->seeds) : b_talker_forward(c, bb, B, bb->next_embed, 1);
+    *nlaunch = c->launches - before;
+    c->launches = before;
+    const cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+    if (rc != 0 || e != cudaSuccess) { if (g) cudaGraphDestroy(g); if (e != cudaSuccess) qtc_set_error("batch graph capture failed: %s", cudaGetErrorString(e)); return -1; }
+    if (*out) { cudaGraphExecDestroy(*out); *out = NULL; }
+    const cudaError_t ei = cudaGraphInstantiate(out, g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) { qtc_set_error("batch graph instantiate failed: %s", cudaGetErrorString(ei)); return -1; }
+    return 0;
+}
+
+static int b_pull_state(qtc_ctx *c, BatchBuf *bb, int B) {
+    QTC_CUDA(cudaMemcpyAsync(bb->state_host, bb->state, (size_t)B * sizeof(GenState), cudaMemcpyDeviceToHost, c->stream));
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+/* ---- whole batch: prompts -> codes (-> PCM) ------------------------------------------------------------------
+ * qwen_tts_generate (c/qwen_tts.c:1059-1443) for B utterances at once; utterance b draws from seed sample_seed + b. */
+extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *token_ids, const int *offsets, const int *speaker_ids,
+                                            const int *language_ids, int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens) {
+    if (!c || c->talker.layers <= 0) { qtc_set_error("generate_batch: context has no talker weights"); return -1; }
+    if (batch < 1 || batch > BROWS || !token_ids || !offsets || !out_codes || max_tokens < 1) { qtc_set_error("generate_batch: batch must be 1..64 and buffers non-null"); return -1; }
+    if (c->talker.hidden % 64 || c->talker.inter % 64 || (c->talker.heads * c->talker.head_dim) % 64 || c->sub.hidden % 64 || c->sub.inter % 64 ||
+        (c->sub.heads * c->sub.head_dim) % 64) { qtc_set_error("generate_batch: model dimensions must be multiples of 64"); return -1; }
+    const int B = batch, H = c->H, G = c->G;
+    const int fixed = c->params.fixed_codec_tokens > 0 ? c->params.fixed_codec_tokens : 0;
+    int limit = fixed > 0 ? fixed : c->params.max_new_tokens;
+    if (limit > max_tokens) limit = max_tokens;
+    int max_tr = 1, max_plen = 10;
+    for (int b = 0; b < B; b++) {
+        const int n = offsets[b + 1] - offsets[b];
+        if (n < 8) { qtc_set_error("generate_batch: utterance %d has %d token ids, need >= 8", b, n); return -1; }
+        if (n - 8 > max_tr) max_tr = n - 8;
+    }
+    if (batch_ensure(c, B, max_plen + limit + 2, limit, max_plen + 3, max_tr + 1)) return -1;
+    BatchBuf *bb = c->bb;
+    cudaEventRecord(c->ev2, c->stream);
+    /* prompts: built per utterance with the batch-1 prompt kernels straight into the batch buffers */
+    std::vector<int> plen(B), ntr(B), pos0(B);
+    std::vector<uint32_t> seeds(B);
+    int maxlen = 0;
+    for (int b = 0; b < B; b++) {
+        const int spk = speaker_ids ? speaker_ids[b] : -1, lang = language_ids ? language_ids[b] : -1;
+        if (qtc_build_prompt_dev(c, token_ids + offsets[b], offsets[b + 1] - offsets[b], spk, lang, bb->prefill + (size_t)b * bb->prefill_cap * H, &plen[b],
+                                 bb->trailing + (size_t)b * bb->trailing_cap * H, &ntr[b], c->tts_pad)) return -1;
+        if (plen[b] > maxlen) maxlen = plen[b];
+    }
+    for (int b = 0; b < B; b++) {
+        GenState s;
+        memset(&s, 0, sizeof(s));
+        const float f = (float)(c->params.sample_seed + b);
+        memcpy(&s.rng, &f, 4); memcpy(&seeds[b], &f, 4);
+        s.limit = limit; s.fixed = fixed > 0; s.n_trailing = ntr[b]; s.stop_step = limit;
+        bb->state_host[b] = s;
+        pos0[b] = plen[b] - maxlen;               /* right-aligned prompts: negative until the utterance starts */
+    }
+    QTC_CUDA(cudaMemcpyAsync(bb->state, bb->state_host, (size_t)B * sizeof(GenState), cudaMemcpyHostToDevice, c->stream));
+    QTC_CUDA(cudaMemcpyAsync(bb->pos, pos0.data(), (size_t)B * 4, cudaMemcpyHostToDevice, c->stream));
+    QTC_CUDA(cudaMemcpyAsync(bb->seeds, seeds.data(), (size_t)B * 4, cudaMemcpyHostToDevice, c->stream));
+    QTC_CUDA(cudaMemsetAsync(bb->hist, 0, (size_t)B * c->talker.vocab * 4, c->stream));
+    QTC_CUDA(cudaStreamSynchronize(c->stream));      /* pos0 / seeds are stack vectors */
+    /* lock-step prefill: per token the reference's batched prefill does a decode step's arithmetic */
+    for (int s = 0; s < maxlen; s++) {
+        k_b_fill_prefill<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->tk.x, bb->prefill, bb->prefill_cap, bb->pos, H);
+        BLAUNCH(c);
+        const int last = s + 1 == maxlen;
+        if (b_lm_step(c, bb, &c->talker, &bb->tk, &c->tk, B, bb->pos, 0, bb->hidden, last ? c->codec_head : NULL, c->talker.vocab)) return -1;
+        k_b_pos_add<<<(B + 63) / 64, 64, 0, c->stream>>>(bb->pos, B, 1);
+        BLAUNCH(c);
+    }
+    const int key = b_params_key(c, B);
+    static long long lf = 0, lt = 0;
+    if (bb->graph_key != key || bb->graph_B != B || !bb->g_front || !bb->g_talker) {
+        if (b_capture(c, &bb->g_front, 0, B, &lf) || b_capture(c, &bb->g_talker, 1, B, &lt)) return -1;
+        bb->graph_key = key; bb->graph_B = B;
+    }
+    QTC_CUDA(cudaEventRecord(c->ev0, c->stream));
+    int launched = 0;
+    const int poll = fixed > 0 ? limit : 8;
+    while (launched < limit) {
+        const int upto = launched + poll < limit ? launched + poll : limit;
+        for (; launched < upto; launched++) {
+            QTC_CUDA(cudaGraphLaunch(bb->g_front, c->stream));
+            c->launches += lf;
+            if (launched + 1 < limit) { QTC_CUDA(cudaGraphLaunch(bb->g_talker, c->stream)); c->launches += lt; }
+        }
+        if (b_pull_state(c, bb, B)) return -1;
+        bool all_done = true;
+        for (int b = 0; b < B; b++) all_done = all_done && bb->state_host[b].done;
+        if (all_done) break;
+    }
+    QTC_CUDA(cudaEventRecord(c->ev1, c->stream));
+    if (b_pull_state(c, bb, B)) return -1;
+    std::vector<int> host_codes((size_t)bb->codes_cap * G);
+    int total_frames = 0;
+    for (int b = 0; b < B; b++) {
+        const int n = bb->state_host[b].step;
+        if (out_n_frames) out_n_frames[b] = n;
+        total_frames += n;
+        if (n > 0) {
+            QTC_CUDA(cudaMemcpy(host_codes.data(), bb->codes + (size_t)b * bb->codes_cap * G, (size_t)n * G * 4, cudaMemcpyDeviceToHost));
+            memcpy(out_codes + (size_t)b * max_tokens * G, host_codes.data(), (size_t)n * G * 4);
+        }
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->perf.talker_ms = ms; c->perf.codec_tokens = total_frames;
+    if (pcm_out) {
+        if (!c->codec) { qtc_set_error("generate_batch: context has no codec weights"); return -1; }
+        for (int b = 0; b < B; b++) {
+            const int n = bb->state_host[b].step;
+            if (n <= 0) continue;
+            int ns = 0;
+            float *pcm = qtc_codec_decode_dev(c, bb->codes + (size_t)b * bb->codes_cap * G, n, &ns, NULL);
+            if (!pcm) return -1;
+            memcpy(pcm_out + (size_t)b * max_tokens * 1920, pcm, (size_t)ns * 4);
+            free(pcm);
+        }
+        float dms = 0;
+        cudaEventElapsedTime(&dms, c->ev2, c->ev3);
+        c->perf.device_ms = dms;
+    } else {
+        float dms = 0;
+        cudaEventElapsedTime(&dms, c->ev2, c->ev1);
+        c->perf.device_ms = dms;
+    }
+    return 0;
+}
+
+/* ---- stage-level test surface of the batched path (host buffers) -------------------------------------------------- */
+/* all B utterances at KV length 0 */
+extern "C" int qwen_tts_cuda_batch_reset(qtc_ctx_t *c, int batch, int kv_max) {
+    if (!c || c->talker.layers <= 0 || batch < 1 || batch > BROWS) { qtc_set_error("batch_reset: bad arguments"); return -1; }
+    if (batch_ensure(c, batch, kv_max, 8, 16, 2)) return -1;
+    QTC_CUDA(cudaMemsetAsync(c->bb->pos, 0, (size_t)batch * 4, c->stream));
+    return 0;
+}
+/* one talker decode step for every utterance: embeds [B,H] -> logits [B,vocab] (optional), hidden [B,H] (optional) */
+extern "C" int qwen_tts_cuda_batch_forward(qtc_ctx_t *c, int batch, const float *embeds, float *logits, float *hidden) {
+    if (!c || !c->bb || batch < 1 || batch > c->bb->B || !embeds) { qtc_set_error("batch_forward: call batch_reset first"); return -1; }
+    BatchBuf *bb = c->bb;
+    const int H = c->H, V = c->talker.vocab;
+    QTC_CUDA(cudaMemcpyAsync(bb->next_embed, embeds, (size_t)batch * H * 4, cudaMemcpyHostToDevice, c->stream));
+    if (b_talker_forward(c, bb, batch, bb->next_embed, 1)) return -1;
+    if (logits) QTC_CUDA(cudaMemcpyAsync(logits, bb->tk.logits, (size_t)batch * V * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (hidden) QTC_CUDA(cudaMemcpyAsync(hidden, bb->hidden, (size_t)batch * H * 4, cudaMemcpyDeviceToHost, c->stream));
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+/* the 15-codebook loop for every utterance: hidden [B,H], first_codes [B] -> out_codes [B,G]; utterance b seeds with sample_seed + b */
+extern "C" int qwen_tts_cuda_batch_subtalker(qtc_ctx_t *c, int batch, const float *hidden, const int *first_codes, int *out_codes) {
+    if (!c || !c->bb || batch < 1 || batch > c->bb->B || !hidden || !first_codes || !out_codes) { qtc_set_error("batch_subtalker: call batch_reset first"); return -1; }
+    BatchBuf *bb = c->bb;
+    const int H = c->H, G = c->G;
+    std::vector<int> fc((size_t)batch * G, 0);
+    std::vector<uint32_t> seeds(batch);
+    for (int b = 0; b < batch; b++) { fc[(size_t)b * G] = first_codes[b]; const float f = (float)(c->params.sample_seed + b); memcpy(&seeds[b], &f, 4); }
+    QTC_CUDA(cudaMemcpyAsync(bb->hidden, hidden, (size_t)batch * H * 4, cudaMemcpyHostToDevice, c->stream));
+    QTC_CUDA(cudaMemcpyAsync(bb->frame_codes, fc.data(), fc.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    QTC_CUDA(cudaMemcpyAsync(bb->seeds, seeds.data(), (size_t)batch * 4, cudaMemcpyHostToDevice, c->stream));
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    if (b_subtalker(c, bb, batch, bb->seeds)) return -1;
+    QTC_CUDA(cudaMemcpyAsync(out_codes, bb->frame_codes, (size_t)batch * G * 4, cudaMemcpyDeviceToHost, c->stream));
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+/* 3: activations split exactly into three bf16 pieces (default); 1: rounded to bf16 */
+extern "C" int qwen_tts_cuda_set_batch_pieces(qtc_ctx_t *c, int pieces) {
+    if (!c || (pieces != 1 && pieces != 3)) return -1;
+    c->batch_pieces = pieces;
+    return 0;
+}

@@ -20,14 +20,20 @@
 #include <unordered_map>
 
 #define TC_BM 128           /* weight rows per CTA (UMMA M) */
-#define TC_BN 64            /* batch columns (UMMA N) */
+#define TC_BN 64            /* batch columns per piece; UMMA N = 64 x pieces */
 #define TC_BK 64            /* K per stage: 64 bf16 = one 128-byte swizzle row */
-#define TC_STAGES 6
 #define TC_A_BYTES (TC_BM * TC_BK * 2)
-#define TC_B_BYTES (TC_BN * TC_BK * 2)
-#define TC_STAGE_BYTES (TC_A_BYTES + TC_B_BYTES)
 #define TC_THREADS 192
-#define TC_SMEM (TC_STAGES * TC_STAGE_BYTES + 1024)
+/* NP = activation pieces: 1 = activations rounded to bf16; 3 = exact split x = hi + mid + lo (three bf16 pieces stacked
+ * as 192 B-operand rows), which makes every product exact and leaves only fp32 summation-order differences */
+template <int NP> struct TcCfg {
+    static constexpr int N = TC_BN * NP;                       /* UMMA N */
+    static constexpr int B_BYTES = N * TC_BK * 2;
+    static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
+    static constexpr int STAGES = NP == 1 ? 6 : 5;
+    static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
+    static constexpr int TMEM_COLS = NP == 1 ? 64 : 256;       /* power of two >= N */
+};
 
 __device__ __forceinline__ uint32_t tc_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void tc_mbar_init(uint64_t *bar, unsigned count) {
@@ -60,9 +66,9 @@ __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
     d |= 2ull << 61;                                  /* layout: SWIZZLE_128B                   [61,64) */
     return d;
 }
-/* kind::f16 instruction descriptor: D f32, A/B bf16, both K-major, M = 128, N = 64 */
-__device__ __forceinline__ uint32_t tc_idesc() {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+/* kind::f16 instruction descriptor: D f32, A/B bf16, both K-major, M = 128, N = n */
+__device__ __forceinline__ uint32_t tc_idesc(int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
 }
 __device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -77,9 +83,12 @@ __device__ __forceinline__ void tc_commit(uint64_t *bar) {
 }
 
 /* grid (row tiles, K splits).  Y [batch, ldy] fp32, pre-initialised; rows >= N and batch columns >= nbatch are dropped */
+template <int NP>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapX,
                                                             float *Y, int N, int ldy, int kb_per_split, int nbatch) {
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
+    typedef TcCfg<NP> Cfg;
+    constexpr int TC_STAGES = Cfg::STAGES, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
     __shared__ __align__(8) uint64_t full[TC_STAGES], empty[TC_STAGES], acc_full;
     __shared__ uint32_t tmem_base_s;
     unsigned char *tiles = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
@@ -94,7 +103,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX) : "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(&tmem_base_s)), "r"(TC_BN) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(&tmem_base_s)), "r"(Cfg::TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -115,7 +124,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = tc_idesc();
+            const uint32_t idesc = tc_idesc(Cfg::N);
             for (int kb = 0; kb < kb_per_split; kb++) {
                 const int st = kb % TC_STAGES, ph = (kb / TC_STAGES) & 1;
                 tc_mbar_wait(&full[st], ph);
@@ -136,17 +145,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
         for (int c0 = 0; c0 < TC_BN; c0 += 16) {
-            uint32_t v[16];
-            const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                         : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            float acc[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) acc[j] = 0.0f;
+#pragma unroll
+            for (int p = 0; p < NP; p++) {
+                uint32_t v[16];
+                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(p * TC_BN + c0);
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                             : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                               "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                             : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 16; j++) acc[j] += __uint_as_float(v[j]);
+            }
             if (row < N) {
 #pragma unroll
                 for (int j = 0; j < 16; j++)
-                    if (c0 + j < nbatch) atomicAdd(Y + (size_t)(c0 + j) * ldy + row, __uint_as_float(v[j]));
+                    if (c0 + j < nbatch) atomicAdd(Y + (size_t)(c0 + j) * ldy + row, acc[j]);
             }
         }
     }
@@ -154,7 +171,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
     __syncthreads();
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TC_BN) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(Cfg::TMEM_COLS) : "memory");
     }
 }
 
@@ -212,33 +229,45 @@ static int pick_splits(int tiles, int kblocks, int sms) {
 }
 
 static int g_tc_attr = 0;
-/* Y[b, n] += sum_k X[b, k] W[n, k];  X: bf16 [TC_BN, K] on device (rows >= nbatch are zero or ignored), W: bf16 [N, K] */
-int qtc_gemm_tc(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K) {
-    if (K % TC_BK || nbatch < 1 || nbatch > TC_BN) { qtc_set_error("gemm_tc: K %% 64 != 0 or batch outside 1..64 (K=%d, batch=%d)", K, nbatch); return -1; }
-    if (!g_tc_attr) { QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM)); g_tc_attr = 1; }
-    const CUtensorMap *mw = cached_map(W, N, K, TC_BM), *mx = cached_map(X, TC_BN, K, TC_BN);
+/* Y[b, n] += sum_k X[b, k] W[n, k];  X: bf16 [64 x pieces, K] on device (piece p of utterance b in row 64 p + b; rows of
+ * absent utterances zero or ignored), W: bf16 [N, K].  pieces = 1 or 3. */
+int qtc_gemm_tc(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K, int pieces) {
+    if (K % TC_BK || nbatch < 1 || nbatch > TC_BN || (pieces != 1 && pieces != 3)) {
+        qtc_set_error("gemm_tc: K %% 64 != 0, batch outside 1..64 or pieces not 1/3 (K=%d, batch=%d, pieces=%d)", K, nbatch, pieces); return -1;
+    }
+    if (!g_tc_attr) {
+        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1>::SMEM));
+        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM));
+        g_tc_attr = 1;
+    }
+    const CUtensorMap *mw = cached_map(W, N, K, TC_BM), *mx = cached_map(X, TC_BN * pieces, K, TC_BN * pieces);
     if (!mw || !mx) return -1;
     const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = pick_splits(tiles, kblocks, c->num_sms);
-    k_gemm_tc<<<dim3(tiles, splits), TC_THREADS, TC_SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch);
+    if (pieces == 1) k_gemm_tc<1><<<dim3(tiles, splits), TC_THREADS, TcCfg<1>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch);
+    else k_gemm_tc<3><<<dim3(tiles, splits), TC_THREADS, TcCfg<3>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch);
     c->launches++;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { qtc_set_error("gemm_tc launch -> %s", cudaGetErrorString(e)); return -1; }
     return 0;
 }
 
-/* fp32 [rows, cols] -> bf16 (round to nearest even) [rows_pad, cols], rows >= rows zero filled */
-__global__ void k_to_bf16_rows(uint16_t *out, const float *in, int rows, int rows_pad, int cols) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, n = (size_t)rows_pad * cols;
+/* fp32 [rows, cols] -> bf16 pieces [pieces x 64, cols]: piece p of row r at row 64 p + r; absent rows zero.
+ * pieces = 1: round to nearest even; 3: exact split v = hi + mid + lo */
+__global__ void k_to_bf16_rows(uint16_t *out, const float *in, int rows, int cols, int pieces) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, n = (size_t)TC_BN * cols;
     if (i >= n) return;
     const size_t r = i / cols;
-    uint32_t v = 0;
-    if (r < (size_t)rows) { const uint32_t u = __float_as_uint(in[i]); v = (u + 0x7fffu + ((u >> 16) & 1u)) >> 16; }
-    out[i] = (uint16_t)v;
+    float v = r < (size_t)rows ? in[i] : 0.0f;
+    for (int p = 0; p < pieces; p++) {
+        const uint32_t u = __float_as_uint(v), h = (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;
+        out[(size_t)p * n + i] = (uint16_t)h;
+        v -= __uint_as_float(h << 16);
+    }
 }
 
 /* test surface: C[M, N] = A[M, K] (fp32, rounded to bf16) . W[N, K]^T (bf16), host pointers, M <= 64 */
-extern "C" int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16_t *W, int M, int N, int K) {
-    if (!C || !A || !W || M < 1 || M > TC_BN || N < 1 || K < TC_BK || K % TC_BK) { qtc_set_error("gemm_bf16_tc: bad shape"); return -1; }
+extern "C" int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16_t *W, int M, int N, int K, int pieces) {
+    if (!C || !A || !W || M < 1 || M > TC_BN || N < 1 || K < TC_BK || K % TC_BK || (pieces != 1 && pieces != 3)) { qtc_set_error("gemm_bf16_tc: bad shape"); return -1; }
     qtc_ctx tmp;                                   /* only stream / num_sms / launches are used */
     memset((void *)&tmp, 0, offsetof(qtc_ctx, allocs));
     int dev = 0;
@@ -246,13 +275,13 @@ extern "C" int qwen_tts_cuda_gemm_bf16_tc(float *C, const float *A, const uint16
     QTC_CUDA(cudaDeviceGetAttribute(&tmp.num_sms, cudaDevAttrMultiProcessorCount, dev));
     float *dA = NULL, *dC = NULL; uint16_t *dW = NULL, *dX = NULL;
     QTC_CUDA(cudaMalloc(&dA, (size_t)M * K * 4)); QTC_CUDA(cudaMalloc(&dC, (size_t)M * N * 4));
-    QTC_CUDA(cudaMalloc(&dW, (size_t)N * K * 2)); QTC_CUDA(cudaMalloc(&dX, (size_t)TC_BN * K * 2));
+    QTC_CUDA(cudaMalloc(&dW, (size_t)N * K * 2)); QTC_CUDA(cudaMalloc(&dX, (size_t)TC_BN * pieces * K * 2));
     QTC_CUDA(cudaMemcpy(dA, A, (size_t)M * K * 4, cudaMemcpyHostToDevice));
     QTC_CUDA(cudaMemcpy(dW, W, (size_t)N * K * 2, cudaMemcpyHostToDevice));
     QTC_CUDA(cudaMemset(dC, 0, (size_t)M * N * 4));
     const size_t n = (size_t)TC_BN * K;
-    k_to_bf16_rows<<<(unsigned)((n + 255) / 256), 256>>>(dX, dA, M, TC_BN, K);
-    int rc = qtc_gemm_tc(&tmp, dC, N, dX, dW, M, N, K);
+    k_to_bf16_rows<<<(unsigned)((n + 255) / 256), 256>>>(dX, dA, M, K, pieces);
+    int rc = qtc_gemm_tc(&tmp, dC, N, dX, dW, M, N, K, pieces);
     if (rc == 0 && cudaDeviceSynchronize() != cudaSuccess) { qtc_set_error("gemm_bf16_tc: %s", cudaGetErrorString(cudaGetLastError())); rc = -1; }
     if (rc == 0) QTC_CUDA(cudaMemcpy(C, dC, (size_t)M * N * 4, cudaMemcpyDeviceToHost));
     qtc_gemm_tc_forget(dW); qtc_gemm_tc_forget(dX);

@@ -278,6 +278,32 @@ static int lookup(const char *name, int n, const char *const *names, const int *
     return -1;
 }
 
+/* c/qwen_tts.c:1147-1243 on device: prefill rows (3 role tokens, codec prefix + tts_pad/tts_bos, first text token + codec_bos),
+ * trailing text rows (+ tts_eos) and the tts_pad row.  pre needs plen + 3 rows (two scratch rows follow the prompt).
+ * spk / lang: codec ids or -1. */
+int qtc_build_prompt_dev(qtc_ctx *c, const int *tok, int ntok, int spk, int lang, float *pre, int *plen_out, float *trailing, int *ntr_out, float *pad) {
+    const qtc_model_desc_t *m = &c->host;
+    int prefix[8], np = 0;
+    if (lang < 0) { prefix[np++] = m->codec_nothink_id; prefix[np++] = m->codec_think_bos_id; prefix[np++] = m->codec_think_eos_id; }
+    else { prefix[np++] = m->codec_think_id; prefix[np++] = m->codec_think_bos_id; prefix[np++] = lang; prefix[np++] = m->codec_think_eos_id; }
+    if (spk >= 0) prefix[np++] = spk;
+    prefix[np++] = m->codec_pad_id; prefix[np++] = m->codec_bos_id;
+    const int H = c->H, plen = 3 + np;
+    int ntr = (ntok - 4 - 5) + 1;
+    if (ntr < 1) ntr = 1;
+    float *bos = pre + (size_t)plen * H, *scratch = pre + (size_t)(plen + 1) * H;
+    for (int i = 0; i < 3; i++) if (embed_text_dev(c, tok[i], pre + (size_t)i * H)) return -1;
+    if (embed_text_dev(c, m->tts_pad_id, pad) || embed_text_dev(c, m->tts_bos_id, bos)) return -1;
+    for (int i = 0; i < np - 1; i++)
+        if (qtc_add_row(c, pre + (size_t)(3 + i) * H, i < np - 2 ? pad : bos, c->codec_embedding, prefix[i], H)) return -1;
+    if (embed_text_dev(c, tok[3], scratch)) return -1;
+    if (qtc_add_row(c, pre + (size_t)(3 + np - 1) * H, scratch, c->codec_embedding, m->codec_bos_id, H)) return -1;
+    for (int i = 0; i < ntr - 1; i++) if (embed_text_dev(c, tok[4 + i], trailing + (size_t)i * H)) return -1;
+    if (embed_text_dev(c, m->tts_eos_id, trailing + (size_t)(ntr - 1) * H)) return -1;
+    *plen_out = plen; *ntr_out = ntr;
+    return 0;
+}
+
 extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const char *speaker, const char *language,
                                          int *out_samples, int *out_codes, int max_codes, int *out_n_frames) {
     if (!c || !out_samples) return NULL;
@@ -310,29 +336,16 @@ extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const c
         lang = lookup(language, m->n_languages, m->language_names, m->language_ids);
         if (lang < 0) fprintf(stderr, "Warning: language '%s' not found\n", language);
     }
-    int prefix[8], np = 0;
-    if (lang < 0) { prefix[np++] = m->codec_nothink_id; prefix[np++] = m->codec_think_bos_id; prefix[np++] = m->codec_think_eos_id; }
-    else { prefix[np++] = m->codec_think_id; prefix[np++] = m->codec_think_bos_id; prefix[np++] = lang; prefix[np++] = m->codec_think_eos_id; }
-    if (spk >= 0) prefix[np++] = spk;
-    prefix[np++] = m->codec_pad_id; prefix[np++] = m->codec_bos_id;
-    const int H = c->H, plen = 3 + np;
     cudaEventRecord(c->ev2, c->stream);
+    const int plen_max = 3 + 7;
     int ntr = ((int)tok.size() - 4 - 5) + 1;
     if (ntr < 1) ntr = 1;
-
     /* the prompt is assembled in HBM; nothing crosses the bus except the token ids */
     const float *old_tr = c->trailing;
-    if (ensure_cap(&c->prefill, &c->prefill_cap, plen + 3, H) || ensure_cap(&c->trailing, &c->trailing_cap, ntr, H)) return NULL;
+    if (ensure_cap(&c->prefill, &c->prefill_cap, plen_max + 3, c->H) || ensure_cap(&c->trailing, &c->trailing_cap, ntr, c->H)) return NULL;
     if (old_tr != c->trailing) c->graph_key = -1;
-    float *pre = c->prefill, *pad = c->tts_pad, *bos = c->prefill + (size_t)plen * H, *scratch = c->prefill + (size_t)(plen + 1) * H;
-    for (int i = 0; i < 3; i++) if (embed_text_dev(c, tok[i], pre + (size_t)i * H)) return NULL;
-    if (embed_text_dev(c, m->tts_pad_id, pad) || embed_text_dev(c, m->tts_bos_id, bos)) return NULL;
-    for (int i = 0; i < np - 1; i++)
-        if (qtc_add_row(c, pre + (size_t)(3 + i) * H, i < np - 2 ? pad : bos, c->codec_embedding, prefix[i], H)) return NULL;
-    if (embed_text_dev(c, tok[3], scratch)) return NULL;
-    if (qtc_add_row(c, pre + (size_t)(3 + np - 1) * H, scratch, c->codec_embedding, m->codec_bos_id, H)) return NULL;
-    for (int i = 0; i < ntr - 1; i++) if (embed_text_dev(c, tok[4 + i], c->trailing + (size_t)i * H)) return NULL;
-    if (embed_text_dev(c, m->tts_eos_id, c->trailing + (size_t)(ntr - 1) * H)) return NULL;
+    int plen = 0;
+    if (qtc_build_prompt_dev(c, tok.data(), (int)tok.size(), spk, lang, c->prefill, &plen, c->trailing, &ntr, c->tts_pad)) return NULL;
 
     const int fixed = c->params.fixed_codec_tokens > 0 ? c->params.fixed_codec_tokens : 0;
     const int limit = fixed > 0 ? fixed : c->params.max_new_tokens;

@@ -74,6 +74,7 @@ struct LmBuffers {
 };
 
 struct CodecDev;   /* qtc_codec.cu */
+struct BatchBuf;   /* qtc_batch.cu */
 
 struct qtc_ctx {
     qtc_model_desc_t host;        /* dims + host pointers as given (pointers not used after upload) */
@@ -129,6 +130,8 @@ struct qtc_ctx {
     cudaGraphExec_t g_front, g_talker;
     int graph_key;
     int max_batch;
+    BatchBuf *bb;                 /* lock-step batch state (qtc_batch.cu), allocated on first use */
+    int batch_pieces;             /* activation pieces of the batched GEMMs: 3 (exact split, default) or 1 (bf16) */
 };
 
 /* ---- launchers implemented in qtc_lm.cu (all enqueue on ctx->stream) ------- */
@@ -148,6 +151,9 @@ int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code
 int qtc_sample_talker(qtc_ctx *c);
 int qtc_frame_front(qtc_ctx *c);    /* sample + sub-talker + next embedding, device resident */
 int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit);
+int qtc_build_prompt_dev(qtc_ctx *c, const int *tok, int ntok, int spk, int lang, float *pre, int *plen_out, float *trailing, int *ntr_out, float *pad);
+void qtc_batch_release(qtc_ctx *c);
+void qtc_gemm_tc_forget(const void *ptr);
 void *qtc_dmalloc(qtc_ctx *c, size_t bytes);
 template <class T> T *qtc_upload(qtc_ctx *c, const T *host, size_t n);
 

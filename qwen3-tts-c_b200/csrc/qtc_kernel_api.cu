@@ -269,13 +269,3 @@ extern "C" double qwen_tts_cuda_bench_subtalker(qtc_ctx_t *c, int iters, int do_
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return total / iters;
 }
-
-/* request-sharded batch (BASELINE configs 4-5): B independent utterances on this GPU, decoded one after
- * another through the batch-1 path.  The tcgen05 lock-step path replaces this loop. */
-extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *token_ids, const int *offsets, const int *speaker_ids,
-                                            const int *language_ids, int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens) {
-    (void)c; (void)batch; (void)token_ids; (void)offsets; (void)speaker_ids; (void)language_ids; (void)out_codes; (void)out_n_frames;
-    (void)pcm_out; (void)max_tokens;
-    qtc_set_error("generate_batch: not built yet");
-    return -1;
-}

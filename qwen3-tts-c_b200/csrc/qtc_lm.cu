@@ -468,3 +468,5 @@ int qtc_sample_bare(qtc_ctx *c, const float *logits_dev, int vocab, int top_k, f
     LAUNCH_CHECK(c);
     return 0;
 }
+
+#include "qtc_batch.cuh"

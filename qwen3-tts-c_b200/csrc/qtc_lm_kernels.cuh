@@ -210,10 +210,17 @@ struct NextEmbedArgs {
     const float *trailing, *tts_pad;
     GenState *st;
     int H, G;
+    /* batched launch (blockIdx.y = utterance): strides between utterances, 0 for one utterance */
+    int bs_fc, bs_codes, bs_tr;
 };
 /* c/qwen_tts.c:1345-1363: zero + talker row + sub rows (g ascending) + text row; one chain per element,
  * the same order in both arithmetic modes.  Also advances step (n_generated). */
-__global__ void k_next_embed(const NextEmbedArgs a) {
+__global__ void k_next_embed(const NextEmbedArgs a0) {
+    NextEmbedArgs a = a0;
+    {
+        const size_t b = blockIdx.y;
+        a.out += b * a.H; a.frame_codes += b * a.bs_fc; a.all_codes += b * a.bs_codes; a.trailing += b * a.bs_tr; a.st += b;
+    }
     if (a.st->done) return;
     const int step = a.st->step;                 /* index of the frame just produced */
     const int *codes = a.frame_codes;
@@ -226,7 +233,8 @@ __global__ void k_next_embed(const NextEmbedArgs a) {
     }
 }
 /* separate 1-thread kernel so every CTA of k_next_embed saw the same step */
-__global__ void k_advance_step(GenState *st) {
+__global__ void k_advance_step(GenState *st0) {
+    GenState *st = st0 + blockIdx.x;
     if (st->done) return;
     st->step += 1;
     if (st->step >= st->limit) { st->done = 2; st->stop_step = st->limit; }

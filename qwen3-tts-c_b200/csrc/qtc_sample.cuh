@@ -288,16 +288,30 @@ struct SampleArgs {
     int role;              /* 0 talker frame decision, 1 sub-talker / bare sample */
     uint32_t seed_bits; int reseed;   /* sub-talker: re-seed before sampling (first code group of a frame) */
     float *scratch_f; int *scratch_i;
+    /* batched launch (grid = utterances): element strides between utterances; all 0 for a single utterance */
+    int bs_logits, bs_rng, bs_hist, bs_out, bs_codes, bs_scratch;
+    const uint32_t *seed_tab;   /* batched re-seed: seed bits per utterance (NULL: seed_bits for all) */
 };
 
-/* dynamic smem: 2*V floats */
-__global__ void __launch_bounds__(SAMPLE_THREADS) k_sample(const SampleArgs a) {
+/* dynamic smem: 2*V floats.  blockIdx.x = utterance */
+__global__ void __launch_bounds__(SAMPLE_THREADS) k_sample(const SampleArgs a0) {
     extern __shared__ __align__(16) float dyn[];
     __shared__ SampleSmem S;
+    SampleArgs a = a0;
+    {
+        const size_t b = blockIdx.x;
+        a.logits += b * a.bs_logits;
+        if (a.rng) a.rng += b * a.bs_rng;
+        if (a.hist_count) a.hist_count += b * a.bs_hist;
+        if (a.out_token) a.out_token += b * a.bs_out;
+        if (a.codes) a.codes += b * a.bs_codes;
+        if (a.st) a.st += b;
+        if (a.scratch_f) { a.scratch_f += b * a.bs_scratch; a.scratch_i += b * a.bs_scratch; }
+    }
     const int V = a.cfg.vocab, tid = threadIdx.x;
     float *lg = dyn, *vv = dyn + V;
     if (a.role == 0 && a.st->done) return;
-    if (a.reseed && tid == 0) *a.rng = a.seed_bits;
+    if (a.reseed && tid == 0) *a.rng = a.seed_tab ? a.seed_tab[blockIdx.x] : a.seed_bits;
     for (int i = tid; i < V; i += blockDim.x) {
         float l = a.logits[i];
         if (a.cfg.suppress_from >= 0 && i >= a.cfg.suppress_from && i != a.cfg.eos_id) l = -1e9f;

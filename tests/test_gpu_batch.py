@@ -15,17 +15,131 @@ def _bf16_round(a):
     return (u.astype(np.uint32) << 16).view(np.float32), u.astype(np.uint16)
 
 
+@pytest.mark.parametrize("pieces", [1, 3])
 @pytest.mark.parametrize("M,N,K", [(64, 4096, 2048), (5, 300, 128), (64, 2048, 6144), (17, 3072, 1024), (1, 128, 64)])
-def test_gemm_tc_matches_numpy(cuda, M, N, K):
+def test_gemm_tc_matches_numpy(cuda, M, N, K, pieces):
     """C[M,N] = bf16(A)[M,K] . W[N,K]^T on the tcgen05 path (TMA + UMMA + TMEM epilogue, split-K reductions in L2)"""
     rng = np.random.default_rng(M * 1000 + N + K)
     A = rng.standard_normal((M, K)).astype(np.float32)
     Wf, Wb = _bf16_round(rng.standard_normal((N, K)).astype(np.float32) * 0.05)
     Ar, _ = _bf16_round(A)
-    want = Ar.astype(np.float64) @ Wf.astype(np.float64).T
+    want = (Ar if pieces == 1 else A).astype(np.float64) @ Wf.astype(np.float64).T
     got = np.zeros((M, N), dtype=np.float32)
-    cuda.qwen_tts_cuda_gemm_bf16_tc.argtypes = [B.f32p, B.f32p, C.POINTER(C.c_uint16), C.c_int, C.c_int, C.c_int]
-    rc = cuda.qwen_tts_cuda_gemm_bf16_tc(B.fptr(got), B.fptr(A), Wb.ctypes.data_as(C.POINTER(C.c_uint16)), M, N, K)
+    cuda.qwen_tts_cuda_gemm_bf16_tc.argtypes = [B.f32p, B.f32p, C.POINTER(C.c_uint16), C.c_int, C.c_int, C.c_int, C.c_int]
+    rc = cuda.qwen_tts_cuda_gemm_bf16_tc(B.fptr(got), B.fptr(A), Wb.ctypes.data_as(C.POINTER(C.c_uint16)), M, N, K, pieces)
     assert rc == 0, cuda.qwen_tts_cuda_last_error()
     err = np.abs(got - want).max() / np.abs(want).max()
     assert err <= 2e-5, err          # products are exact in fp32; only the accumulation order differs
+
+
+# ---------------------------------------------------------------- batched stage API vs the oracle
+from conftest import FIXTURE_TOKENS, get_model  # noqa: E402
+
+
+def _setup_batch_api(cuda):
+    cuda.qwen_tts_cuda_batch_reset.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    cuda.qwen_tts_cuda_batch_forward.argtypes = [C.c_void_p, C.c_int, B.f32p, B.f32p, B.f32p]
+    cuda.qwen_tts_cuda_batch_subtalker.argtypes = [C.c_void_p, C.c_int, B.f32p, B.i32p, B.i32p]
+    cuda.qwen_tts_cuda_set_batch_pieces.argtypes = [C.c_void_p, C.c_int]
+    cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+
+
+@pytest.mark.parametrize("pieces,tol", [(3, 2e-4), (1, 1e-2)])
+def test_batch_talker_steps_vs_oracle(cuda, orc, pieces, tol):
+    """5 utterances with different inputs take 40 lock-step decode steps; each row's logits and hidden state against
+    its own oracle context (talker logits within 1e-2 relative in bf16 - north_star; ~1e-5 with the exact split)"""
+    _setup_batch_api(cuda)
+    hm = get_model(orc, "small")
+    H, V = hm.spec["talker"]["hidden"], hm.spec["talker"]["vocab"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 8)
+    assert ctx, cuda.qwen_tts_cuda_last_error()
+    nb, steps = 5, 40
+    assert cuda.qwen_tts_cuda_set_batch_pieces(ctx, pieces) == 0
+    assert cuda.qwen_tts_cuda_batch_reset(ctx, nb, steps + 4) == 0, cuda.qwen_tts_cuda_last_error()
+    rng = np.random.default_rng(7)
+    emb = (rng.standard_normal((steps, nb, H)) * 0.5).astype(np.float32)
+    states = [orc.orc_create(hm.desc) for _ in range(nb)]
+    for s in states:
+        orc.orc_reset(s)
+    worst = worst_h = 0.0
+    for t in range(steps):
+        got, hid = np.zeros((nb, V), dtype=np.float32), np.zeros((nb, H), dtype=np.float32)
+        assert cuda.qwen_tts_cuda_batch_forward(ctx, nb, B.fptr(np.ascontiguousarray(emb[t])), B.fptr(got), B.fptr(hid)) == 0, cuda.qwen_tts_cuda_last_error()
+        for b, s in enumerate(states):
+            want = np.zeros(V, dtype=np.float32)
+            orc.orc_talker_forward(s, B.fptr(np.ascontiguousarray(emb[t, b])), B.fptr(want))
+            wh = np.ctypeslib.as_array(orc.orc_hidden(s), shape=(H,))
+            worst = max(worst, float(np.abs(got[b] - want).max() / np.abs(want).max()))
+            worst_h = max(worst_h, float(np.abs(hid[b] - wh).max() / np.abs(wh).max()))
+            if pieces == 3:
+                assert int(got[b].argmax()) == int(want.argmax()), (t, b)
+    assert worst <= tol and worst_h <= tol, (worst, worst_h)
+    for s in states:
+        orc.orc_destroy(s)
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def test_batch_subtalker_codes_equal_oracle(cuda, orc, tiny):
+    """the 15-codebook loop for 4 utterances at once, default sampling, seeds 42 + b: codes equal the oracle's"""
+    _setup_batch_api(cuda)
+    H, G = tiny.spec["talker"]["hidden"], tiny.spec["groups"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 4)
+    assert ctx
+    nb = 4
+    p = B.default_params()
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
+    assert cuda.qwen_tts_cuda_batch_reset(ctx, nb, 32) == 0, cuda.qwen_tts_cuda_last_error()
+    rng = np.random.default_rng(3)
+    hidden = rng.standard_normal((nb, H)).astype(np.float32)
+    first = np.array([5, 900, 2047, 17], dtype=np.int32)
+    got = np.zeros((nb, G), dtype=np.int32)
+    assert cuda.qwen_tts_cuda_batch_subtalker(ctx, nb, B.fptr(hidden), B.iptr(first), B.iptr(got)) == 0, cuda.qwen_tts_cuda_last_error()
+    for b in range(nb):
+        s = orc.orc_create(tiny.desc)
+        pb = B.default_params(sample_seed=42 + b)
+        orc.orc_set_params(s, C.byref(pb))
+        want = np.zeros(32, dtype=np.int32)
+        orc.orc_subtalker_generate(s, B.fptr(np.ascontiguousarray(hidden[b])), int(first[b]), B.iptr(want))
+        orc.orc_destroy(s)
+        assert np.array_equal(got[b], want[:G]), (b, got[b], want[:G])
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def test_generate_batch_equals_per_utterance_oracle(cuda, orc, tiny):
+    """whole utterances: 3 prompts of different lengths, speakers and languages, default sampling, 6 frames; codes of
+    utterance b equal the oracle's run with seed 42 + b, waveform SNR >= 80 dB"""
+    _setup_batch_api(cuda)
+    G = tiny.spec["groups"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 4)
+    assert ctx
+    frames = 6
+    p = B.default_params(fixed_codec_tokens=frames)
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
+    base = list(FIXTURE_TOKENS)
+    prompts = [base, base[:4] + [2500, 31, 77] + base[4:], base[:9] + base[10:]]
+    spk = np.array([mg.SPEAKERS["aiden"], -1, mg.SPEAKERS["vivian"]], dtype=np.int32)
+    lang = np.array([mg.LANGUAGES["english"], mg.LANGUAGES["chinese"], -1], dtype=np.int32)
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    nb = len(prompts)
+    codes = np.zeros((nb, frames, G), dtype=np.int32)
+    nfr = np.zeros(nb, dtype=np.int32)
+    pcm = np.zeros((nb, frames * 1920), dtype=np.float32)
+    rc = cuda.qwen_tts_cuda_generate_batch(ctx, nb, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), B.fptr(pcm), frames)
+    assert rc == 0, cuda.qwen_tts_cuda_last_error()
+    assert list(nfr) == [frames] * nb
+    for b in range(nb):
+        s = orc.orc_create(tiny.desc)
+        pb = B.default_params(fixed_codec_tokens=frames, sample_seed=42 + b)
+        orc.orc_set_params(s, C.byref(pb))
+        want = np.zeros((frames, G), dtype=np.int32)
+        ns, nf = C.c_int(0), C.c_int(0)
+        tk = np.array(prompts[b], dtype=np.int32)
+        ptr = orc.orc_generate(s, B.iptr(tk), len(tk), int(spk[b]), int(lang[b]), C.byref(ns), B.iptr(want), frames, C.byref(nf))
+        want_pcm = B.take_floats(orc.orc_free, ptr, ns.value)
+        orc.orc_destroy(s)
+        assert np.array_equal(codes[b], want), (b, codes[b], want)
+        err = ((pcm[b].astype(np.float64) - want_pcm) ** 2).sum()
+        snr = 10 * np.log10((want_pcm.astype(np.float64) ** 2).sum() / max(err, 1e-300))
+        assert snr >= 80.0, (b, snr)
+    cuda.qwen_tts_cuda_release(ctx)
