@@ -30,7 +30,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "qwen3-tts-c_b200"))
-from harness import binding as B, modelgen as mg  # noqa: E402
+from harness import binding as B, modelgen as mg, shard  # noqa: E402
 
 TOKENS = [151644, 77091, 198, 2354, 2244, 2355, 4041, 2244, 11752, 13, 151645, 198, 151644, 77091, 198]
 CSV = ",".join(str(t) for t in TOKENS).encode()
@@ -38,6 +38,15 @@ FRAMES = 360
 FRAME_S = 1920 / 24000.0
 REF_FRAMES = 2          # frames per reference step: ~2.7 s of single-thread GEMV work per frame on the 1.7B shapes
 METRIC = "audio-sec generated/sec (RTF), 1.7B-CustomVoice batch 1, 360 frames"
+
+
+def ncu_traffic(mode):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one talker-step launch, from the committed ncu --set full capture"""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        return json.load(open(p)).get(f"talker_step_mode{mode}")
+    except Exception:
+        return None
 
 
 def peaks():
@@ -205,6 +214,79 @@ def cpu_baseline_sample(hm, orc, spec, main, frames=1):
     return frames * FRAME_S / dt, dt
 
 
+def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
+    """configs 4-5: `--batch` utterances per GPU decoded in lock-step (tcgen05 GEMM path), fixed frame budget, codes only
+    (the codec decode of each utterance is the batch-1 decoder and is timed by the default line)"""
+    nb, frames, G = args.batch, args.frames, spec["groups"]
+    cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+    cuda.qwen_tts_cuda_set_batch_pieces.argtypes = [C.c_void_p, C.c_int]
+    assert cuda.qwen_tts_cuda_set_batch_pieces(ctx, args.pieces) == 0
+    p = B.default_params(fixed_codec_tokens=frames, sample_seed=1000 * rank + 42)
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
+    rng = np.random.default_rng(rank)
+    prompts = []
+    for b in range(nb):                       # fixture prompt with a random-length run of text ids in the middle
+        extra = [int(x) for x in rng.integers(1000, 5000, size=int(rng.integers(0, 24)))]
+        prompts.append(TOKENS[:4] + extra + TOKENS[4:])
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    spk = np.full(nb, mg.SPEAKERS["aiden"], dtype=np.int32)
+    lang = np.full(nb, mg.LANGUAGES["english"], dtype=np.int32)
+    codes = np.zeros((nb, frames, G), dtype=np.int32)
+    nfr = np.zeros(nb, dtype=np.int32)
+    perf = B.Perf()
+
+    def one():
+        t0 = time.perf_counter()
+        rc = cuda.qwen_tts_cuda_generate_batch(ctx, nb, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), None, frames)
+        wall = time.perf_counter() - t0
+        if rc != 0 or int(nfr.min()) != frames:
+            raise RuntimeError("generate_batch failed: " + cuda.qwen_tts_cuda_last_error().decode())
+        cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+        return wall, perf.device_ms / 1e3, perf.talker_ms / 1e3
+
+    for _ in range(args.warmup):
+        one()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    l0 = perf.kernel_launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    devs, loops = [], []
+    for _ in range(args.steps):
+        w, dv, lp = one()
+        devs.append(dv); loops.append(lp)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall_total, dev_total = time.perf_counter() - t0, sum(devs)
+    sampler.stop_flag = True
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=f"cuda:{local}")
+    if rank == 0:
+        audio_s = world * args.steps * nb * frames * FRAME_S
+        hbm, which = peaks()
+        ms_frame = sum(loops) / (args.steps * frames) * 1e3
+        step_bytes = cuda.qwen_tts_cuda_talker_step_bytes(ctx, 10 + frames // 2) + cuda.qwen_tts_cuda_subtalker_frame_bytes(ctx)
+        ach = step_bytes / (ms_frame * 1e-3) / 1e9
+        print(json.dumps({
+            "metric": "audio-sec generated/sec, 1.7B-CustomVoice lock-step batch", "value": audio_s / dev_total, "unit": "audio_s/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall_total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16 x bf16 -> f32 (tcgen05), activations as %d bf16 piece(s)" % args.pieces, "data": "synthetic",
+            "config": {"workload": f"{args.model} CustomVoice shapes, {nb} utterances per GPU in lock-step, {frames} frames each, default sampling, "
+                                   "ragged prompts, codes only (no codec decode)", "batch": nb, "pieces": args.pieces},
+            "ms_per_frame": ms_frame, "e2e": {"value": audio_s / wall_total, "unit": "audio_s/s", "h2d_bytes_per_step": int(toks.nbytes + offs.nbytes),
+                                              "d2h_bytes_per_step": int(codes.nbytes)},
+            "gpu_launches": int(perf.kernel_launches - l0),
+            "roofline": {"bound": "hbm", "kernel": "one frame = talker step + 16 sub-talker steps, weights streamed once per step for the whole batch",
+                         "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": which,
+                         "bytes_per_frame": step_bytes},
+            "clocks": sampler.summary()}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -216,6 +298,8 @@ def main():
     ap.add_argument("--mode", type=int, default=1, help="1: fused persistent decode kernels (default); 0: one kernel per op")
     ap.add_argument("--strict", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
+    ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")
+    ap.add_argument("--pieces", type=int, default=3, help="batched GEMM activations: 3 = exact bf16 split, 1 = bf16")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -241,6 +325,12 @@ def main():
     cuda.qwen_tts_cuda_set_mode(ctx, args.mode)
     cuda.qwen_tts_cuda_set_arith(ctx, args.strict)
     frames = args.frames
+    if args.batch > 0:
+        run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch)
+        cuda.qwen_tts_cuda_release(ctx)
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     p = B.default_params(fixed_codec_tokens=frames, sample_seed=42 + rank)     # every rank: its own utterance
     cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
     G = spec["groups"]
@@ -284,10 +374,7 @@ def main():
     launches = perf.kernel_launches - launches0
 
     dev_total, wall_total = sum(devs), t_all
-    if dist is not None:
-        t = torch.tensor([dev_total, wall_total], device=f"cuda:{local}", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_total, wall_total = t.tolist()
+    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=f"cuda:{local}")   # slowest rank
     audio_s = world * args.steps * frames * FRAME_S
     value, e2e = audio_s / dev_total, audio_s / wall_total
 
@@ -311,7 +398,7 @@ def main():
                 "e2e": {"value": e2e, "unit": "audio_s/s", "h2d_bytes_per_step": len(CSV), "d2h_bytes_per_step": pcm_bytes + frames * G * 4},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "talker decode step (all kernels of one step)", "achieved": ach, "peak": hbm, "unit": "GB/s",
-                             "frac": ach / hbm, "traffic": None, "peak_source": which, "bytes_per_step": step_bytes, "ms_per_talker_step": step_ms,
+                             "frac": ach / hbm, "traffic": ncu_traffic(args.mode), "peak_source": which, "bytes_per_step": step_bytes, "ms_per_talker_step": step_ms,
                              "subtalker": {"ms_per_frame": sub_ms, "streamed_bytes": sub_bytes, "achieved": sub_bytes / (sub_ms * 1e-3) / 1e9,
                                            "frac": sub_bytes / (sub_ms * 1e-3) / 1e9 / hbm}},
                 "clocks": sampler.summary()}
