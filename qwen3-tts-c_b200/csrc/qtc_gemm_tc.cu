@@ -83,9 +83,13 @@ __device__ __forceinline__ void tc_commit(uint64_t *bar) {
 }
 
 /* grid (row tiles, K splits).  Y [batch, ldy] fp32, pre-initialised; rows >= N and batch columns >= nbatch are dropped */
-template <int NP>
+/* EPI 0: Y += acc (fp32 reductions in L2, any K split).
+ * EPI 1 (one K split only): the weight rows are gate/up interleaved (row 2u = gate u, 2u+1 = up u); the epilogue forms
+ *        silu(gate.x) * (up.x) (c/qwen_tts_kernels.c:229-232) and stores it as bf16 pieces - the next GEMM's input - at
+ *        xo[(p*64 + b) * (N/2) + u]: SwiGLU costs no kernel and no fp32 round trip. */
+template <int NP, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapX,
-                                                            float *Y, int N, int ldy, int kb_per_split, int nbatch) {
+                                                            float *Y, int N, int ldy, int kb_per_split, int nbatch, uint16_t *xo, int xo_pieces) {
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     typedef TcCfg<NP> Cfg;
     constexpr int TC_STAGES = Cfg::STAGES, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
@@ -160,10 +164,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
 #pragma unroll
                 for (int j = 0; j < 16; j++) acc[j] += __uint_as_float(v[j]);
             }
-            if (row < N) {
+            if (EPI == 0) {
+                if (row < N) {
 #pragma unroll
-                for (int j = 0; j < 16; j++)
-                    if (c0 + j < nbatch) atomicAdd(Y + (size_t)(c0 + j) * ldy + row, acc[j]);
+                    for (int j = 0; j < 16; j++)
+                        if (c0 + j < nbatch) atomicAdd(Y + (size_t)(c0 + j) * ldy + row, acc[j]);
+                }
+            } else {
+                const int I = N >> 1, u = row >> 1;
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    const float up = __shfl_xor_sync(0xffffffffu, acc[j], 1);       /* odd lane = the up row of my unit */
+                    if (!(lane & 1) && row < N && c0 + j < nbatch) {
+                        float v = (acc[j] / (1.0f + __expf(-acc[j]))) * up;
+                        for (int p = 0; p < xo_pieces; p++) {
+                            const uint32_t bits = __float_as_uint(v), h = (bits + 0x7fffu + ((bits >> 16) & 1u)) >> 16;
+                            xo[((size_t)p * TC_BN + (c0 + j)) * I + u] = (uint16_t)h;
+                            v -= __uint_as_float(h << 16);
+                        }
+                    }
+                }
             }
         }
     }
@@ -231,20 +251,34 @@ static int pick_splits(int tiles, int kblocks, int sms) {
 static int g_tc_attr = 0;
 /* Y[b, n] += sum_k X[b, k] W[n, k];  X: bf16 [64 x pieces, K] on device (piece p of utterance b in row 64 p + b; rows of
  * absent utterances zero or ignored), W: bf16 [N, K].  pieces = 1 or 3. */
+int qtc_gemm_tc_ex(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K, int pieces, uint16_t *swiglu_out);
 int qtc_gemm_tc(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K, int pieces) {
+    return qtc_gemm_tc_ex(c, Y, ldy, X, W, nbatch, N, K, pieces, NULL);
+}
+/* swiglu_out != NULL: W is gate/up interleaved [N = 2I, K]; the result goes to swiglu_out as bf16 pieces [pieces*64, I] (Y unused) */
+int qtc_gemm_tc_ex(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K, int pieces, uint16_t *swiglu_out) {
     if (K % TC_BK || nbatch < 1 || nbatch > TC_BN || (pieces != 1 && pieces != 3)) {
         qtc_set_error("gemm_tc: K %% 64 != 0, batch outside 1..64 or pieces not 1/3 (K=%d, batch=%d, pieces=%d)", K, nbatch, pieces); return -1;
     }
     if (!g_tc_attr) {
-        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1>::SMEM));
-        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM));
+        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1>::SMEM));
+        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM));
+        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1>::SMEM));
+        QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM));
         g_tc_attr = 1;
     }
     const CUtensorMap *mw = cached_map(W, N, K, TC_BM), *mx = cached_map(X, TC_BN * pieces, K, TC_BN * pieces);
     if (!mw || !mx) return -1;
-    const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = pick_splits(tiles, kblocks, c->num_sms);
-    if (pieces == 1) k_gemm_tc<1><<<dim3(tiles, splits), TC_THREADS, TcCfg<1>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch);
-    else k_gemm_tc<3><<<dim3(tiles, splits), TC_THREADS, TcCfg<3>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch);
+    const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = swiglu_out ? 1 : pick_splits(tiles, kblocks, c->num_sms);
+    if (swiglu_out && (N & 1)) { qtc_set_error("gemm_tc: interleaved gate/up needs an even row count"); return -1; }
+    const dim3 grid(tiles, splits);
+    if (swiglu_out) {
+        if (pieces == 1) k_gemm_tc<1, 1><<<grid, TC_THREADS, TcCfg<1>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
+        else k_gemm_tc<3, 1><<<grid, TC_THREADS, TcCfg<3>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
+    } else {
+        if (pieces == 1) k_gemm_tc<1, 0><<<grid, TC_THREADS, TcCfg<1>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch, NULL, 0);
+        else k_gemm_tc<3, 0><<<grid, TC_THREADS, TcCfg<3>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch, NULL, 0);
+    }
     c->launches++;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { qtc_set_error("gemm_tc launch -> %s", cudaGetErrorString(e)); return -1; }
