@@ -14,13 +14,14 @@
 
 struct AttPlan { int S, h, sp, g, t0, t1, active, staged, cap; };
 
-__device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, int ncta, int cap = ATT_STAGE_MAX) {
+/* land_words > 0 (mode 3): the partial records of all heads must fit a landing zone of that many 8-byte words */
+__device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, int ncta, int cap = ATT_STAGE_MAX, int land_words = 0) {
     AttPlan p;
     p.cap = cap;
     const int n = pos + 1;
     p.S = (n + 31) / 32;
     if (p.S > FUSED_MAX_SPLIT) p.S = FUSED_MAX_SPLIT;
-    while (p.S > 1 && (lm.heads * p.S > ncta || lm.heads * p.S * (lm.head_dim + 4) > 2 * cap * lm.head_dim)) p.S--;
+    while (p.S > 1 && (lm.heads * p.S > ncta || lm.heads * p.S * (lm.head_dim + 4) > (land_words > 0 ? land_words : 2 * cap * lm.head_dim))) p.S--;
     p.active = cta < lm.heads * p.S;
     p.h = p.active ? cta / p.S : 0;
     p.sp = cta - p.h * p.S;

@@ -9,6 +9,7 @@
  */
 #include "qtc_fused_main.cuh"
 #include "qtc_ring_main.cuh"
+#include "qtc_ll.cuh"
 #include "qtc_gemv.cuh"
 #include "qtc_internal.h"
 #include "qtc_lm_kernels.cuh"
@@ -218,9 +219,66 @@ static int ring_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_p
     c->launches++;
     return 0;
 }
+/* mode 3: the fused step without grid barriers (qtc_ll.cuh) */
+static int g_ll_attr = 0, g_ll_max_smem = 0;
+static int ll_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
+                   const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog) {
+    if (!g_ll_attr) {
+        cudaFuncAttributes fa;
+        QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_ll));
+        g_ll_max_smem = 227 * 1024 - (int)fa.sharedSizeBytes;
+        QTC_CUDA(cudaFuncSetAttribute(k_lm_ll, cudaFuncAttributeMaxDynamicSharedMemorySize, g_ll_max_smem));
+        g_ll_attr = 1;
+    }
+    FusedArgs a;
+    memset(&a, 0, sizeof(a));
+    const int k = lm == &c->talker ? 0 : 1;
+    a.lm = k == 0 ? c->talker_dev : c->sub_dev;
+    a.x = b->x;
+    a.kc = b->k; a.vc = b->v; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
+    a.pos_ptr = pos_ptr; a.pos_add = pos_add;
+    a.head_w = head_w; a.head_rows = head_rows; a.logits = logits; a.st = st;
+    a.prof = (c->prof_sub ? lm == &c->sub : lm == &c->talker) ? c->prof : NULL; a.prof_layer = c->prof_layer;
+    { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
+    LLArgs ll;
+    ll.xa = c->ll_xa[k]; ll.xb = c->ll_xb[k]; ll.qkv = c->ll_qkv[k]; ll.g = c->ll_g[k]; ll.part = c->ll_part; ll.logits = c->ll_logits;
+    ll.epoch = c->ll_epoch; ll.err = c->ll_err;
+    const int qd = lm->heads * lm->head_dim;
+    int vec = lm->hidden > lm->inter ? lm->hidden : lm->inter;
+    if (qd > vec) vec = qd;
+    SubProg sp;
+    memset(&sp, 0, sizeof(sp));
+    if (prog) {
+        sp = *prog;
+        if (2 * sp.vocab > vec) vec = 2 * sp.vocab;
+        if (sp.Hin > vec) vec = sp.Hin;
+    }
+    int sc = (b->kv_max + c->num_sms / lm->heads - 1) / (c->num_sms / lm->heads > 0 ? c->num_sms / lm->heads : 1);
+    if (sc < 64) sc = 64;
+    const int attn = 5 * lm->head_dim + FUSED_THREADS + sc + 64 + 3 * lm->heads * FUSED_MAX_SPLIT;
+    a.xs_floats = (vec + 3) & ~3;
+    a.att_floats = (attn + 3) & ~3;
+    a.kv_floats = 2 * ATT_STAGE_MAX * lm->head_dim;
+    /* landing zone of the polled words: the widest staged vector, and as many attention splits' records as fit */
+    const size_t fixed = (size_t)(a.xs_floats + a.att_floats + a.kv_floats) * 4;
+    int need = lm->hidden > lm->inter ? lm->hidden : lm->inter;
+    if (prog && sp.vocab > need) need = sp.vocab;
+    const int rec1 = lm->heads * (lm->head_dim + 4);                 /* words of one split of every head */
+    if (rec1 > need) need = rec1;
+    if (fixed + (size_t)need * 8 > (size_t)g_ll_max_smem) { qtc_set_error("ll step: %zu bytes of shared memory needed, %d available", fixed + (size_t)need * 8, g_ll_max_smem); return -1; }
+    int words = (int)(((size_t)g_ll_max_smem - fixed) / 8);
+    if (words > rec1 * FUSED_MAX_SPLIT && rec1 * FUSED_MAX_SPLIT >= need) words = rec1 * FUSED_MAX_SPLIT;
+    a.ring_off = words & ~1;
+    const size_t smem = fixed + (size_t)a.ring_off * 8;
+    void *args[] = {&a, &sp, &ll};
+    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_ll, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
+    c->launches++;
+    return 0;
+}
 static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
                       const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog = NULL) {
     if (ring_ok(c, lm, prog)) return ring_step(c, lm, b, pos_ptr, pos_add, head_w, head_rows, logits, st, prog);
+    if (c->mode == 3 && lm->vocab % 2 == 0) return ll_step(c, lm, b, pos_ptr, pos_add, head_w, head_rows, logits, st, prog);
     if (!g_fused_attr) {
         cudaFuncAttributes fa;
         QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_fused));

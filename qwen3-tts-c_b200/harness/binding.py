@@ -232,6 +232,8 @@ def load_cuda():
     lib.qwen_tts_cuda_snake_beta.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_matmul_f32.argtypes = [f32p, f32p, f32p, C.c_int, C.c_int, C.c_int]
     lib.qwen_tts_cuda_matmul_bf16.argtypes = [f32p, f32p, u16p, C.c_int, C.c_int, C.c_int]
+    lib.qwen_tts_cuda_exchange_error.argtypes = [vp]
+    lib.qwen_tts_cuda_exchange_error.restype = C.c_int
     lib.qwen_tts_cuda_bench_talker_step.restype = C.c_double
     lib.qwen_tts_cuda_bench_talker_step.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     lib.qwen_tts_cuda_bench_subtalker.restype = C.c_double
