@@ -287,6 +287,72 @@ def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
             "clocks": sampler.summary()}))
 
 
+def run_codec(args, cuda, ctx, spec, hm, orc, rank, world, local, dist, torch):
+    """BASELINE config 3: codec decoder only, 16 codebooks x T frames -> 24 kHz PCM (qwen_tts_codec_decode, c/qwen_tts_codec.c:581-749).
+    value: audio-seconds per second, codes resident in HBM .. last codec kernel (CUDA events); e2e: host codes in, host PCM out."""
+    T, G = args.codec_frames, spec["groups"]
+    rng = np.random.default_rng(rank)
+    codes = rng.integers(0, 2048, size=(T, G), dtype=np.int32)
+    perf = B.Perf()
+
+    def one():
+        ns = C.c_int(0)
+        t0 = time.perf_counter()
+        ptr = cuda.qwen_tts_cuda_codec_decode(ctx, B.iptr(codes), T, C.byref(ns))
+        wall = time.perf_counter() - t0
+        if not ptr or ns.value != T * 1920:
+            raise RuntimeError("codec_decode failed: " + cuda.qwen_tts_cuda_last_error().decode())
+        cuda.qwen_tts_cuda_free_host(ptr)
+        cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+        return wall, perf.device_ms / 1e3
+
+    for _ in range(args.warmup):
+        one()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    l0 = perf.kernel_launches
+    sampler = ClockSampler(local)
+    sampler.start()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    devs = [one()[1] for _ in range(args.steps)]
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall_total, dev_total = time.perf_counter() - t0, sum(devs)
+    sampler.stop_flag = True
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=f"cuda:{local}")
+    if rank == 0:
+        audio_s = world * args.steps * T * FRAME_S
+        flops = 5.12e9 * T                        # SURVEY.md 8(a) a12 / 8(d): 18.44 TFLOP at T = 3600, 93 % of it in the vocoder convolutions
+        ach = flops / (dev_total / args.steps) / 1e12
+        fp32_peak = 148 * 128 * 2 * 1.965e9 / 1e12   # FFMA lanes x 2 flop x boost clock: the pipe k_conv_tile / k_sgemm_nt run on
+        line = {"metric": "audio-sec decoded/sec, codec decoder only (16 codebooks x T frames -> 24 kHz PCM)", "value": audio_s / dev_total, "unit": "audio_s/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall_total / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"Qwen3-TTS-Tokenizer-12Hz decoder shapes, {T} frames ({T * FRAME_S:.0f} s audio), codes ~ U[0,2048), random-init f32 weights",
+                           "l2": "activations (up to 2.65 GB per layer at T = 3600) exceed the 126 MB L2"},
+                "e2e": {"value": audio_s / wall_total, "unit": "audio_s/s", "h2d_bytes_per_step": int(codes.nbytes), "d2h_bytes_per_step": T * 1920 * 4},
+                "gpu_launches": int(perf.kernel_launches - l0),
+                "roofline": {"bound": "fp32-fma (direct convolutions on the FFMA pipe; not yet on tensor cores)", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
+                             "frac": ach / fp32_peak, "traffic": None, "peak_source": "nominal 148 SM x 128 FFMA x 1.965 GHz", "flop_per_step": flops},
+                "clocks": sampler.summary()}
+        if not args.no_cpu and world == 1:
+            Tc = 4
+            s = orc.orc_create(hm.desc)
+            ns = C.c_int(0)
+            t1 = time.perf_counter()
+            ptr = orc.orc_codec_decode(s, B.iptr(codes[:Tc].copy()), Tc, C.byref(ns))
+            dt = time.perf_counter() - t1
+            orc.orc_free(ptr)
+            orc.orc_destroy(s)
+            line["cpu_baseline"] = {"value": Tc * FRAME_S / dt, "unit": "audio_s/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": f"codec decode of {Tc} frames, {dt:.1f} s, oracle port with OpenMP over output channels"}
+        print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -299,6 +365,7 @@ def main():
     ap.add_argument("--strict", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
     ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")
+    ap.add_argument("--codec-frames", type=int, default=0, help="> 0: codec decoder only on this many frames (BASELINE config 3: 3600)")
     ap.add_argument("--pieces", type=int, default=3, help="batched GEMM activations: 3 = exact bf16 split, 1 = bf16")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
@@ -325,6 +392,12 @@ def main():
     cuda.qwen_tts_cuda_set_mode(ctx, args.mode)
     cuda.qwen_tts_cuda_set_arith(ctx, args.strict)
     frames = args.frames
+    if args.codec_frames > 0:
+        run_codec(args, cuda, ctx, spec, hm, orc, rank, world, local, dist, torch)
+        cuda.qwen_tts_cuda_release(ctx)
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     if args.batch > 0:
         run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch)
         cuda.qwen_tts_cuda_release(ctx)

@@ -385,5 +385,6 @@ extern "C" float *qwen_tts_cuda_codec_decode(qtc_ctx_t *c, const int *codes, int
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->perf.codec_ms = ms;
+    if (pcm) { float dms = 0; cudaEventElapsedTime(&dms, c->ev0, c->ev3); c->perf.device_ms = dms; }   /* codes H2D .. last codec kernel */
     return pcm;
 }

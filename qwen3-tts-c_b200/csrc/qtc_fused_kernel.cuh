@@ -186,6 +186,87 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
     if (tid == 0) { mine[0] = mx; mine[1] = tot; }
 }
 
+/* Short contexts (every sub-talker step: n = pos + 1 <= 32, head_dim 128, one CTA per head, rows staged): the whole head in ONE
+ * warp - lane i owns dims 4i..4i+3, q/k norm and RoPE through shuffles (the rotate-half partner of dim d is lane ^ 16), scores
+ * eight rows at a time with interleaved butterfly reductions, lane t keeps score t, V rows weighted by shuffled probabilities.
+ * No block barrier after the staged rows are visible; the step's latency chain is one L2 round trip plus ~1000 cycles. */
+__device__ __forceinline__ void cta_attention_small(const FusedArgs &a, const LmDev &lm, const AttPlan &p, int l, int pos, const float *kvs) {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    if (!p.active) return;
+    compute_sync();                                   /* the staged K/V rows were copied by every thread of the CTA */
+    if (threadIdx.x >= 32) return;
+    const int hd = 128, lane = threadIdx.x, h = p.h, g = p.g, rep = lm.heads / lm.kv_heads, kvd = lm.kv_heads * hd, n = pos + 1;
+    const LmLayerDev &w = lm.layer[l];
+    const float4 qv = __ldcg(reinterpret_cast<const float4 *>(a.q + h * hd) + lane);
+    const float4 kv = __ldcg(reinterpret_cast<const float4 *>(a.kk + g * hd) + lane);
+    const float4 v_new = __ldcg(reinterpret_cast<const float4 *>(a.vv + g * hd) + lane);
+    const float4 qn = reinterpret_cast<const float4 *>(w.q_norm)[lane], kn = reinterpret_cast<const float4 *>(w.k_norm)[lane];
+    const float4 c4 = reinterpret_cast<const float4 *>(a.cos + (size_t)pos * hd)[lane], s4 = reinterpret_cast<const float4 *>(a.sin + (size_t)pos * hd)[lane];
+    float sq = qv.x * qv.x, sk = kv.x * kv.x;
+    sq = fmaf(qv.y, qv.y, sq); sq = fmaf(qv.z, qv.z, sq); sq = fmaf(qv.w, qv.w, sq);
+    sk = fmaf(kv.y, kv.y, sk); sk = fmaf(kv.z, kv.z, sk); sk = fmaf(kv.w, kv.w, sk);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { sq += __shfl_xor_sync(0xffffffffu, sq, o); sk += __shfl_xor_sync(0xffffffffu, sk, o); }
+    const float iq = 1.0f / sqrtf(sq / (float)hd + lm.eps), ik = 1.0f / sqrtf(sk / (float)hd + lm.eps);
+    const float4 qy = make_float4(qv.x * iq * qn.x, qv.y * iq * qn.y, qv.z * iq * qn.z, qv.w * iq * qn.w);
+    const float4 ky = make_float4(kv.x * ik * kn.x, kv.y * ik * kn.y, kv.z * ik * kn.z, kv.w * ik * kn.w);
+    const float sgn = lane < 16 ? -1.0f : 1.0f;       /* first half: y*cos - partner*sin; second half: y*cos + partner*sin */
+    float4 q4, k_new;
+    {
+        const float px = __shfl_xor_sync(0xffffffffu, qy.x, 16), py = __shfl_xor_sync(0xffffffffu, qy.y, 16);
+        const float pz = __shfl_xor_sync(0xffffffffu, qy.z, 16), pw = __shfl_xor_sync(0xffffffffu, qy.w, 16);
+        q4 = lane < 16 ? make_float4(qy.x * c4.x - px * s4.x, qy.y * c4.y - py * s4.y, qy.z * c4.z - pz * s4.z, qy.w * c4.w - pw * s4.w)
+                       : make_float4(qy.x * c4.x + px * s4.x, qy.y * c4.y + py * s4.y, qy.z * c4.z + pz * s4.z, qy.w * c4.w + pw * s4.w);
+    }
+    {
+        const float px = __shfl_xor_sync(0xffffffffu, ky.x, 16), py = __shfl_xor_sync(0xffffffffu, ky.y, 16);
+        const float pz = __shfl_xor_sync(0xffffffffu, ky.z, 16), pw = __shfl_xor_sync(0xffffffffu, ky.w, 16);
+        k_new = lane < 16 ? make_float4(ky.x * c4.x - px * s4.x, ky.y * c4.y - py * s4.y, ky.z * c4.z - pz * s4.z, ky.w * c4.w - pw * s4.w)
+                          : make_float4(ky.x * c4.x + px * s4.x, ky.y * c4.y + py * s4.y, ky.z * c4.z + pz * s4.z, ky.w * c4.w + pw * s4.w);
+    }
+    (void)sgn;
+    if (h % rep == 0) {
+        float *kc = a.kc + (size_t)l * a.kv_max * kvd, *vc = a.vc + (size_t)l * a.kv_max * kvd;
+        *reinterpret_cast<float4 *>(kc + (size_t)pos * kvd + g * hd + lane * 4) = k_new;
+        *reinterpret_cast<float4 *>(vc + (size_t)pos * kvd + g * hd + lane * 4) = v_new;
+    }
+    const float *Ks = kvs, *Vs = kvs + (size_t)p.cap * hd;
+    const float scale = 1.0f / sqrtf((float)hd);
+    float sc = -3.402823466e+38f;
+    for (int t0 = 0; t0 < n; t0 += 8) {
+        float d[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int t = t0 + u;
+            float4 kr = make_float4(0, 0, 0, 0);
+            if (t < pos) kr = *reinterpret_cast<const float4 *>(Ks + (size_t)t * hd + lane * 4);
+            else if (t == pos) kr = k_new;
+            d[u] = q4.x * kr.x;
+            d[u] = fmaf(q4.y, kr.y, d[u]); d[u] = fmaf(q4.z, kr.z, d[u]); d[u] = fmaf(q4.w, kr.w, d[u]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float t8[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) t8[u] = __shfl_xor_sync(0xffffffffu, d[u], o);
+#pragma unroll
+            for (int u = 0; u < 8; u++) d[u] += t8[u];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) if (lane == t0 + u && t0 + u < n) sc = d[u] * scale;
+    }
+    const float mx = warp_max(sc);
+    const float e = lane < n ? __expf(sc - mx) : 0.0f;
+    const float tot = warp_sum(e);
+    float4 o4 = make_float4(0, 0, 0, 0);
+    for (int t = 0; t < n; t++) {
+        const float pr = __shfl_sync(0xffffffffu, e, t);
+        const float4 vr = t < pos ? *reinterpret_cast<const float4 *>(Vs + (size_t)t * hd + lane * 4) : v_new;
+        o4.x = fmaf(pr, vr.x, o4.x); o4.y = fmaf(pr, vr.y, o4.y); o4.z = fmaf(pr, vr.z, o4.z); o4.w = fmaf(pr, vr.w, o4.w);
+    }
+    *reinterpret_cast<float4 *>(a.att + h * hd + lane * 4) = make_float4(o4.x / tot, o4.y / tot, o4.z / tot, o4.w / tot);
+}
+
 /* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector.
  * The heads*S records (contiguous in HBM/L2) are copied into `land` (the KV stage, idle in this phase) with
  * cp.async - one round trip, no registers tied up - and folded from shared memory. */

@@ -150,6 +150,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
     for (int g = 0; g < nsteps; g++) {
         const int pos = pos_base + g;
         const AttPlan plan = att_plan(lm, pos, cta, ncta);
+        const bool small_att = !(a.flags & 2) && plan.S == 1 && plan.staged && lm.head_dim == 128 && pos < 32;   /* every sub-talker step */
         if (sp.G > 0) {
             /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x */
             compute_sync();
@@ -186,7 +187,8 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             grid_barrier(a.bar, target, ncta);
             PROF(3);
             /* P2: attention partials */
-            cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
+            if (small_att) cta_attention_small(a, lm, plan, l, pos, kvs);
+            else cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
             PROF(4);
             barrier_arrive(a.bar, target, ncta);
             phase_seg(a, lm, l, 1, s, cols);
