@@ -55,6 +55,7 @@ __device__ __forceinline__ void store_pieces2(uint16_t *xb, int b, int i, int K,
  * n % 4 == 0; rows up to 256 x 4 x 4 = 4096 values stay in registers between the two passes. */
 __global__ void __launch_bounds__(256) k_b_norm(uint16_t *xb, float *out_f32, const float *x, const float *w, int n, float eps, int pieces,
                                                 float *zero, int zero_n, const int *pos) {
+    pdl_enter();
     __shared__ float red[32];
     const int b = blockIdx.x, tid = threadIdx.x;
     if (zero) {
@@ -92,6 +93,7 @@ __global__ void __launch_bounds__(256) k_b_norm(uint16_t *xb, float *out_f32, co
 
 /* fp32 rows [B, n] -> bf16 pieces; optionally clears the next GEMM's output rows */
 __global__ void k_b_pieces(uint16_t *xb, const float *src, int n, int pieces, float *zero, int zero_n) {
+    pdl_enter();
     const int b = blockIdx.y;
     if (zero) for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < zero_n; i += gridDim.x * blockDim.x) zero[(size_t)b * zero_n + i] = 0.0f;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) store_pieces(xb, b, i, n, pieces, src[(size_t)b * n + i]);
@@ -99,6 +101,7 @@ __global__ void k_b_pieces(uint16_t *xb, const float *src, int n, int pieces, fl
 
 /* SwiGLU of gu [B, 2I] (gate/up interleaved: 2u, 2u+1) -> bf16 pieces [.., I] */
 __global__ void k_b_swiglu(uint16_t *xb, const float *gu, int I, int pieces) {
+    pdl_enter();
     const int b = blockIdx.y;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < I; i += gridDim.x * blockDim.x) {
         const float2 v = *reinterpret_cast<const float2 *>(gu + (size_t)b * 2 * I + 2 * i);
@@ -120,6 +123,7 @@ struct BAttnArgs {
 /* talker_attention_single steps 3-6 (c/qwen_tts_talker.c:150-225) for utterance blockIdx.y, Q head blockIdx.x.
  * dynamic smem: 2 hd + (pos + 1) floats */
 __global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
+    pdl_enter();
     extern __shared__ __align__(16) float sm[];
     __shared__ float red[32];
     const int hd = a.hd, half = hd >> 1, b = blockIdx.y, h = blockIdx.x;
@@ -179,6 +183,7 @@ __global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
 /* the same for short contexts (n = pos + 1 <= 32, head_dim <= 128: every sub-talker step): a warp per (utterance, head),
  * lane i owns dims 4i..4i+3, eight K/V rows in flight per lane, no block barrier.  grid (ceil(heads / 4), B), 128 threads */
 __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
+    pdl_enter();
     __shared__ __align__(16) float scr[4][2][128];
     const int hd = a.hd, half = hd >> 1, b = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.x * 4 + warp;
@@ -261,33 +266,39 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
 /* ---- small batched helpers --------------------------------------------------------------------------- */
 /* x[b] = prefill[b][pos[b]] while the utterance is inside its prompt window (pos[b] >= 0), else 0 */
 __global__ void k_b_fill_prefill(float *x, const float *prefill, int rows_cap, const int *pos, int H) {
+    pdl_enter();
     const int b = blockIdx.y, p = pos[b];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < H; i += gridDim.x * blockDim.x)
         x[(size_t)b * H + i] = p >= 0 ? prefill[((size_t)b * rows_cap + p) * H + i] : 0.0f;
 }
 __global__ void k_b_copy_rows(float *dst, const float *src, int n) {
+    pdl_enter();
     const int b = blockIdx.y;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[(size_t)b * n + i] = src[(size_t)b * n + i];
 }
-__global__ void k_b_pos_add(int *pos, int n, int add) { const int b = blockIdx.x * blockDim.x + threadIdx.x; if (b < n) pos[b] += add; }
+__global__ void k_b_pos_add(int *pos, int n, int add) { pdl_enter(); const int b = blockIdx.x * blockDim.x + threadIdx.x; if (b < n) pos[b] += add; }
 /* talker position of every utterance follows its GenState (captured graphs replay without host patching) */
 __global__ void k_b_bump_state_pos(GenState *st, int *pos, int n) {
+    pdl_enter();
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b < n) { if (!st[b].done) st[b].pos += 1; pos[b] = st[b].pos; }
 }
 /* sub-talker input of code group g (ST_PROJECT_INPUT, c/qwen_tts_talker.c:693-726): the talker hidden state (g = 0) or the
  * bf16 embedding row of the previous code -> fp32 rows [B, Hin] */
 __global__ void k_b_sub_input(float *out, const float *hidden, const uint16_t *table, const int *codes, int code_stride, int code_idx, int Hin) {
+    pdl_enter();
     const int b = blockIdx.y;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Hin; i += gridDim.x * blockDim.x)
         out[(size_t)b * Hin + i] = table ? bf16_to_f32(table[(size_t)codes[(size_t)b * code_stride + code_idx] * Hin + i]) : hidden[(size_t)b * Hin + i];
 }
 /* y[b, i] = bias[i] (or 0): initial value of a GEMM output that accumulates */
 __global__ void k_b_init_rows(float *y, const float *bias, int n) {
+    pdl_enter();
     const int b = blockIdx.y;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) y[(size_t)b * n + i] = bias ? bias[i] : 0.0f;
 }
 __global__ void k_b_copy_pad_rows(float *dst, const float *src, int n_in, int n_out) {
+    pdl_enter();
     const int b = blockIdx.y;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_out; i += gridDim.x * blockDim.x) dst[(size_t)b * n_out + i] = i < n_in ? src[(size_t)b * n_in + i] : 0.0f;
 }
@@ -430,7 +441,7 @@ static int b_lm_step(qtc_ctx *c, BatchBuf *bb, const LmDev *lm, BStack *s, const
     const size_t kv_stride = (size_t)lm->layers * s->kv_max * kvd;
     for (int l = 0; l < lm->layers; l++) {
         const LmLayerDev *w = &lm->layer[l];
-        k_b_norm<<<B, 256, 0, c->stream>>>(bb->xb, NULL, s->x, w->in_norm, H, lm->eps, np, s->qkv, ldq, pos);
+        qtc_launch_pdl(c->stream, k_b_norm, dim3(B), dim3(256), 0, bb->xb, (float *)NULL, s->x, w->in_norm, H, lm->eps, np, s->qkv, ldq, pos);
         BLAUNCH(c);
         if (qtc_gemm_tc(c, s->qkv, ldq, bb->xb, s->wqkv[l], B, ldq, H, np)) return -1;
         BAttnArgs a;
@@ -438,24 +449,24 @@ static int b_lm_step(qtc_ctx *c, BatchBuf *bb, const LmDev *lm, BStack *s, const
         a.kc = s->kc + (size_t)l * s->kv_max * kvd; a.vc = s->vc + (size_t)l * s->kv_max * kvd; a.kv_stride = kv_stride;
         a.xb = bb->xb; a.pos = pos; a.pos_add = pos_add; a.heads = lm->heads; a.kv_heads = lm->kv_heads; a.hd = hd; a.pieces = np;
         a.eps = lm->eps; a.scale = 1.0f / sqrtf((float)hd);
-        if (!pos && pos_add + 1 <= 32 && hd <= 128 && hd % 4 == 0) k_b_attn_small<<<dim3((lm->heads + 3) / 4, B), 128, 0, c->stream>>>(a);
-        else k_b_attn<<<dim3(lm->heads, B), 128, (size_t)(2 * hd + s->kv_max + 32) * 4, c->stream>>>(a);
+        if (!pos && pos_add + 1 <= 32 && hd <= 128 && hd % 4 == 0) qtc_launch_pdl(c->stream, k_b_attn_small, dim3(dim3((lm->heads + 3) / 4, B)), dim3(128), 0, a);
+        else qtc_launch_pdl(c->stream, k_b_attn, dim3(dim3(lm->heads, B)), dim3(128), (size_t)(2 * hd + s->kv_max + 32) * 4, a);
         BLAUNCH(c);
         if (qtc_gemm_tc(c, s->x, H, bb->xb, w->wo, B, H, qd, np)) return -1;                      /* x += Wo . att */
         static int epi = -1;
         if (epi < 0) { const char *e = getenv("QTC_BATCH_SWIGLU_EPI"); epi = e ? atoi(e) : 0; }   /* measured: split-K + kernel 7.6 ms/frame, epilogue 9.7 (B = 64, 1.7B) */
-        k_b_norm<<<B, 256, 0, c->stream>>>(bb->xb, NULL, s->x, w->post_norm, H, lm->eps, np, epi ? NULL : s->gu, 2 * I, pos);
+        qtc_launch_pdl(c->stream, k_b_norm, dim3(B), dim3(256), 0, bb->xb, (float *)NULL, s->x, w->post_norm, H, lm->eps, np, epi ? (float *)NULL : s->gu, 2 * I, pos);
         BLAUNCH(c);
         if (epi) {
             if (qtc_gemm_tc_ex(c, NULL, 0, bb->xb, s->wgu[l], B, 2 * I, H, np, s->xh)) return -1; /* gate/up + SwiGLU in the epilogue */
         } else {
             if (qtc_gemm_tc(c, s->gu, 2 * I, bb->xb, s->wgu[l], B, 2 * I, H, np)) return -1;      /* split-K, then SwiGLU as a kernel */
-            k_b_swiglu<<<dim3((I + 255) / 256, B), 256, 0, c->stream>>>(s->xh, s->gu, I, np);
+            qtc_launch_pdl(c->stream, k_b_swiglu, dim3(dim3((I + 255) / 256, B)), dim3(256), 0, s->xh, s->gu, I, np);
             BLAUNCH(c);
         }
         if (qtc_gemm_tc(c, s->x, H, s->xh, w->down, B, H, I, np)) return -1;                      /* x += Wdown . h */
     }
-    k_b_norm<<<B, 256, 0, c->stream>>>(bb->xb, hidden_out, s->x, lm->final_norm, H, lm->eps, np, head_w ? s->logits : NULL, head_rows, pos);
+    qtc_launch_pdl(c->stream, k_b_norm, dim3(B), dim3(256), 0, bb->xb, hidden_out, s->x, lm->final_norm, H, lm->eps, np, head_w ? s->logits : (float *)NULL, head_rows, pos);
     BLAUNCH(c);
     if (head_w && qtc_gemm_tc(c, s->logits, head_rows, bb->xb, head_w, B, head_rows, H, np)) return -1;
     return 0;
@@ -464,10 +475,10 @@ static int b_lm_step(qtc_ctx *c, BatchBuf *bb, const LmDev *lm, BStack *s, const
 /* qwen_tts_talker_forward for every utterance: embeds [B,H] (device) -> hidden, logits; positions advance */
 static int b_talker_forward(qtc_ctx *c, BatchBuf *bb, int B, const float *embeds_dev, int with_head) {
     const int H = c->H;
-    k_b_copy_rows<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->tk.x, embeds_dev, H);
+    qtc_launch_pdl(c->stream, k_b_copy_rows, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, bb->tk.x, embeds_dev, H);
     BLAUNCH(c);
     if (b_lm_step(c, bb, &c->talker, &bb->tk, &c->tk, B, bb->pos, 0, bb->hidden, with_head ? c->codec_head : NULL, c->talker.vocab)) return -1;
-    k_b_pos_add<<<(B + 63) / 64, 64, 0, c->stream>>>(bb->pos, B, 1);
+    qtc_launch_pdl(c->stream, k_b_pos_add, dim3((B + 63) / 64), dim3(64), 0, bb->pos, B, 1);
     BLAUNCH(c);
     return 0;
 }
@@ -490,23 +501,23 @@ static int b_subtalker(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_tab
     if (set_smem_attrs()) return -1;
     for (int g = 0; g < G; g++) {
         const uint16_t *table = g == 0 ? NULL : (g == 1 ? c->codec_embedding : c->sub_emb[g - 2]);
-        k_b_sub_input<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->sub_in, bb->hidden, table, bb->frame_codes, G, g > 0 ? g - 1 : 0, H);
+        qtc_launch_pdl(c->stream, k_b_sub_input, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, bb->sub_in, bb->hidden, table, bb->frame_codes, G, g > 0 ? g - 1 : 0, H);
         BLAUNCH(c);
         if (c->sub_in_w) {
-            k_b_pieces<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->xb, bb->sub_in, H, np, NULL, 0);
+            qtc_launch_pdl(c->stream, k_b_pieces, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, bb->xb, bb->sub_in, H, np, (float *)NULL, 0);
             BLAUNCH(c);
-            k_b_init_rows<<<dim3((h + 255) / 256, B), 256, 0, c->stream>>>(bb->st.x, c->sub_in_b, h);
+            qtc_launch_pdl(c->stream, k_b_init_rows, dim3(dim3((h + 255) / 256, B)), dim3(256), 0, bb->st.x, c->sub_in_b, h);
             BLAUNCH(c);
             if (qtc_gemm_tc(c, bb->st.x, h, bb->xb, c->sub_in_w, B, h, H, np)) return -1;
         } else {
-            k_b_copy_pad_rows<<<dim3((h + 255) / 256, B), 256, 0, c->stream>>>(bb->st.x, bb->sub_in, H < h ? H : h, h);
+            qtc_launch_pdl(c->stream, k_b_copy_pad_rows, dim3(dim3((h + 255) / 256, B)), dim3(256), 0, bb->st.x, bb->sub_in, H < h ? H : h, h);
             BLAUNCH(c);
         }
         if (b_lm_step(c, bb, lm, &bb->st, &c->st, B, NULL, g, NULL, g >= 1 ? c->sub_head[g - 1] : NULL, lm->vocab)) return -1;
         if (g >= 1) {
             SampleArgs a;
             b_sub_sample_args(c, bb, &a, g, seed_tab);
-            k_sample<<<B, SAMPLE_THREADS, (size_t)a.cfg.vocab * 8, c->stream>>>(a);
+            qtc_launch_pdl(c->stream, k_sample, dim3(B), dim3(SAMPLE_THREADS), (size_t)a.cfg.vocab * 8, a);
             BLAUNCH(c);
         }
     }
@@ -526,7 +537,7 @@ static int b_frame_front(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_t
     a.hist_count = bb->hist; a.bs_hist = lm->vocab; a.st = bb->state; a.codes = bb->frame_codes; a.bs_codes = G; a.G = G; a.role = 0;
     a.scratch_f = bb->scratch_f; a.scratch_i = bb->scratch_i; a.bs_scratch = lm->vocab > c->sub.vocab ? lm->vocab : c->sub.vocab;
     if (set_smem_attrs()) return -1;
-    k_sample<<<B, SAMPLE_THREADS, (size_t)lm->vocab * 8, c->stream>>>(a);
+    qtc_launch_pdl(c->stream, k_sample, dim3(B), dim3(SAMPLE_THREADS), (size_t)lm->vocab * 8, a);
     BLAUNCH(c);
     if (b_subtalker(c, bb, B, seed_tab)) return -1;
     NextEmbedArgs n;
@@ -535,9 +546,9 @@ static int b_frame_front(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_t
     for (int g = 0; g < G - 1; g++) n.sub_emb[g] = c->sub_emb[g];
     n.frame_codes = bb->frame_codes; n.bs_fc = G; n.all_codes = bb->codes; n.bs_codes = bb->codes_cap * G;
     n.trailing = bb->trailing; n.bs_tr = bb->trailing_cap * H; n.tts_pad = c->tts_pad; n.st = bb->state; n.H = H; n.G = G;
-    k_next_embed<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(n);
+    qtc_launch_pdl(c->stream, k_next_embed, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, n);
     BLAUNCH(c);
-    k_advance_step<<<B, 1, 0, c->stream>>>(bb->state);
+    qtc_launch_pdl(c->stream, k_advance_step, dim3(B), dim3(1), 0, bb->state);
     BLAUNCH(c);
     return 0;
 }
@@ -620,11 +631,11 @@ extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *
     QTC_CUDA(cudaStreamSynchronize(c->stream));      /* pos0 / seeds are stack vectors */
     /* lock-step prefill: per token the reference's batched prefill does a decode step's arithmetic */
     for (int s = 0; s < maxlen; s++) {
-        k_b_fill_prefill<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->tk.x, bb->prefill, bb->prefill_cap, bb->pos, H);
+        qtc_launch_pdl(c->stream, k_b_fill_prefill, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, bb->tk.x, bb->prefill, bb->prefill_cap, bb->pos, H);
         BLAUNCH(c);
         const int last = s + 1 == maxlen;
         if (b_lm_step(c, bb, &c->talker, &bb->tk, &c->tk, B, bb->pos, 0, bb->hidden, last ? c->codec_head : NULL, c->talker.vocab)) return -1;
-        k_b_pos_add<<<(B + 63) / 64, 64, 0, c->stream>>>(bb->pos, B, 1);
+        qtc_launch_pdl(c->stream, k_b_pos_add, dim3((B + 63) / 64), dim3(64), 0, bb->pos, B, 1);
         BLAUNCH(c);
     }
     const int key = b_params_key(c, B);

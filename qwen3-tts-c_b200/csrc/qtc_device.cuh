@@ -30,6 +30,14 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
     return r;
 }
 
+/* programmatic dependent launch (batched path): every kernel of a captured frame starts with pdl_enter() - the next kernel may
+ * be scheduled as soon as all CTAs of this one are resident (its launch latency and prologue overlap this kernel's run), and
+ * nothing of this kernel's own work happens before the previous kernel has completed and flushed.  Without the launch
+ * attribute both instructions are no-ops. */
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -15,6 +15,7 @@
  * Warp roles: 0 TMA producer, 1 MMA issuer (+ TMEM alloc/free), 2..5 epilogue (TMEM lane quarter = warp % 4).
  */
 #include "qtc_internal.h"
+#include "qtc_device.cuh"
 
 #include <cuda.h>
 #include <unordered_map>
@@ -115,9 +116,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = tmem_base_s;
 
+    /* programmatic dependent launch: everything above ran while the previous kernel was still finishing; the weights do not
+     * depend on it either, so the producer fills the pipeline's weight tiles BEFORE it waits - only the activation tiles and
+     * the accumulation into Y are ordered after the previous kernel. */
+    pdl_trigger();
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < kb_per_split; kb++) {
+            const int npre = kb_per_split < TC_STAGES ? kb_per_split : TC_STAGES;
+            for (int kb = 0; kb < npre; kb++) {
+                unsigned char *sa = tiles + (size_t)kb * TC_STAGE_BYTES;
+                tc_mbar_expect_tx(&full[kb], TC_STAGE_BYTES);
+                tc_tma_2d(sa, &mapW, (kb0 + kb) * TC_BK, row0, &full[kb]);
+            }
+            pdl_wait();
+            for (int kb = 0; kb < npre; kb++) {
+                unsigned char *sb = tiles + (size_t)kb * TC_STAGE_BYTES + TC_A_BYTES;
+                tc_tma_2d(sb, &mapX, (kb0 + kb) * TC_BK, 0, &full[kb]);
+            }
+            for (int kb = npre; kb < kb_per_split; kb++) {
                 const int st = kb % TC_STAGES, ph = (kb / TC_STAGES) & 1;
                 tc_mbar_wait(&empty[st], ph ^ 1);
                 unsigned char *sa = tiles + (size_t)st * TC_STAGE_BYTES, *sb = sa + TC_A_BYTES;
@@ -127,6 +143,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
             }
         }
     } else if (warp == 1) {
+        pdl_wait();
         if (lane == 0) {
             const uint32_t idesc = tc_idesc(Cfg::N);
             for (int kb = 0; kb < kb_per_split; kb++) {
@@ -145,6 +162,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
     } else {
         /* epilogue: warp w may touch TMEM lanes [32 (w % 4), +32); thread = one weight row, 64 batch columns */
         const int q = warp & 3, row = row0 + q * 32 + lane;
+        pdl_wait();
         tc_mbar_wait(&acc_full, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
@@ -273,11 +291,11 @@ int qtc_gemm_tc_ex(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint1
     if (swiglu_out && (N & 1)) { qtc_set_error("gemm_tc: interleaved gate/up needs an even row count"); return -1; }
     const dim3 grid(tiles, splits);
     if (swiglu_out) {
-        if (pieces == 1) k_gemm_tc<1, 1><<<grid, TC_THREADS, TcCfg<1>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
-        else k_gemm_tc<3, 1><<<grid, TC_THREADS, TcCfg<3>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
+        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
+        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
     } else {
-        if (pieces == 1) k_gemm_tc<1, 0><<<grid, TC_THREADS, TcCfg<1>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch, NULL, 0);
-        else k_gemm_tc<3, 0><<<grid, TC_THREADS, TcCfg<3>::SMEM, c->stream>>>(*mw, *mx, Y, N, ldy, kblocks / splits, nbatch, NULL, 0);
+        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 0>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0);
+        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 0>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0);
     }
     c->launches++;
     const cudaError_t e = cudaGetLastError();

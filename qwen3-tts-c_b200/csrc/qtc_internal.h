@@ -31,6 +31,24 @@ void qtc_set_error(const char *fmt, ...);
         }                                                                                      \
     } while (0)
 
+/* launch with the programmatic-stream-serialization attribute (kernels that begin with pdl_enter(), qtc_device.cuh);
+ * QTC_PDL=0 in the environment launches them the plain way */
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+static inline cudaError_t qtc_launch_pdl(cudaStream_t st, void (*k)(KArgs...), dim3 g, dim3 b, size_t smem, Args &&...args) {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("QTC_PDL"); on = e ? atoi(e) : 1; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = g; cfg.blockDim = b; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    memset(at, 0, sizeof(at));
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = on ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, k, static_cast<KArgs>(args)...);
+}
+#endif
+
 /* ---- device-side descriptors (plain structs, passed by value or by pointer) - */
 struct LmLayerDev {
     const uint16_t *wq, *wk, *wv, *wo, *gate, *up, *down;   /* bf16, row-major as in the reference */

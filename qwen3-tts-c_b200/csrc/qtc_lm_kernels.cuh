@@ -216,6 +216,7 @@ struct NextEmbedArgs {
 /* c/qwen_tts.c:1345-1363: zero + talker row + sub rows (g ascending) + text row; one chain per element,
  * the same order in both arithmetic modes.  Also advances step (n_generated). */
 __global__ void k_next_embed(const NextEmbedArgs a0) {
+    pdl_enter();
     NextEmbedArgs a = a0;
     {
         const size_t b = blockIdx.y;
@@ -234,6 +235,7 @@ __global__ void k_next_embed(const NextEmbedArgs a0) {
 }
 /* separate 1-thread kernel so every CTA of k_next_embed saw the same step */
 __global__ void k_advance_step(GenState *st0) {
+    pdl_enter();
     GenState *st = st0 + blockIdx.x;
     if (st->done) return;
     st->step += 1;

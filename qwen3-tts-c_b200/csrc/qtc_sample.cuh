@@ -295,6 +295,7 @@ struct SampleArgs {
 
 /* dynamic smem: 2*V floats.  blockIdx.x = utterance */
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample(const SampleArgs a0) {
+    pdl_enter();
     extern __shared__ __align__(16) float dyn[];
     __shared__ SampleSmem S;
     SampleArgs a = a0;
