@@ -365,12 +365,16 @@ def main():
     ap.add_argument("--strict", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
     ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")
+    ap.add_argument("--greedy", action="store_true", help="greedy decoding (BASELINE config 1: --model 0.6b --frames 74 --greedy)")
     ap.add_argument("--codec-frames", type=int, default=0, help="> 0: codec decoder only on this many frames (BASELINE config 3: 3600)")
     ap.add_argument("--pieces", type=int, default=3, help="batched GEMM activations: 3 = exact bf16 split, 1 = bf16")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
+        # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is rank 0 alone and is entitled to every host
+        # thread (its convolutions are OpenMP loops), so undo that before libgomp is loaded
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
         run_reference(args, rank, world)
         return
 
@@ -404,7 +408,7 @@ def main():
         if dist is not None:
             dist.destroy_process_group()
         return
-    p = B.default_params(fixed_codec_tokens=frames, sample_seed=42 + rank)     # every rank: its own utterance
+    p = (B.greedy_params if args.greedy else B.default_params)(fixed_codec_tokens=frames, sample_seed=42 + rank)     # every rank: its own utterance
     cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
     G = spec["groups"]
     codes = np.zeros((frames, G), dtype=np.int32)
@@ -460,11 +464,13 @@ def main():
         step_bytes = cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos)
         sub_bytes = cuda.qwen_tts_cuda_subtalker_frame_bytes(ctx)
         ach = step_bytes / (step_ms * 1e-3) / 1e9
-        line = {"metric": METRIC, "value": value, "unit": "audio_s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        metric = METRIC if (args.model == "1.7b" and frames == FRAMES and not args.greedy) else \
+            f"audio-sec generated/sec (RTF), {args.model}-CustomVoice batch 1, {frames} frames{', greedy' if args.greedy else ''}"
+        line = {"metric": metric, "value": value, "unit": "audio_s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": wall_total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32 (bf16 weights)", "data": "synthetic",
-                "config": {"workload": f"{args.model} CustomVoice shapes, batch 1 per GPU, {frames} frames ({frames * FRAME_S:.1f} s audio), "
-                                       "default sampling (temp 0.9, top-k 50, rep-pen 1.05), random-init weights, fixed frame budget",
+                "config": {"workload": f"{args.model} CustomVoice shapes, batch 1 per GPU, {frames} frames ({frames * FRAME_S:.1f} s audio), " +
+                                       ("greedy, " if args.greedy else "default sampling (temp 0.9, top-k 50, rep-pen 1.05), ") + "random-init weights, fixed frame budget",
                            "mode": args.mode, "arith": "strict" if args.strict else "fast",
                            "l2": "weights per step (2.8 GB talker, 157 MB x16 sub-talker) exceed the 126 MB L2; the roofline probe flushes L2 between iterations"},
                 "ms_per_frame": sum(loops) / (args.steps * frames) * 1e3,

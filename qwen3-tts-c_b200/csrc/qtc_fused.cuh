@@ -255,6 +255,25 @@ __device__ __forceinline__ void prefetch_seg(const Seg3 &s, int cols, int cta, i
     }
 }
 
+/* rows [r0, r1) of one matrix -> L2, issued by the last warp in <= 32 KB bulk prefetches */
+__device__ __forceinline__ void prefetch_rows(const uint16_t *w, int r0, int r1, int cols) {
+    if ((threadIdx.x >> 5) != FUSED_WARPS - 1 || r1 <= r0) return;
+    const int lane = threadIdx.x & 31;
+    const char *p = reinterpret_cast<const char *>(w) + (size_t)r0 * cols * 2;
+    const size_t bytes = (size_t)(r1 - r0) * cols * 2;
+    for (size_t off = (size_t)lane * 32768; off < bytes; off += 32 * 32768) {
+        const size_t nb = bytes - off < 32768 ? bytes - off : 32768;
+        prefetch_l2_bulk(p + off, (unsigned)nb);
+    }
+}
+/* this CTA's gate/up units (rows u0..u1 of both matrices) -> L2 */
+__device__ __forceinline__ void prefetch_swiglu(const uint16_t *gate, const uint16_t *up, int inter, int cols, int cta, int ncta) {
+    int u0, u1;
+    row_range(inter, cta, ncta, u0, u1);
+    prefetch_rows(gate, u0, u1, cols);
+    prefetch_rows(up, u0, u1, cols);
+}
+
 /* weight phase `k` of layer `l`: 0 QKV, 1 O, 2 gate+up (as two segments of I rows), 3 down */
 __device__ __forceinline__ bool phase_seg(const FusedArgs &a, const LmDev &lm, int l, int k, Seg3 &s, int &cols) {
     if (l >= lm.layers) {

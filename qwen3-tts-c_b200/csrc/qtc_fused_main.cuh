@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
     if (tid == 0) { const unsigned long long v = ld_acquire_u64(a.bar); target = v - v % (unsigned long long)ncta; }
     const int nsteps = sp.G > 0 ? sp.G : 1;
     if (sp.G > 0 && tid == 0) s_codes[0] = sp.codes[0];
+    const bool pf_l2 = (a.flags & 4) != 0;          /* experiment: L2 prefetch of the next phases at the END of a phase */
     Seg3 s; int cols;
     WTrip tp;
     if (sp.G == 0) { phase_seg(a, lm, 0, 0, s, cols); gemv_prefetch(tp, s, cols, cta, ncta); }
@@ -183,6 +184,12 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             phase_seg(a, lm, l, 0, s, cols);
             gemv_run(tp, s, cols, sm, NULL, cta, ncta);
             att_stage_issue(a, lm, plan, l, pos, kvs);
+            if (pf_l2) {       /* HBM idles through the attention phase and its two barriers: pull O and gate/up into L2 meanwhile */
+                Seg3 s2; int c2;
+                phase_seg(a, lm, l, 1, s2, c2);
+                prefetch_seg(s2, c2, cta, ncta);
+                prefetch_swiglu(w.gate, w.up, I, H, cta, ncta);
+            }
             PROF(2);
             grid_barrier(a.bar, target, ncta);
             PROF(3);
@@ -200,6 +207,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             else stage_attention_out(sm, att_sm, kvs, a, lm, plan.S);
             PROF(15);
             gemv_run(tp, s, cols, sm, a.x, cta, ncta);
+            if (pf_l2) { Seg3 s2; int c2; phase_seg(a, lm, l, 3, s2, c2); prefetch_seg(s2, c2, cta, ncta); }      /* down */
             PROF(6);
             barrier_arrive(a.bar, target, ncta);
             swiglu_prefetch(tp, w.gate, w.up, I, H, cta, ncta);
@@ -209,6 +217,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             stage_rmsnorm(sm, a.x, w.post_norm, H, lm.eps, red);
             PROF(8);
             swiglu_run(tp, w.gate, w.up, a.g, I, H, sm, cta, ncta);
+            if (pf_l2) { Seg3 s2; int c2; if (phase_seg(a, lm, l + 1, 0, s2, c2)) prefetch_seg(s2, c2, cta, ncta); }  /* next QKV / head */
             PROF(9);
             barrier_arrive(a.bar, target, ncta);
             phase_seg(a, lm, l, 3, s, cols);
