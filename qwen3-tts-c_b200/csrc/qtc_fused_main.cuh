@@ -235,12 +235,16 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             PROF(13);
         }
 #undef PROF
-        /* final norm (every CTA, into shared memory), then x is overwritten in place with the normed hidden */
-        stage_rmsnorm(sm, a.x, lm.final_norm, H, lm.eps, red);
-        grid_barrier(a.bar, target, ncta);
-        if (cta == 0 && sp.G == 0) {          /* (inside the sub-talker loop nobody reads the hidden state back) */
-            for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = sm[i];
-            if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
+        /* final norm (every CTA, into shared memory).  Talker: x is then overwritten in place with the normed hidden (ctx->tk_x),
+         * which needs every CTA to have staged x first - one grid barrier.  Inside the sub-talker loop nobody reads the hidden
+         * state back, so there is no overwrite and no barrier; position 0 has no head either, so it skips the norm as well. */
+        if (sp.G == 0 || a.head_w) stage_rmsnorm(sm, a.x, lm.final_norm, H, lm.eps, red);
+        if (sp.G == 0) {
+            grid_barrier(a.bar, target, ncta);
+            if (cta == 0) {
+                for (int i = tid; i < H; i += FUSED_THREADS) a.x[i] = sm[i];
+                if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
+            }
         }
         if (phase_seg(a, lm, L, 0, s, cols)) gemv_run(tp, s, cols, sm, NULL, cta, ncta);
         if (sp.G > 0 && g >= 1) {

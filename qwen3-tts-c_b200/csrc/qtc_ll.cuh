@@ -39,7 +39,7 @@ struct LLArgs {
 
 __device__ __forceinline__ void ll_store(u64 *p, float v, uint32_t tag) {
     const u64 w = ((u64)tag << 32) | (u64)__float_as_uint(v);
-    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(w));       /* no "memory" clobber: the next rows' weight loads may be hoisted above it */
 }
 __device__ __forceinline__ u64 ll_load(const u64 *p) {
     u64 w;
@@ -424,7 +424,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_ll(const FusedArgs a0, co
             ll_stage_attention_out(sm, att_sm, land, ll, lm, plan.S, t2, ctl);
             PROF(15);
             const uint32_t t3 = base + (++seq);
-            if (xcur) { const u64 *xc = xcur; ll_gemv_run(tp, s, cols, sm, [xc](int r) -> float { return ll_val(ll_load(xc + r)); }, ll.xb, t3, cta, ncta); }
+            if (xcur) { const u64 *xc = xcur; ll_gemv_run(tp, s, cols, sm, [xc](int r) -> float { return __ldcg(reinterpret_cast<const float *>(xc + r)); }   /* validated when it was staged: a plain L2 read of the value half */, ll.xb, t3, cta, ncta); }
             else { const float *xp = a.x; ll_gemv_run(tp, s, cols, sm, [xp](int r) -> float { return __ldcg(xp + r); }, ll.xb, t3, cta, ncta); }
             PROF(6); PROF(7);
             /* P4: (poll xb) RMSNorm -> gate/up -> SwiGLU */
@@ -443,7 +443,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_ll(const FusedArgs a0, co
             compute_sync();
             PROF(11);
             const uint32_t t5 = base + (++seq);
-            { const u64 *xc = ll.xb; ll_gemv_run(tp, s, cols, sm, [xc](int r) -> float { return ll_val(ll_load(xc + r)); }, ll.xa, t5, cta, ncta); }
+            { const u64 *xc = ll.xb; ll_gemv_run(tp, s, cols, sm, [xc](int r) -> float { return __ldcg(reinterpret_cast<const float *>(xc + r)); }   /* validated when it was staged: a plain L2 read of the value half */, ll.xa, t5, cta, ncta); }
             xcur = ll.xa; xtag = t5;
             PROF(12); PROF(13);
             if (phase_seg(a, lm, l + 1, 0, s, cols)) gemv_prefetch(tp, s, cols, cta, ncta);   /* next layer's QKV, or the head */
