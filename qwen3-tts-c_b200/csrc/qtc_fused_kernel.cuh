@@ -15,11 +15,11 @@
 struct AttPlan { int S, h, sp, g, t0, t1, active, staged, cap; };
 
 /* land_words > 0 (mode 3): the partial records of all heads must fit a landing zone of that many 8-byte words */
-__device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, int ncta, int cap = ATT_STAGE_MAX, int land_words = 0) {
+__device__ __forceinline__ AttPlan att_plan(const LmDev &lm, int pos, int cta, int ncta, int cap = ATT_STAGE_MAX, int land_words = 0, int per = 32) {
     AttPlan p;
     p.cap = cap;
     const int n = pos + 1;
-    p.S = (n + 31) / 32;
+    p.S = (n + per - 1) / per;
     if (p.S > FUSED_MAX_SPLIT) p.S = FUSED_MAX_SPLIT;
     while (p.S > 1 && (lm.heads * p.S > ncta || lm.heads * p.S * (lm.head_dim + 4) > (land_words > 0 ? land_words : 2 * cap * lm.head_dim))) p.S--;
     p.active = cta < lm.heads * p.S;
@@ -265,6 +265,102 @@ __device__ __forceinline__ void cta_attention_small(const FusedArgs &a, const Lm
         o4.x = fmaf(pr, vr.x, o4.x); o4.y = fmaf(pr, vr.y, o4.y); o4.z = fmaf(pr, vr.z, o4.z); o4.w = fmaf(pr, vr.w, o4.w);
     }
     *reinterpret_cast<float4 *>(a.att + h * hd + lane * 4) = make_float4(o4.x / tot, o4.y / tot, o4.z / tot, o4.w / tot);
+}
+
+/* Split-KV attention with the block barriers taken out of the chain (head_dim 128, staged range of <= 64 positions): every warp
+ * norms and rotates q for itself (lane i owns dims 4i..4i+3, rotate-half partner = lane ^ 16), takes up to four positions of the
+ * CTA's range round-robin, reduces their four scores with interleaved butterflies, and keeps an un-normalised (max, sum, out)
+ * triple in registers; ONE block barrier later 128 threads fold the 16 triples into the CTA's partial record
+ * [max, sum, -, -, out[hd]] - also when the head is not split (the O projection's staging normalises).
+ * sm: [wm 16 | wl 16 | wo 16 x hd] */
+__device__ __forceinline__ void cta_attention_warps(const FusedArgs &a, const LmDev &lm, const AttPlan &p, int l, int pos, float *sm, const float *kvs) {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    if (!p.active) return;
+    compute_sync();                                   /* the staged K/V rows were copied by every thread of the CTA */
+    const int hd = 128, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int h = p.h, g = p.g, rep = lm.heads / lm.kv_heads, kvd = lm.kv_heads * hd, t0 = p.t0, t1 = p.t1;
+    const LmLayerDev &w = lm.layer[l];
+    float *wm = sm, *wl = sm + FUSED_WARPS, *wo = sm + 2 * FUSED_WARPS;
+    const bool writer = p.sp == 0 && h % rep == 0 && warp == FUSED_WARPS - 1;
+    const bool has_new = t1 == pos + 1 && ((pos - t0 - warp) % FUSED_WARPS == 0) && pos - t0 >= warp;      /* this warp's positions include t == pos */
+    const float4 c4 = reinterpret_cast<const float4 *>(a.cos + (size_t)pos * hd)[lane], s4 = reinterpret_cast<const float4 *>(a.sin + (size_t)pos * hd)[lane];
+    auto norm_rope = [&](const float *src, const float *nw) -> float4 {
+        const float4 v = __ldcg(reinterpret_cast<const float4 *>(src) + lane), n4 = reinterpret_cast<const float4 *>(nw)[lane];
+        float ss = v.x * v.x;
+        ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
+        ss = warp_sum(ss);
+        const float inv = 1.0f / sqrtf(ss / (float)hd + lm.eps);
+        const float4 y = make_float4(v.x * inv * n4.x, v.y * inv * n4.y, v.z * inv * n4.z, v.w * inv * n4.w);
+        const float px = __shfl_xor_sync(0xffffffffu, y.x, 16), py = __shfl_xor_sync(0xffffffffu, y.y, 16);
+        const float pz = __shfl_xor_sync(0xffffffffu, y.z, 16), pw = __shfl_xor_sync(0xffffffffu, y.w, 16);
+        return lane < 16 ? make_float4(y.x * c4.x - px * s4.x, y.y * c4.y - py * s4.y, y.z * c4.z - pz * s4.z, y.w * c4.w - pw * s4.w)
+                         : make_float4(y.x * c4.x + px * s4.x, y.y * c4.y + py * s4.y, y.z * c4.z + pz * s4.z, y.w * c4.w + pw * s4.w);
+    };
+    const float4 q4 = norm_rope(a.q + h * hd, w.q_norm);
+    float4 k_new = make_float4(0, 0, 0, 0), v_new = k_new;
+    if (has_new || writer) {
+        k_new = norm_rope(a.kk + g * hd, w.k_norm);
+        v_new = __ldcg(reinterpret_cast<const float4 *>(a.vv + g * hd) + lane);
+    }
+    if (writer) {
+        float *kc = a.kc + (size_t)l * a.kv_max * kvd, *vc = a.vc + (size_t)l * a.kv_max * kvd;
+        *reinterpret_cast<float4 *>(kc + (size_t)pos * kvd + g * hd + lane * 4) = k_new;
+        *reinterpret_cast<float4 *>(vc + (size_t)pos * kvd + g * hd + lane * 4) = v_new;
+    }
+    const float *Ks = kvs, *Vs = kvs + (size_t)p.cap * hd;
+    const float scale = 1.0f / sqrtf((float)hd);
+    float d[4];
+    float4 vr[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int t = t0 + warp + FUSED_WARPS * j;
+        float4 kr = make_float4(0, 0, 0, 0);
+        vr[j] = kr;
+        if (t < t1) {
+            if (t < pos) { kr = *reinterpret_cast<const float4 *>(Ks + (size_t)(t - t0) * hd + lane * 4); vr[j] = *reinterpret_cast<const float4 *>(Vs + (size_t)(t - t0) * hd + lane * 4); }
+            else { kr = k_new; vr[j] = v_new; }
+        }
+        d[j] = q4.x * kr.x;
+        d[j] = fmaf(q4.y, kr.y, d[j]); d[j] = fmaf(q4.z, kr.z, d[j]); d[j] = fmaf(q4.w, kr.w, d[j]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float t4[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) t4[j] = __shfl_xor_sync(0xffffffffu, d[j], o);
+#pragma unroll
+        for (int j = 0; j < 4; j++) d[j] += t4[j];
+    }
+    float mx = -3.402823466e+38f;
+#pragma unroll
+    for (int j = 0; j < 4; j++) if (t0 + warp + FUSED_WARPS * j < t1) { d[j] *= scale; mx = fmaxf(mx, d[j]); }
+    float tot = 0.0f;
+    float4 o4 = make_float4(0, 0, 0, 0);
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        if (t0 + warp + FUSED_WARPS * j < t1) {
+            const float e = __expf(d[j] - mx);
+            tot += e;
+            o4.x = fmaf(e, vr[j].x, o4.x); o4.y = fmaf(e, vr[j].y, o4.y); o4.z = fmaf(e, vr[j].z, o4.z); o4.w = fmaf(e, vr[j].w, o4.w);
+        }
+    if (lane == 0) { wm[warp] = mx; wl[warp] = tot; }
+    *reinterpret_cast<float4 *>(wo + warp * hd + lane * 4) = o4;
+    compute_sync();
+    if (tid < hd) {
+        float M = -3.402823466e+38f;
+#pragma unroll
+        for (int k = 0; k < FUSED_WARPS; k++) M = fmaxf(M, wm[k]);
+        float L = 0.0f, o = 0.0f;
+#pragma unroll
+        for (int k = 0; k < FUSED_WARPS; k++) {
+            const float f = wl[k] > 0.0f ? __expf(wm[k] - M) : 0.0f;
+            L = fmaf(wl[k], f, L);
+            o = fmaf(wo[k * hd + tid], f, o);
+        }
+        float *mine = a.part + ((size_t)h * p.S + p.sp) * (hd + 4);
+        mine[4 + tid] = o;
+        if (tid == 0) { mine[0] = M; mine[1] = L; }
+    }
 }
 
 /* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector.

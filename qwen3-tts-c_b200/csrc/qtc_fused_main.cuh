@@ -150,7 +150,10 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
 
     for (int g = 0; g < nsteps; g++) {
         const int pos = pos_base + g;
-        const AttPlan plan = att_plan(lm, pos, cta, ncta);
+        /* flags & 8: the older 32-position splits with block-level reductions */
+        const bool warp_att_ok = !(a.flags & 8) && lm.head_dim == 128 && a.att_floats >= 2 * FUSED_WARPS + FUSED_WARPS * 128;
+        const AttPlan plan = att_plan(lm, pos, cta, ncta, ATT_STAGE_MAX, 0, warp_att_ok ? 64 : 32);
+        const bool warp_att = warp_att_ok && plan.staged && plan.t1 - plan.t0 <= 64;
         const bool small_att = !(a.flags & 2) && plan.S == 1 && plan.staged && lm.head_dim == 128 && pos < 32;   /* every sub-talker step */
         if (sp.G > 0) {
             /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x */
@@ -195,6 +198,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             PROF(3);
             /* P2: attention partials */
             if (small_att) cta_attention_small(a, lm, plan, l, pos, kvs);
+            else if (warp_att) cta_attention_warps(a, lm, plan, l, pos, att_sm, kvs);
             else cta_attention(a, lm, plan, l, pos, att_sm, kvs, red);
             PROF(4);
             barrier_arrive(a.bar, target, ncta);
@@ -203,7 +207,7 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             barrier_wait(a.bar, target);
             PROF(5);
             /* P3: combine partials -> O projection + residual */
-            if (plan.S == 1) stage_vec(sm, a.att, lm.heads * lm.head_dim);
+            if (plan.S == 1 && (small_att || !warp_att)) stage_vec(sm, a.att, lm.heads * lm.head_dim);
             else stage_attention_out(sm, att_sm, kvs, a, lm, plan.S);
             PROF(15);
             gemv_run(tp, s, cols, sm, a.x, cta, ncta);

@@ -309,7 +309,8 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     /* score buffer: a staged chunk (<= 64) or, for long contexts, ceil(n / splits) positions */
     int sc = (b->kv_max + c->num_sms / lm->heads - 1) / (c->num_sms / lm->heads > 0 ? c->num_sms / lm->heads : 1);
     if (sc < 64) sc = 64;
-    const int attn = 2 * lm->head_dim + FUSED_THREADS + sc + 64 + 3 * lm->heads * FUSED_MAX_SPLIT;
+    int attn = 2 * lm->head_dim + FUSED_THREADS + sc + 64 + 3 * lm->heads * FUSED_MAX_SPLIT;
+    if (attn < 2 * FUSED_WARPS + FUSED_WARPS * lm->head_dim) attn = 2 * FUSED_WARPS + FUSED_WARPS * lm->head_dim;   /* cta_attention_warps: 16 (max, sum, out[hd]) triples */
     a.xs_floats = (vec + 3) & ~3;
     a.att_floats = (attn + 3) & ~3;
     const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
