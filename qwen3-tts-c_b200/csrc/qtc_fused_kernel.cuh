@@ -369,24 +369,12 @@ __device__ __forceinline__ void cta_attention_warps(const FusedArgs &a, const Lm
 __device__ __forceinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
     const int hd = lm.head_dim, heads = lm.heads, qd = heads * hd, tid = threadIdx.x, rec = hd + 4;
     const int n16 = heads * S * rec / 4;
-    if (n16 <= 4 * FUSED_THREADS) {
-        /* <= 4 x 16 bytes per thread: plain L2 loads */
-#pragma unroll
-        for (int j0 = 0; j0 < 4; j0 += 2) {           /* two at a time: the prefetched weight trip keeps 32 registers */
-            float4 v[2];
-#pragma unroll
-            for (int j = 0; j < 2; j++) { const int i = tid + FUSED_THREADS * (j0 + j); if (i < n16) v[j] = __ldcg(reinterpret_cast<const float4 *>(a.part) + i); }
-#pragma unroll
-            for (int j = 0; j < 2; j++) { const int i = tid + FUSED_THREADS * (j0 + j); if (i < n16) reinterpret_cast<float4 *>(land)[i] = v[j]; }
-        }
-    } else {
-        for (int i = tid; i < n16; i += FUSED_THREADS) {
-            const uint32_t sa = (uint32_t)__cvta_generic_to_shared(land + i * 4);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(a.part + i * 4));
-        }
-        asm volatile("cp.async.commit_group;");
-        asm volatile("cp.async.wait_all;" ::: "memory");
+    for (int i = tid; i < n16; i += FUSED_THREADS) {
+        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(land + i * 4);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(a.part + i * 4));
     }
+    asm volatile("cp.async.commit_group;");
+    asm volatile("cp.async.wait_all;" ::: "memory");
     compute_sync();
     float *fac = scr;
     for (int h = tid; h < heads; h += FUSED_THREADS) {
