@@ -132,6 +132,14 @@ __device__ __forceinline__ void barrier_wait(unsigned long long *bar, const unsi
 }
 
 __device__ __forceinline__ void row_range(int rows, int cta, int ncta, int &r0, int &r1) {
+    /* rows * (cta + 1) < 2^32 for every matrix of these models (rows < 2^24, <= 256 CTAs): 32-bit unsigned division.  The s64
+     * division subroutine (~100 instructions, 30 call sites after inlining, every warp, every phase) was ~0.5 us of pure
+     * instruction issue per phase. */
+    if (rows < (1 << 24) && ncta <= 256) {
+        r0 = (int)(((unsigned)rows * (unsigned)cta) / (unsigned)ncta);
+        r1 = (int)(((unsigned)rows * (unsigned)(cta + 1)) / (unsigned)ncta);
+        return;
+    }
     r0 = (int)(((long long)rows * cta) / ncta);
     r1 = (int)(((long long)rows * (cta + 1)) / ncta);
 }

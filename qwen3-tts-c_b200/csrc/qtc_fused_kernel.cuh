@@ -347,16 +347,14 @@ __device__ __forceinline__ void cta_attention_warps(const FusedArgs &a, const Lm
     *reinterpret_cast<float4 *>(wo + warp * hd + lane * 4) = o4;
     compute_sync();
     if (tid < hd) {
-        float M = -3.402823466e+38f;
+        /* lanes k < 16 hold the warps' (max, sum); factors by butterfly, broadcast by shuffle */
+        const float m = lane < FUSED_WARPS ? wm[lane] : -3.402823466e+38f, lw = lane < FUSED_WARPS ? wl[lane] : 0.0f;
+        const float M = warp_max(m);
+        const float f = lw > 0.0f ? __expf(m - M) : 0.0f;
+        const float L = warp_sum(lw * f);
+        float o = 0.0f;
 #pragma unroll
-        for (int k = 0; k < FUSED_WARPS; k++) M = fmaxf(M, wm[k]);
-        float L = 0.0f, o = 0.0f;
-#pragma unroll
-        for (int k = 0; k < FUSED_WARPS; k++) {
-            const float f = wl[k] > 0.0f ? __expf(wm[k] - M) : 0.0f;
-            L = fmaf(wl[k], f, L);
-            o = fmaf(wo[k * hd + tid], f, o);
-        }
+        for (int k = 0; k < FUSED_WARPS; k++) o = fmaf(wo[k * hd + tid], __shfl_sync(0xffffffffu, f, k), o);
         float *mine = a.part + ((size_t)h * p.S + p.sp) * (hd + 4);
         mine[4 + tid] = o;
         if (tid == 0) { mine[0] = M; mine[1] = L; }
@@ -366,29 +364,43 @@ __device__ __forceinline__ void cta_attention_warps(const FusedArgs &a, const Lm
 /* xs[h*hd + i] = softmax-combine of the S partials of head h: the O projection's input vector.
  * The heads*S records (contiguous in HBM/L2) are copied into `land` (the KV stage, idle in this phase) with
  * cp.async - one round trip, no registers tied up - and folded from shared memory. */
-__device__ __forceinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S) {
-    const int hd = lm.head_dim, heads = lm.heads, qd = heads * hd, tid = threadIdx.x, rec = hd + 4;
+__device__ __forceinline__ void stage_attention_out(float *xs, float *scr, float *land, const FusedArgs &a, const LmDev &lm, int S, long long *pp = NULL) {
+    const int hd = lm.head_dim, heads = lm.heads, tid = threadIdx.x, rec = hd + 4;
     const int n16 = heads * S * rec / 4;
     for (int i = tid; i < n16; i += FUSED_THREADS) {
         const uint32_t sa = (uint32_t)__cvta_generic_to_shared(land + i * 4);
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(a.part + i * 4));
     }
     asm volatile("cp.async.commit_group;");
+    if (pp) pp[20] = clock64();
     asm volatile("cp.async.wait_all;" ::: "memory");
+    if (pp) pp[21] = clock64();
     compute_sync();
-    float *fac = scr;
-    for (int h = tid; h < heads; h += FUSED_THREADS) {
-        float M = -3.402823466e+38f, L = 0.0f;
-        for (int k = 0; k < S; k++) M = fmaxf(M, land[(h * S + k) * rec]);
-        for (int k = 0; k < S; k++) L = fmaf(land[(h * S + k) * rec + 1], __expf(land[(h * S + k) * rec] - M), L);
-        for (int k = 0; k < S; k++) fac[h * FUSED_MAX_SPLIT + k] = __expf(land[(h * S + k) * rec] - M) / L;
+    if (pp) pp[22] = clock64();
+    /* a warp per head: lanes k < S hold the S (max, sum) pairs, the fold factors exp(m_k - M) / L come from two butterflies, then
+     * each lane folds its dims (lane, lane + 32, ...) with the factors broadcast by shuffle.  (The first version - 16 threads
+     * computing factors serially, then a generic per-output loop - cost 2.5 us of pure instruction issue per layer.) */
+    (void)scr;
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int h = warp; h < heads; h += FUSED_WARPS) {
+        const float *r0 = land + (size_t)h * S * rec;
+        const float m = lane < S ? r0[lane * rec] : -3.402823466e+38f, l = lane < S ? r0[lane * rec + 1] : 0.0f;
+        const float M = warp_max(m);
+        const float f = lane < S ? __expf(m - M) : 0.0f;
+        const float L = warp_sum(l * f);
+        const float fn = f / L;
+        for (int d0 = 0; d0 < hd; d0 += 128) {
+            float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            for (int k = 0; k < S; k++) {
+                const float fk = __shfl_sync(0xffffffffu, fn, k);
+                const float *ok = r0 + k * rec + 4 + d0 + lane;
+#pragma unroll
+                for (int j = 0; j < 4; j++) if (d0 + lane + 32 * j < hd) acc[j] = fmaf(ok[32 * j], fk, acc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (d0 + lane + 32 * j < hd) xs[h * hd + d0 + lane + 32 * j] = acc[j];
+        }
     }
-    compute_sync();
-    for (int i = tid; i < qd; i += FUSED_THREADS) {
-        const int h = i / hd, d = i - h * hd;
-        float acc = 0.0f;
-        for (int k = 0; k < S; k++) acc = fmaf(land[(h * S + k) * rec + 4 + d], fac[h * FUSED_MAX_SPLIT + k], acc);
-        xs[i] = acc;
-    }
+    if (pp) pp[23] = pp[24] = clock64();
     compute_sync();
 }

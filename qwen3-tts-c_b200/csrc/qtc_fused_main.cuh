@@ -203,13 +203,14 @@ __global__ void __launch_bounds__(FUSED_BLOCK, 1) k_lm_fused(const FusedArgs a0,
             PROF(4);
             barrier_arrive(a.bar, target, ncta);
             phase_seg(a, lm, l, 1, s, cols);
-            gemv_prefetch(tp, s, cols, cta, ncta);
+            if (!(a.flags & 32)) gemv_prefetch(tp, s, cols, cta, ncta);
             barrier_wait(a.bar, target);
             PROF(5);
             /* P3: combine partials -> O projection + residual */
             if (plan.S == 1 && (small_att || !warp_att)) stage_vec(sm, a.att, lm.heads * lm.head_dim);
-            else stage_attention_out(sm, att_sm, kvs, a, lm, plan.S);
+            else stage_attention_out(sm, att_sm, kvs, a, lm, plan.S, (a.prof && tid == 0 && l == a.prof_layer) ? a.prof + cta * 32 : NULL);
             PROF(15);
+            if (a.flags & 32) gemv_prefetch(tp, s, cols, cta, ncta);      /* diagnostic: O-projection trip issued after the staging */
             gemv_run(tp, s, cols, sm, a.x, cta, ncta);
             if (pf_l2) { Seg3 s2; int c2; phase_seg(a, lm, l, 3, s2, c2); prefetch_seg(s2, c2, cta, ncta); }      /* down */
             PROF(6);

@@ -4,6 +4,6 @@
 TAG=${1:-fl}; OUT=gpurun_out/$TAG; mkdir -p $OUT
 for f in ${2:-0 4}; do
   echo "=== QTC_FUSED_FLAGS=$f"
-  QTC_FUSED_FLAGS=$f QTC_MODE=1 timeout 120 python scripts/phase_profile.py 1.7b 190 5 > $OUT/phase_talker_f$f.txt 2>&1; grep -v "^\s*\[" $OUT/phase_talker_f$f.txt
+  QTC_FUSED_FLAGS=$f QTC_MODE=1 timeout 120 python scripts/phase_profile.py 1.7b 190 5 > $OUT/phase_talker_f$f.txt 2>&1; grep -v "qkv consume" $OUT/phase_talker_f$f.txt
   QTC_FUSED_FLAGS=$f QTC_MODE=1 timeout 120 python scripts/phase_profile.py 1.7b -1 2 > $OUT/phase_sub_f$f.txt 2>&1; grep -E "layer total|sub-talker frame" $OUT/phase_sub_f$f.txt
 done

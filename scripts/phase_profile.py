@@ -34,6 +34,10 @@ def main():
     for nm, a, b in (("qkv consume only", 1, 16), ("stage (P3)", 5, 15)):
         dd = (raw[:, b] - raw[:, a]) / 1.965e3
         print(f"  [{nm}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
+    if raw[:, 20].any():
+        for nm, a_, b_ in (("P3 issue cp.async", 5, 20), ("P3 wait_all", 20, 21), ("P3 sync", 21, 22), ("P3 fac", 22, 23), ("P3 sync", 23, 24), ("P3 combine+sync", 24, 15)):
+            dd = (raw[:, b_] - raw[:, a_]) / 1.965e3
+            print(f"  [{nm:18s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
     if raw[:, 17].any():
         names = {26: "before geom", 17: "consume entry", 18: "x slice loaded", 19: "quad0 loaded", 20: "quad0 mma done", 21: "quad0 released", 22: "chunk1 done",
                  23: "chunk2 full", 24: "chunk2 done", 25: "loop end", 16: "after consume", 27: "PRODUCER at qkv", 28: "PRODUCER got slot"}
