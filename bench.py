@@ -86,10 +86,16 @@ class ClockSampler(threading.Thread):
 
 
 def build_model(preset):
-    orc = B.load_oracle()
     spec = mg.PRESETS[preset]
     main, cod = mg.build_tensors(spec, seed=0)
-    return orc, spec, main, cod, B.HostModel(spec, main, cod, orc)
+    return spec, main, cod, B.HostModel(spec, main, cod)
+
+
+def load_checker():
+    """oracle/ is test infrastructure: only the CPU legs of this file (cpu_baseline, --impl reference) load it"""
+    sys.path.insert(0, ROOT)
+    from oracle import orc_binding as O
+    return O
 
 
 def run_reference(args, rank, world):
@@ -99,12 +105,14 @@ def run_reference(args, rank, world):
     frames.  Rank 0 only."""
     if rank != 0:
         return
-    if not B.have_ref():
+    O = load_checker()
+    if not O.have_ref():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libqtts_ref.so not built (no /root/reference at build time)"}))
         return
     import tempfile
-    ref = B.load_ref()
-    orc, spec, main, cod, hm = build_model(args.model)
+    ref = O.load_ref()
+    orc = O.load_oracle()
+    spec, main, cod, hm = build_model(args.model)
     d = tempfile.mkdtemp(prefix="qtts_model_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     try:
         mg.write_model_dir(d, spec, main, cod)
@@ -184,8 +192,9 @@ def run_reference(args, rank, world):
         shutil.rmtree(d, ignore_errors=True)
 
 
-def cpu_baseline_sample(hm, orc, spec, main, frames=1):
+def cpu_baseline_sample(hm, spec, main, frames=1):
     """bounded CPU sample for the default line: the oracle port (OpenMP over rows) on `frames` frames after prefill"""
+    orc = load_checker().load_oracle()
     s = orc.orc_create(hm.desc)
     p = B.default_params(fixed_codec_tokens=frames)
     orc.orc_set_params(s, C.byref(p))
@@ -289,7 +298,7 @@ def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
             "clocks": sampler.summary()}))
 
 
-def run_codec(args, cuda, ctx, spec, hm, orc, rank, world, local, dist, torch):
+def run_codec(args, cuda, ctx, spec, hm, rank, world, local, dist, torch):
     """BASELINE config 3: codec decoder only, 16 codebooks x T frames -> 24 kHz PCM (qwen_tts_codec_decode, c/qwen_tts_codec.c:581-749).
     value: audio-seconds per second, codes resident in HBM .. last codec kernel (CUDA events); e2e: host codes in, host PCM out."""
     T, G = args.codec_frames, spec["groups"]
@@ -343,6 +352,7 @@ def run_codec(args, cuda, ctx, spec, hm, orc, rank, world, local, dist, torch):
                 "clocks": sampler.summary()}
         if not args.no_cpu and world == 1:
             Tc = 4
+            orc = load_checker().load_oracle()
             s = orc.orc_create(hm.desc)
             ns = C.c_int(0)
             t1 = time.perf_counter()
@@ -391,7 +401,7 @@ def main():
     cuda = B.load_cuda()                       # raises if the extension was not built: there is no fallback
     if cuda.qwen_tts_cuda_init(local) != 0:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
-    orc, spec, main_t, cod, hm = build_model(args.model)
+    spec, main_t, cod, hm = build_model(args.model)
     ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
     if not ctx:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
@@ -399,7 +409,7 @@ def main():
     cuda.qwen_tts_cuda_set_arith(ctx, args.strict)
     frames = args.frames
     if args.codec_frames > 0:
-        run_codec(args, cuda, ctx, spec, hm, orc, rank, world, local, dist, torch)
+        run_codec(args, cuda, ctx, spec, hm, rank, world, local, dist, torch)
         cuda.qwen_tts_cuda_release(ctx)
         if dist is not None:
             dist.destroy_process_group()
@@ -484,7 +494,7 @@ def main():
                                            "frac": sub_bytes / (sub_ms * 1e-3) / 1e9 / hbm}},
                 "clocks": sampler.summary()}
         if not args.no_cpu and world == 1:
-            rtf_cpu, dt = cpu_baseline_sample(hm, orc, spec, main_t, frames=1)
+            rtf_cpu, dt = cpu_baseline_sample(hm, spec, main_t, frames=1)
             line["cpu_baseline"] = {"value": rtf_cpu, "unit": "audio_s/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": f"1 frame (sub-talker + talker step) + codec decode of it after an untimed prefill, {dt:.1f} s; "
                                               "oracle port, OpenMP over output rows (the reference's own GEMVs are single-threaded: see --impl reference)"}

@@ -77,7 +77,8 @@ float *qwen_tts_generate(qwen_tts_ctx_t *ctx, const char *text, const char *spea
     qwen_tts_cuda_set_params(g_dev, &p);
     int cap = ctx->fixed_codec_tokens > 0 ? ctx->fixed_codec_tokens : ctx->max_new_tokens;
     if (cap < 1) cap = 1;
-    const int G = ctx->config.codec_num_quantizers > 0 ? ctx->config.codec_num_quantizers : 16;
+    /* the library writes codes with stride num_code_groups (c/qwen_tts.c:1261,1339), not codec_num_quantizers */
+    const int G = ctx->config.num_code_groups > 0 ? ctx->config.num_code_groups : 16;
     int *codes = (int *)malloc((size_t)cap * G * sizeof(int));
     int n_frames = 0;
     if (out_samples) *out_samples = 0;
@@ -87,7 +88,8 @@ float *qwen_tts_generate(qwen_tts_ctx_t *ctx, const char *text, const char *spea
     ctx->perf_total_ms = pf.total_ms; ctx->perf_talker_ms = pf.talker_ms;
     ctx->perf_codec_ms = pf.codec_ms; ctx->perf_codec_tokens = pf.codec_tokens;
     if (!pcm) {
-        fprintf(stderr, "Error: %s\n", qwen_tts_cuda_last_error());
+        /* EOS at step 0 is not an error: the reference returns NULL / 0 samples silently (c/qwen_tts.c:1324-1330, 1388-1392) */
+        if (!(n_frames == 0 && pf.stop_reason == 1)) fprintf(stderr, "Error: %s\n", qwen_tts_cuda_last_error());
         free(codes);
         return NULL;
     }

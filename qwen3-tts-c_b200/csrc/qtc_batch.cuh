@@ -344,6 +344,7 @@ static void *balloc(BatchBuf *bb, size_t bytes) {
     bb->allocs.push_back(p);
     return p;
 }
+void qtc_batch_invalidate_graphs(qtc_ctx *c) { if (c->bb) c->bb->graph_key = -1; }
 void qtc_batch_release(qtc_ctx *c) {
     BatchBuf *bb = c->bb;
     if (!bb) return;
@@ -428,6 +429,9 @@ static int batch_ensure(qtc_ctx *c, int B, int kv_need, int frames, int pre_rows
     if (cudaMallocHost(&bb->state_host, (size_t)B * sizeof(GenState)) != cudaSuccess) { qtc_set_error("batch: pinned state"); return -1; }
     /* RoPE tables of both stacks must cover the positions (they are shared with the batch-1 path) */
     if (qtc_ensure_kv(c, &c->tk, &c->talker, kv_max) || qtc_ensure_kv(c, &c->st, &c->sub, G + 2)) return -1;
+    /* balloc's memsets and the weight re-layout copies ran on the legacy default stream, which c->stream (non-blocking) does
+     * not order against: nothing on c->stream may touch these buffers before they have landed */
+    QTC_CUDA(cudaDeviceSynchronize());
     return 0;
 }
 

@@ -175,6 +175,7 @@ int qtc_frame_front(qtc_ctx *c);    /* sample + sub-talker + next embedding, dev
 int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit);
 int qtc_build_prompt_dev(qtc_ctx *c, const int *tok, int ntok, int spk, int lang, float *pre, int *plen_out, float *trailing, int *ntr_out, float *pad);
 void qtc_batch_release(qtc_ctx *c);
+void qtc_batch_invalidate_graphs(qtc_ctx *c);
 void qtc_gemm_tc_forget(const void *ptr);
 void *qtc_dmalloc(qtc_ctx *c, size_t bytes);
 template <class T> T *qtc_upload(qtc_ctx *c, const T *host, size_t n);

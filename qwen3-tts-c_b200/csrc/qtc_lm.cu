@@ -129,7 +129,8 @@ int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
     QTC_CUDA(cudaMemcpy(nsn, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
     cudaFree(b->k); cudaFree(b->v); cudaFree(b->cos); cudaFree(b->sin);
     b->k = nk; b->v = nv; b->cos = ncs; b->sin = nsn; b->kv_max = nmax;
-    c->graph_key = -1;      /* pointers changed: captured graphs are stale */
+    c->graph_key = -1;      /* pointers changed: captured graphs are stale - the batched ones too (they hold cos/sin) */
+    if (c->bb) qtc_batch_invalidate_graphs(c);
     return 0;
 }
 

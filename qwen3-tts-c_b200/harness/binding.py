@@ -1,9 +1,6 @@
-"""ctypes mirror of include/qwen_tts_cuda.h plus loaders for the three shared
-libraries a test can talk to:
-
-  * libqwen_tts_cuda.so  - the product (qwen3-tts-c_b200/csrc), C ABI of include/qwen_tts_cuda.h
-  * oracle/liboracle.so  - the CPU restatement (checker only)
-  * oracle/_ref/libqtts_ref.so - the unmodified reference + shim (checker only, may be absent)
+"""ctypes mirror of include/qwen_tts_cuda.h and the loader of the product library
+(libqwen_tts_cuda.so, qwen3-tts-c_b200/csrc).  The loaders of the CPU checker live with the checker
+(oracle/orc_binding.py) and are imported only by tests/, __graft_entry__.smoke() and bench.py's CPU legs.
 
 Python is harness only: no arithmetic of the hot path happens here.
 """
@@ -16,9 +13,6 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 CUDA_LIB = os.path.join(ROOT, "qwen3-tts-c_b200", "csrc", "libqwen_tts_cuda.so")
-ORACLE_LIB = os.path.join(ROOT, "oracle", "liboracle.so")
-REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libqtts_ref.so")
-REF_CLI = os.path.join(ROOT, "oracle", "_ref", "qwen-tts")
 
 MAX_LM_LAYERS, MAX_CODEC_LAYERS, MAX_GROUPS, MAX_Q, MAX_NAMES = 32, 12, 32, 16, 64
 u16p, f32p, i32p = C.POINTER(C.c_uint16), C.POINTER(C.c_float), C.POINTER(C.c_int)
@@ -122,78 +116,6 @@ def _p(a, typ):
     return None if a is None else a.ctypes.data_as(typ)
 
 
-def load_oracle():
-    lib = C.CDLL(ORACLE_LIB)
-    lib.orc_create.restype = C.c_void_p
-    lib.orc_create.argtypes = [C.POINTER(ModelDesc)]
-    for n in ("orc_destroy", "orc_reset"):
-        getattr(lib, n).argtypes = [C.c_void_p]
-        getattr(lib, n).restype = None
-    lib.orc_set_params.argtypes = [C.c_void_p, C.POINTER(GenParams)]
-    lib.orc_talker_prefill.argtypes = [C.c_void_p, f32p, C.c_int]
-    lib.orc_talker_forward.argtypes = [C.c_void_p, f32p, f32p]
-    lib.orc_subtalker_generate.argtypes = [C.c_void_p, f32p, C.c_int, i32p]
-    lib.orc_codec_decode.restype = C.c_void_p
-    lib.orc_codec_decode.argtypes = [C.c_void_p, i32p, C.c_int, i32p]
-    lib.orc_hidden.restype = f32p
-    lib.orc_hidden.argtypes = [C.c_void_p]
-    lib.orc_kv_len.argtypes = [C.c_void_p]
-    lib.orc_head_logits.argtypes = [C.c_void_p, f32p]
-    lib.orc_embed_text_token.argtypes = [C.c_void_p, C.c_int, f32p]
-    lib.orc_generate_frames.argtypes = [C.c_void_p, f32p, C.c_int, f32p, C.c_int, f32p, i32p, C.c_int, i32p, i32p]
-    lib.orc_build_prompt.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p), i32p,
-                                     C.POINTER(C.c_void_p), i32p, C.POINTER(C.c_void_p)]
-    lib.orc_generate.restype = C.c_void_p
-    lib.orc_generate.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_int, i32p, i32p, C.c_int, i32p]
-    lib.orc_free.argtypes = [C.c_void_p]
-    lib.orc_sample.argtypes = [f32p, C.c_int, C.c_int, C.c_float, C.c_float, f32p]
-    lib.orc_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
-    lib.orc_swiglu_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
-    lib.orc_rms_norm.argtypes = [f32p, f32p, f32p, C.c_int, C.c_float]
-    lib.orc_matmul_f32.argtypes = [f32p, f32p, f32p, C.c_int, C.c_int, C.c_int]
-    lib.orc_matmul_bf16.argtypes = [f32p, f32p, u16p, C.c_int, C.c_int, C.c_int]
-    lib.orc_snake_beta.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int]
-    lib.orc_causal_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 6
-    lib.orc_transposed_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 5 + [i32p]
-    lib.orc_prep_snake.argtypes = [f32p, f32p, C.c_int]
-    lib.orc_prep_codebook.argtypes = [f32p, f32p, f32p, C.c_int, C.c_int]
-    lib.orc_repetition_penalty.argtypes = [f32p, i32p, C.c_int, C.c_int, C.c_float]
-    return lib
-
-
-def have_ref() -> bool:
-    return os.path.exists(REF_LIB)
-
-
-def load_ref():
-    lib = C.CDLL(REF_LIB)
-    lib.ref_load.restype = C.c_void_p
-    lib.ref_load.argtypes = [C.c_char_p, C.c_int]
-    lib.ref_free.argtypes = [C.c_void_p]
-    lib.ref_fill_desc.argtypes = [C.c_void_p, C.POINTER(ModelDesc)]
-    lib.ref_set_params.argtypes = [C.c_void_p, C.POINTER(GenParams)]
-    lib.ref_reset.argtypes = [C.c_void_p]
-    lib.ref_prefill.argtypes = [C.c_void_p, f32p, C.c_int]
-    lib.ref_forward.argtypes = [C.c_void_p, f32p, f32p]
-    lib.ref_subtalker.argtypes = [C.c_void_p, f32p, C.c_int, i32p]
-    lib.ref_codec_decode.restype = C.c_void_p
-    lib.ref_codec_decode.argtypes = [C.c_void_p, i32p, C.c_int, i32p]
-    lib.ref_hidden.restype = f32p
-    lib.ref_hidden.argtypes = [C.c_void_p]
-    lib.ref_kv_len.argtypes = [C.c_void_p]
-    lib.ref_generate.restype = C.c_void_p
-    lib.ref_generate.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, i32p]
-    lib.ref_perf.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
-    lib.ref_free_buf.argtypes = [C.c_void_p]
-    lib.ref_last_codes.argtypes = [i32p]
-    lib.kernel_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
-    lib.kernel_sample_top_k.argtypes = [f32p, C.c_int, C.c_int, C.c_float, C.c_float, f32p]
-    lib.kernel_causal_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 6
-    lib.kernel_transposed_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 5 + [i32p]
-    lib.kernel_snake_beta.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int]
-    return lib
-
-
 def load_cuda():
     """The product library.  Fails loudly if it was not built: there is no fallback."""
     if not os.path.exists(CUDA_LIB):
@@ -248,16 +170,43 @@ def load_cuda():
     return lib
 
 
+_LIBM = None
+
+
+def _expf(a: np.ndarray) -> np.ndarray:
+    """glibc expf, element by element: numpy's float32 exp is a different implementation and may differ in the last bit
+    from what the reference's loader computes (c/qwen_tts.c:596-602).  The SnakeBeta vectors are a few thousand elements."""
+    global _LIBM
+    if _LIBM is None:
+        _LIBM = C.CDLL("libm.so.6")
+        _LIBM.expf.restype = C.c_float
+        _LIBM.expf.argtypes = [C.c_float]
+    return np.array([_LIBM.expf(float(v)) for v in a.ravel()], dtype=np.float32).reshape(a.shape)
+
+
+def prep_codebook(embedding_sum: np.ndarray, usage: np.ndarray) -> np.ndarray:
+    """c/qwen_tts.c:577-594: E[c] = embedding_sum[c] * (1.0f / max(usage[c], 1e-5f)); IEEE fp32 ops, so numpy is bit-identical"""
+    inv = np.float32(1.0) / np.maximum(usage.astype(np.float32), np.float32(1e-5))
+    return np.ascontiguousarray(embedding_sum.astype(np.float32) * inv[:, None], dtype=np.float32)
+
+
+def prep_snake(alpha: np.ndarray, beta: np.ndarray):
+    """c/qwen_tts.c:596-602: a = expf(alpha), inv_b = 1.0f / (expf(beta) + 1e-9f)"""
+    a = _expf(alpha.astype(np.float32))
+    b = (np.float32(1.0) / (_expf(beta.astype(np.float32)) + np.float32(1e-9))).astype(np.float32)
+    return np.ascontiguousarray(a), np.ascontiguousarray(b)
+
+
 class HostModel:
     """Tensors of modelgen.build_tensors bound into a ModelDesc (keeps the arrays alive).
-    Applies the reference's load-time preprocessing through the oracle's C restatement of it
-    so values are bit-identical to a model loaded by the reference (c/qwen_tts.c:577-602)."""
+    Applies the reference's load-time preprocessing (c/qwen_tts.c:577-602) in numpy / libm, so values are bit-identical
+    to a model loaded by the reference; the checker (oracle/) is not involved (tests/test_oracle_golden.py holds the
+    two to each other)."""
 
     def __init__(self, spec, main, cod, oracle_lib=None):
         from . import modelgen as mg
         self.spec, self.keep = spec, []
         d = ModelDesc()
-        orc = oracle_lib or load_oracle()
 
         def b16(name):
             a = main.get(name)
@@ -320,15 +269,12 @@ class HostModel:
             for q in range(Cc["nq"]):
                 p = ("decoder.quantizer.rvq_first.vq.layers.0._codebook." if q == 0
                      else f"decoder.quantizer.rvq_rest.vq.layers.{q - 1}._codebook.")
-                emb = np.empty((Cc["cb_size"], vq), dtype=np.float32)
-                orc.orc_prep_codebook(_p(emb, f32p), _p(cod[p + "embedding_sum"], f32p),
-                                      _p(cod[p + "cluster_usage"], f32p), Cc["cb_size"], vq)
+                emb = prep_codebook(cod[p + "embedding_sum"].reshape(Cc["cb_size"], vq), cod[p + "cluster_usage"])
                 self.keep.append(emb)
                 k.codebooks[q] = emb.ctypes.data_as(f32p)
 
             def snake(a_name, b_name):
-                a, b = cod[a_name].copy(), cod[b_name].copy()
-                orc.orc_prep_snake(_p(a, f32p), _p(b, f32p), a.size)
+                a, b = prep_snake(cod[a_name], cod[b_name])
                 self.keep += [a, b]
                 return a.ctypes.data_as(f32p), b.ctypes.data_as(f32p)
 

@@ -54,6 +54,14 @@ PRESETS["small"] = dict(
     sub=dict(vocab=2048, hidden=1024, inter=3072, layers=2, heads=16, kv=8, hd=128),
     codec=PRESETS["tiny"]["codec"],
 )
+# one 1.7B-shaped layer stack cut to 4 + 2 layers: the row split over 148 CTAs at H = 2048 / I = 6144 and long KV ranges
+# at a cost the oracle pays in seconds per hundred steps
+PRESETS["1.7b-4L"] = dict(
+    talker=dict(vocab=3072, hidden=2048, inter=6144, layers=4, heads=16, kv=8, hd=128),
+    text_hidden=2048, text_vocab=151936, groups=16, mrope=[24, 20, 20], theta=1000000.0,
+    sub=dict(vocab=2048, hidden=1024, inter=3072, layers=2, heads=16, kv=8, hd=128),
+    codec=PRESETS["tiny"]["codec"],
+)
 SPEAKERS = {"aiden": 3010, "vivian": 3011}
 LANGUAGES = {"english": 2050, "chinese": 2055}
 CODEC_IDS = dict(codec_pad_id=2148, codec_bos_id=2149, codec_eos_token_id=2150, codec_think_id=2154,

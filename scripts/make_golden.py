@@ -17,7 +17,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "qwen3-tts-c_b200"))
+sys.path.insert(0, ROOT)
 from harness import binding as B, modelgen as mg  # noqa: E402
+from oracle import orc_binding as O  # noqa: E402
 
 TOKENS = [151644, 77091, 198, 2354, 2244, 2355, 4041, 2244, 11752, 13, 151645, 198, 151644, 77091, 198]
 CSV = ",".join(str(t) for t in TOKENS).encode()
@@ -37,7 +39,7 @@ def run_generate(ref, ctx, params, n_frames, speaker=b"aiden", language=b"englis
 
 def main():
     out = {}
-    ref = B.load_ref()
+    ref = O.load_ref()
     spec = mg.PRESETS["tiny"]
     main_t, cod_t = mg.build_tensors(spec, seed=0)
     with tempfile.TemporaryDirectory() as d:

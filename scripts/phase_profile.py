@@ -18,11 +18,11 @@ def main():
     preset = sys.argv[1] if len(sys.argv) > 1 else "1.7b"
     pos = int(sys.argv[2]) if len(sys.argv) > 2 else 190
     layer = int(sys.argv[3]) if len(sys.argv) > 3 else 5
-    cuda, orc = B.load_cuda(), B.load_oracle()
+    cuda = B.load_cuda()
     assert cuda.qwen_tts_cuda_init(0) == 0
     spec = mg.PRESETS[preset]
     main_t, cod = mg.build_tensors(spec, seed=0, with_codec=False)
-    hm = B.HostModel(spec, main_t, {}, orc)
+    hm = B.HostModel(spec, main_t, {})
     ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
     assert ctx
     cuda.qwen_tts_cuda_set_mode(ctx, int(os.environ.get("QTC_MODE", "2")))

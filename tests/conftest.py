@@ -20,11 +20,11 @@ def pytest_configure(config):
 
 @pytest.fixture(scope="session")
 def orc():
-    from harness import binding as B
-    if not os.path.exists(B.ORACLE_LIB):
+    from oracle import orc_binding as O
+    if not os.path.exists(O.ORACLE_LIB):
         import subprocess
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"])
-    return B.load_oracle()
+    return O.load_oracle()
 
 
 _MODELS = {}
@@ -36,7 +36,7 @@ def get_model(orc, preset, seed=0, with_lm=True, with_codec=True):
     if key not in _MODELS:
         spec = mg.PRESETS[preset]
         main, cod = mg.build_tensors(spec, seed=seed, with_lm=with_lm, with_codec=with_codec)
-        _MODELS[key] = B.HostModel(spec, main, cod, orc)
+        _MODELS[key] = B.HostModel(spec, main, cod)
     return _MODELS[key]
 
 

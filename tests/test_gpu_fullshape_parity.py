@@ -1,0 +1,204 @@
+"""BASELINE shapes against the oracle ("What's weak" 1): the 1.7B and 0.6B decoder stacks and the full-size
+codec are compared with the CPU oracle for a bounded budget - a prefill plus a few frames is seconds of OpenMP work -
+so the things that exist only at full size are held to a second opinion, not to themselves:
+
+  * k_lm_fused's 148-CTA row split at H = 2048 / I = 6144 (and 1024 / 3072) over 28 layers, the 5-layer sub-talker program;
+  * the codec at 1536/768/384/192/96 channels, 1024-wide transformer with window 72 (T = 80 > 72);
+  * KV ranges 64..420 (up to 7 splits per head) and the page boundaries of the KV pool, on 1.7B-shaped layers;
+  * the lock-step batch at B = 64 on 1.7B shapes, rows against the oracle's solo run of the same prompt and seed.
+
+Bars: codes equal (sampled and greedy; fast and strict arithmetic), strict logits bit-identical, fast logits within 2e-4
+relative (north_star: 1e-2), PCM SNR >= 80 dB.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import FIXTURE_TOKENS, get_model
+from harness import binding as B, modelgen as mg
+from test_gpu_parity import CSV, TOK, bits, snr_db
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", params=["1.7b", "0.6b"])
+def full(request, cuda, orc):
+    hm = get_model(orc, request.param)
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    assert ctx, cuda.qwen_tts_cuda_last_error()
+    yield request.param, hm, ctx
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def _oracle_generate(orc, hm, params, n, tok=TOK, spk=3010, lang=2050):
+    s = orc.orc_create(hm.desc)
+    orc.orc_set_params(s, C.byref(params))
+    ns, nf = C.c_int(0), C.c_int(0)
+    want = np.zeros((n, 16), dtype=np.int32)
+    ptr = orc.orc_generate(s, B.iptr(tok), len(tok), spk, lang, C.byref(ns), B.iptr(want), n, C.byref(nf))
+    pcm = B.take_floats(orc.orc_free, ptr, ns.value)
+    orc.orc_destroy(s)
+    return want[: nf.value], pcm
+
+
+def _generate(cuda, ctx, params, n, csv=CSV):
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(params))
+    ns, nf = C.c_int(0), C.c_int(0)
+    codes = np.zeros((n, 16), dtype=np.int32)
+    ptr = cuda.qwen_tts_cuda_generate(ctx, csv, b"aiden", b"english", C.byref(ns), B.iptr(codes), n, C.byref(nf))
+    assert ptr, cuda.qwen_tts_cuda_last_error()
+    return codes[: nf.value], B.take_floats(cuda.qwen_tts_cuda_free_host, ptr, ns.value)
+
+
+@pytest.mark.parametrize("greedy", [0, 1], ids=["sampled", "greedy"])
+def test_full_model_utterance_vs_oracle(cuda, orc, full, greedy):
+    """prompt build + prefill + 4 frames + codec decode of them, whole-utterance API: codes equal, waveform >= 80 dB"""
+    name, hm, ctx = full
+    n = 4
+    p = (B.greedy_params if greedy else B.default_params)(fixed_codec_tokens=n)
+    want, want_pcm = _oracle_generate(orc, hm, p, n)
+    assert len(want) == n and want_pcm.size == n * 1920
+    for strict in (0, 1):
+        cuda.qwen_tts_cuda_set_arith(ctx, strict)
+        codes, pcm = _generate(cuda, ctx, p, n)
+        assert np.array_equal(codes, want), f"{name} strict={strict}: first mismatch at {np.argwhere(codes != want)[0]}"
+        assert snr_db(want_pcm, pcm) >= 80.0
+    cuda.qwen_tts_cuda_set_arith(ctx, 0)
+
+
+def test_full_model_stage_logits_vs_oracle(cuda, orc, full):
+    """stage API at full shapes: 10-token prefill, 3 decode steps, 2 sub-talker frames.  Strict: logits and hidden states
+    bit-identical to the oracle; fast: logits within 2e-4 relative, sub-talker codes equal."""
+    name, hm, ctx = full
+    H, V = hm.spec["talker"]["hidden"], hm.spec["talker"]["vocab"]
+    rng = np.random.default_rng(11)
+    n_pre, n_steps = 10, 3
+    emb = (rng.standard_normal((n_pre + n_steps, H)) * 0.5).astype(np.float32)
+    s = orc.orc_create(hm.desc)
+    orc.orc_reset(s)
+    orc.orc_talker_prefill(s, B.fptr(emb), n_pre)
+    want_hid0 = np.ctypeslib.as_array(orc.orc_hidden(s), shape=(H,)).copy()
+    want_logits, want_hid = np.zeros((n_steps, V), dtype=np.float32), np.zeros((n_steps, H), dtype=np.float32)
+    for i in range(n_steps):
+        orc.orc_talker_forward(s, B.fptr(emb[n_pre + i]), B.fptr(want_logits[i]))
+        want_hid[i] = np.ctypeslib.as_array(orc.orc_hidden(s), shape=(H,))
+    sub_cases = ((B.default_params(), 901), (B.greedy_params(), 17))
+    want_sub = []
+    for pp, fc in sub_cases:
+        orc.orc_set_params(s, C.byref(pp))
+        out = np.zeros(32, dtype=np.int32)
+        orc.orc_subtalker_generate(s, B.fptr(want_hid[0]), fc, B.iptr(out))
+        want_sub.append(out[:16].copy())
+    orc.orc_destroy(s)
+    for strict in (1, 0):
+        cuda.qwen_tts_cuda_set_arith(ctx, strict)
+        cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.greedy_params()))
+        cuda.qwen_tts_cuda_reset(ctx)
+        assert cuda.qwen_tts_cuda_talker_prefill(ctx, B.fptr(emb), n_pre) == 0
+        hid0 = np.zeros(H, dtype=np.float32)
+        assert cuda.qwen_tts_cuda_get_hidden(ctx, B.fptr(hid0)) == 0
+        logits, hid = np.zeros((n_steps, V), dtype=np.float32), np.zeros((n_steps, H), dtype=np.float32)
+        for i in range(n_steps):
+            assert cuda.qwen_tts_cuda_talker_forward(ctx, B.fptr(emb[n_pre + i]), B.fptr(logits[i])) == 0
+            assert cuda.qwen_tts_cuda_get_hidden(ctx, B.fptr(hid[i])) == 0
+        if strict:
+            assert np.array_equal(bits(hid0), bits(want_hid0))
+            assert np.array_equal(bits(logits), bits(want_logits))
+            assert np.array_equal(bits(hid), bits(want_hid))
+        else:
+            rel = float(np.abs(logits - want_logits).max() / np.abs(want_logits).max())
+            assert rel <= 2e-4, rel
+            assert np.abs(hid0 - want_hid0).max() <= 2e-4 * np.abs(want_hid0).max()
+            assert (logits.argmax(1) == want_logits.argmax(1)).all()
+        for (pp, fc), w in zip(sub_cases, want_sub):
+            cuda.qwen_tts_cuda_set_params(ctx, C.byref(pp))
+            out = np.zeros(32, dtype=np.int32)
+            assert cuda.qwen_tts_cuda_subtalker_generate(ctx, B.fptr(want_hid[0]), fc, B.iptr(out)) == 0
+            assert np.array_equal(out[:16], w), (name, strict)
+    cuda.qwen_tts_cuda_set_arith(ctx, 0)
+
+
+def test_full_codec_80_frames_vs_oracle(cuda, orc):
+    """the full-size codec decoder (1536-channel vocoder, 1024-wide transformer, window 72) on 80 frames (> window) of random
+    codes, incl. out-of-range ids (c/qwen_tts_codec.c:169-170): SNR >= 80 dB against the oracle's PCM"""
+    hm = get_model(orc, "1.7b")
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    assert ctx, cuda.qwen_tts_cuda_last_error()
+    T = 80
+    rng = np.random.default_rng(2)
+    codes = rng.integers(0, 2048, size=(T, 16), dtype=np.int32)
+    codes[5, 3], codes[40, 0] = -1, 4096
+    s = orc.orc_create(hm.desc)
+    ns = C.c_int(0)
+    want = B.take_floats(orc.orc_free, orc.orc_codec_decode(s, B.iptr(codes), T, C.byref(ns)), T * 1920)
+    orc.orc_destroy(s)
+    assert ns.value == T * 1920
+    ptr = cuda.qwen_tts_cuda_codec_decode(ctx, B.iptr(codes), T, C.byref(ns))
+    assert ptr and ns.value == T * 1920, cuda.qwen_tts_cuda_last_error()
+    got = B.take_floats(cuda.qwen_tts_cuda_free_host, ptr, ns.value)
+    snr = snr_db(want, got)
+    assert snr >= 80.0, snr
+    assert float(np.abs(got - want).max()) <= 1e-3
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def test_long_kv_on_17b_layers_vs_oracle(cuda, orc):
+    """teacher-forced talker steps on 1.7B-shaped layers (4 of them) from KV 40 to 424: every split count of the split-KV
+    attention (1..7 ranges per head) and six page boundaries of the KV pool, each step against the oracle"""
+    hm = get_model(orc, "1.7b-4L", with_codec=False)
+    H, V = hm.spec["talker"]["hidden"], hm.spec["talker"]["vocab"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    assert ctx, cuda.qwen_tts_cuda_last_error()
+    s = orc.orc_create(hm.desc)
+    rng = np.random.default_rng(4)
+    n_pre, n_steps = 40, 384
+    emb = (rng.standard_normal((n_pre + n_steps, H)) * 0.5).astype(np.float32)
+    orc.orc_reset(s)
+    orc.orc_talker_prefill(s, B.fptr(emb), n_pre)
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.greedy_params()))
+    cuda.qwen_tts_cuda_set_arith(ctx, 0)
+    cuda.qwen_tts_cuda_reset(ctx)
+    assert cuda.qwen_tts_cuda_talker_prefill(ctx, B.fptr(emb), n_pre) == 0
+    worst = 0.0
+    want, got = np.zeros(V, dtype=np.float32), np.zeros(V, dtype=np.float32)
+    for i in range(n_steps):
+        orc.orc_talker_forward(s, B.fptr(emb[n_pre + i]), B.fptr(want))
+        assert cuda.qwen_tts_cuda_talker_forward(ctx, B.fptr(emb[n_pre + i]), B.fptr(got)) == 0
+        worst = max(worst, float(np.abs(got - want).max() / np.abs(want).max()))
+        assert int(got.argmax()) == int(want.argmax()), i
+    assert worst <= 5e-4, worst
+    assert cuda.qwen_tts_cuda_get_kv_len(ctx) == n_pre + n_steps
+    orc.orc_destroy(s)
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def test_batch64_rows_vs_oracle_17b(cuda, orc):
+    """config 4 shapes: 64 ragged prompts in lock-step on the 1.7B model, 3 frames; rows 0, 29 and 63 against the oracle's
+    solo run of the same prompt with seed + row (codes equal)"""
+    hm = get_model(orc, "1.7b")
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    assert ctx, cuda.qwen_tts_cuda_last_error()
+    nb, frames, G = 64, 3, 16
+    cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+    rng = np.random.default_rng(9)
+    prompts = []
+    for b in range(nb):
+        extra = [int(x) for x in rng.integers(1000, 5000, size=int(rng.integers(0, 10)))]
+        prompts.append(FIXTURE_TOKENS[:4] + extra + FIXTURE_TOKENS[4:])
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    spk = np.full(nb, mg.SPEAKERS["aiden"], dtype=np.int32)
+    lang = np.full(nb, mg.LANGUAGES["english"], dtype=np.int32)
+    p = B.default_params(fixed_codec_tokens=frames, sample_seed=300)
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
+    codes = np.zeros((nb, frames, G), dtype=np.int32)
+    nfr = np.zeros(nb, dtype=np.int32)
+    assert cuda.qwen_tts_cuda_generate_batch(ctx, nb, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), None, frames) == 0, \
+        cuda.qwen_tts_cuda_last_error()
+    assert (nfr == frames).all()
+    for b in (0, 29, 63):
+        want, _ = _oracle_generate(orc, hm, B.default_params(fixed_codec_tokens=frames, sample_seed=300 + b), frames,
+                                   tok=np.array(prompts[b], dtype=np.int32))
+        assert np.array_equal(codes[b], want), f"row {b}: first mismatch at {np.argwhere(codes[b] != want)[0]}"
+    cuda.qwen_tts_cuda_release(ctx)

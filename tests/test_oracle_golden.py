@@ -114,3 +114,25 @@ def test_kernel_known_answers(orc):
         assert nl.value == want.shape[1] == L * s
         got = yo.reshape(-1)[:co * nl.value].reshape(co, nl.value)
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), name
+
+
+def test_host_prep_matches_oracle(orc):
+    """harness/binding.py does the reference's load-time preprocessing (c/qwen_tts.c:577-602) in numpy + libm without the
+    checker; hold it bit for bit to the oracle's restatement (orc_prep_codebook / orc_prep_snake)."""
+    import ctypes as C
+    from harness import binding as B
+    rng = np.random.default_rng(3)
+    es = rng.standard_normal((2048, 64)).astype(np.float32)
+    us = rng.uniform(0.0, 1.5, size=2048).astype(np.float32)
+    us[:7] = [0.0, 1e-6, 1e-5, 9.9e-6, 1.0, 3e-5, 2.0]
+    want = np.empty_like(es)
+    orc.orc_prep_codebook.argtypes = [B.f32p, B.f32p, B.f32p, C.c_int, C.c_int]
+    orc.orc_prep_codebook(B.fptr(want), B.fptr(es), B.fptr(us), 2048, 64)
+    assert np.array_equal(B.prep_codebook(es, us).view(np.uint32), want.view(np.uint32))
+    a = (rng.standard_normal(1536) * 0.7).astype(np.float32)
+    b = (rng.standard_normal(1536) * 0.7).astype(np.float32)
+    wa, wb = a.copy(), b.copy()
+    orc.orc_prep_snake.argtypes = [B.f32p, B.f32p, C.c_int]
+    orc.orc_prep_snake(B.fptr(wa), B.fptr(wb), a.size)
+    ga, gb = B.prep_snake(a, b)
+    assert np.array_equal(ga.view(np.uint32), wa.view(np.uint32)) and np.array_equal(gb.view(np.uint32), wb.view(np.uint32))

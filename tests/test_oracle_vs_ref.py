@@ -11,14 +11,15 @@ import pytest
 
 from conftest import FIXTURE_TOKENS
 from harness import binding as B, modelgen as mg
+from oracle import orc_binding as O
 
-pytestmark = pytest.mark.skipif(not B.have_ref(), reason="oracle/_ref/libqtts_ref.so not built (make -C oracle ref)")
+pytestmark = pytest.mark.skipif(not O.have_ref(), reason="oracle/_ref/libqtts_ref.so not built (make -C oracle ref)")
 CSV = ",".join(str(t) for t in FIXTURE_TOKENS).encode()
 
 
 @pytest.fixture(scope="module")
 def loaded(orc, tmp_path_factory):
-    ref = B.load_ref()
+    ref = O.load_ref()
     spec = mg.PRESETS["tiny"]
     main, cod = mg.build_tensors(spec, seed=3)
     d = str(tmp_path_factory.mktemp("model"))
@@ -60,7 +61,7 @@ def test_descriptor_from_reference_equals_harness_descriptor(orc, loaded):
     harness.binding.HostModel, so descriptors built without the reference carry the same numbers"""
     ref, ctx, desc, spec = loaded
     main, cod = mg.build_tensors(spec, seed=3)
-    hm = B.HostModel(spec, main, cod, orc)
+    hm = B.HostModel(spec, main, cod)
     vq = spec["codec"]["cb_dim"] // 2
     for q in (0, 1, 15):
         a = np.ctypeslib.as_array(desc.codec.codebooks[q], shape=(2048 * vq,))
