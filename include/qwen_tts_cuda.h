@@ -287,8 +287,6 @@ double qwen_tts_cuda_subtalker_frame_bytes(const qtc_ctx_t *ctx);
 /* per-phase SM-clock stamps of the fused talker step (layer `layer`, KV position `pos`): 16 slots per CTA,
  * out[num_sms*16]; returns the CTA count.  Evidence for profiles/, not part of the reference's interface. */
 int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *ctx, int pos, int layer, long long *out);
-/* mode 3 (barrier-free fused step): 0, or the tag a poll gave up on - a protocol bug, reported instead of hanging */
-int qwen_tts_cuda_exchange_error(qtc_ctx_t *ctx);
 const char *qwen_tts_cuda_last_error(void);
 
 #ifdef __cplusplus

@@ -194,26 +194,6 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
         cudaMemcpy(c->talker_dev, &c->talker, sizeof(LmDev), cudaMemcpyHostToDevice);
         cudaMemcpy(c->sub_dev, &c->sub, sizeof(LmDev), cudaMemcpyHostToDevice);
         cudaMemset(c->bar, 0, 64);
-        /* mode 3 exchange buffers: {value, tag} words, zero = tag 0 = never valid (the epoch starts at 1) */
-        const qtc_lm_t *ds[2] = {&desc->talker, &desc->sub};
-        bool ll_ok = true;
-        for (int k = 0; k < 2; k++) {
-            const size_t hk = ds[k]->hidden > 0 ? ds[k]->hidden : 1, ik = ds[k]->intermediate > 0 ? ds[k]->intermediate : 1;
-            const size_t qk = (size_t)(ds[k]->heads + 2 * ds[k]->kv_heads) * ds[k]->head_dim + 2;
-            c->ll_xa[k] = (unsigned long long *)qtc_dmalloc(c, hk * 8); c->ll_xb[k] = (unsigned long long *)qtc_dmalloc(c, hk * 8);
-            c->ll_qkv[k] = (unsigned long long *)qtc_dmalloc(c, qk * 8); c->ll_g[k] = (unsigned long long *)qtc_dmalloc(c, ik * 8);
-            ll_ok = ll_ok && c->ll_xa[k] && c->ll_xb[k] && c->ll_qkv[k] && c->ll_g[k];
-            if (ll_ok) { cudaMemset(c->ll_xa[k], 0, hk * 8); cudaMemset(c->ll_xb[k], 0, hk * 8); cudaMemset(c->ll_qkv[k], 0, qk * 8); cudaMemset(c->ll_g[k], 0, ik * 8); }
-        }
-        const size_t part_n = (size_t)(heads > 0 ? heads : 1) * 16 * (hd + 4), lg_n = (size_t)(V > 0 ? V : 1);
-        c->ll_part = (unsigned long long *)qtc_dmalloc(c, part_n * 8);
-        c->ll_logits = (unsigned long long *)qtc_dmalloc(c, lg_n * 8);
-        c->ll_epoch = (uint32_t *)qtc_dmalloc(c, 16);
-        c->ll_err = (int *)qtc_dmalloc(c, 16);
-        if (!ll_ok || !c->ll_part || !c->ll_logits || !c->ll_epoch || !c->ll_err) { qwen_tts_cuda_release(c); return NULL; }
-        cudaMemset(c->ll_part, 0, part_n * 8); cudaMemset(c->ll_logits, 0, lg_n * 8); cudaMemset(c->ll_err, 0, 16);
-        const uint32_t one = 1;
-        cudaMemcpy(c->ll_epoch, &one, 4, cudaMemcpyHostToDevice);
         cudaMemset(c->head_cnt, 0, (size_t)(heads > 0 ? heads : 1) * 4);
     }
     c->sample_scratch = (int *)qtc_dmalloc(c, (size_t)(V > 0 ? V : 1) * 4);
@@ -233,7 +213,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
 extern "C" void qwen_tts_cuda_set_params(qtc_ctx_t *c, const qtc_gen_params_t *p) { if (c && p) { c->params = *p; c->graph_key = -1; } }
 extern "C" void qwen_tts_cuda_get_perf(const qtc_ctx_t *c, qtc_perf_t *out) { if (c && out) { *out = c->perf; out->kernel_launches = c->launches; } }
 extern "C" int qwen_tts_cuda_set_mode(qtc_ctx_t *c, int mode) {
-    if (!c || mode < 0 || mode > 3) return -1;
+    if (!c || mode < 0 || mode > 1) return -1;
     c->mode = mode; c->graph_key = -1;
     return 0;
 }

@@ -128,10 +128,6 @@ struct qtc_ctx {
     unsigned long long *bar;      /* grid barrier counter */
     unsigned *head_cnt;           /* [heads] */
     float *attn_part;             /* [heads, 8, head_dim + 2] */
-    /* barrier-free variant (mode 3, qtc_ll.cuh): tagged 8-byte exchange buffers, [0] talker, [1] sub-talker */
-    unsigned long long *ll_xa[2], *ll_xb[2], *ll_qkv[2], *ll_g[2], *ll_part, *ll_logits;
-    uint32_t *ll_epoch;           /* last tag handed out */
-    int *ll_err;                  /* sticky: a poll timed out (protocol bug) */
     int num_sms;
     int prof_sub;                      /* 1: stamp the sub-talker's steps instead of the talker's */
     long long *prof; int prof_layer;   /* optional per-phase clock stamps of the fused kernel (debug) */
@@ -142,7 +138,7 @@ struct qtc_ctx {
     CodecDev *codec;
     qtc_gen_params_t params;
     qtc_perf_t perf;
-    int mode;                     /* 0 per-op kernels, 1 fused persistent kernels, 2 TMA ring (experimental), 3 fused without grid barriers */
+    int mode;                     /* 0 per-op kernels, 1 fused persistent kernels (default) */
     int arith;                    /* QTC_FAST / QTC_STRICT */
     cudaStream_t stream;
     cudaEvent_t ev0, ev1, ev2, ev3;   /* ev2..ev3: device span of a whole utterance (prompt build .. last codec kernel) */

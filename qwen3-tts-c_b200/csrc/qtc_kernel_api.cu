@@ -249,14 +249,6 @@ extern "C" int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *c, int pos, int layer
     return c->num_sms;
 }
 
-extern "C" int qwen_tts_cuda_exchange_error(qtc_ctx_t *c) {
-    if (!c || !c->ll_err) return 0;
-    int v = 0;
-    if (cudaStreamSynchronize(c->stream) != cudaSuccess || cudaMemcpy(&v, c->ll_err, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
-    if (v) qtc_set_error("mode 3: a tagged-exchange poll timed out (tag 0x%x)", (unsigned)v);
-    return v;
-}
-
 extern "C" double qwen_tts_cuda_bench_subtalker(qtc_ctx_t *c, int iters, int do_flush) {
     if (!c || c->sub.layers <= 0 || iters <= 0) return -1.0;
     cudaMemsetAsync(c->st_proj, 0, (size_t)c->H * 4, c->stream);

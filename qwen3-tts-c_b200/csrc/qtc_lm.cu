@@ -8,8 +8,6 @@
  * captured into a CUDA graph and replayed.
  */
 #include "qtc_fused_main.cuh"
-#include "qtc_ring_main.cuh"
-#include "qtc_ll.cuh"
 #include "qtc_gemv.cuh"
 #include "qtc_internal.h"
 #include "qtc_lm_kernels.cuh"
@@ -141,145 +139,8 @@ static bool fused_ok(const qtc_ctx *c, const LmDev *lm) {
            lm->hidden % 8 == 0 && lm->inter % 8 == 0 && (lm->heads * lm->head_dim) % 8 == 0 && lm->heads <= c->num_sms &&
            lm->heads * (lm->head_dim + 4) <= 2 * ATT_STAGE_MAX * lm->head_dim;
 }
-/* mode 2: the same step with the weights streamed through the shared-memory ring (qtc_ring.cuh) */
-static int g_ring_attr = 0, g_ring_max_smem = 0;
-static bool ring_ok(const qtc_ctx *c, const LmDev *lm, const SubProg *prog) {
-    if (c->mode != 2) return false;
-    const int qd = lm->heads * lm->head_dim;
-    if (!ring_shape_ok(lm->hidden) || !ring_shape_ok(qd) || !ring_shape_ok(lm->inter)) return false;
-    if (lm->hidden > FUSED_THREADS * 8) return false;
-    if (prog && prog->in_w && !ring_shape_ok(prog->Hin)) return false;
-    long long mr = lm->inter > lm->vocab ? lm->inter : lm->vocab;
-    if (qd + 2 * lm->kv_heads * lm->head_dim > mr) mr = qd + 2 * lm->kv_heads * lm->head_dim;
-    if (mr * (c->num_sms + 1) >= (1LL << 31)) return false;            /* row_range32 */
-    return true;
-}
-static int ring_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
-                     const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog) {
-    if (!g_ring_attr) {
-        cudaFuncAttributes fa;
-        QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_ring));
-        g_ring_max_smem = 211 * 1024 - (int)fa.sharedSizeBytes;      /* ~16 KB of the 228 KB stay L1: spills, norm weights, RoPE rows */
-        QTC_CUDA(cudaFuncSetAttribute(k_lm_ring, cudaFuncAttributeMaxDynamicSharedMemorySize, g_ring_max_smem));
-        g_ring_attr = 1;
-    }
-    FusedArgs a;
-    memset(&a, 0, sizeof(a));
-    a.lm = lm == &c->talker ? c->talker_dev : c->sub_dev;
-    a.x = b->x; a.q = b->q; a.kk = b->kk; a.vv = b->vv; a.att = b->att; a.g = b->g;
-    a.kc = b->k; a.vc = b->v; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
-    a.pos_ptr = pos_ptr; a.pos_add = pos_add;
-    a.head_w = head_w; a.head_rows = head_rows; a.logits = logits;
-    a.bar = c->bar; a.head_cnt = c->head_cnt; a.part = c->attn_part; a.st = st;
-    a.prof = (c->prof_sub ? lm == &c->sub : lm == &c->talker) ? c->prof : NULL; a.prof_layer = c->prof_layer;
-    const int n = c->num_sms, qd = lm->heads * lm->head_dim;
-    SubProg sp;
-    memset(&sp, 0, sizeof(sp));
-    if (prog) sp = *prog;
-    /* staged vector: the normed hidden, the attention output, or the gathered sub-talker input */
-    int vec = lm->hidden > qd ? lm->hidden : qd;
-    if (prog && sp.Hin > vec) vec = sp.Hin;
-    a.xs_floats = (vec + 3) & ~3;
-    int sc = (b->kv_max + n / lm->heads - 1) / (n / lm->heads > 0 ? n / lm->heads : 1);
-    if (sc < 64) sc = 64;
-    a.att_floats = (2 * lm->head_dim + FUSED_THREADS + sc + 64 + 3 * lm->heads * FUSED_MAX_SPLIT + 3) & ~3;
-    /* KV stage: the sub-talker never holds more than G + 2 positions; the talker stages up to 64 per CTA */
-    a.att_cap = prog ? 32 : ATT_STAGE_MAX;
-    if (lm->heads * (lm->head_dim + 4) > 2 * a.att_cap * lm->head_dim) { qtc_set_error("ring step: attention partials do not fit the KV stage"); return -1; }
-    size_t kvf = (size_t)2 * a.att_cap * lm->head_dim;
-    if (prog) { const size_t need = (size_t)2 * ((sp.vocab + 3) & ~3) + (sizeof(SampleSmem) + 3) / 4 + 4; if (need > kvf) kvf = need; }
-    a.kv_floats = (int)((kvf + 3) & ~(size_t)3);
-    /* the split input vector of a phase (3 bf16 pieces) lives in the KV stage region */
-    {
-        int mc = lm->hidden > lm->inter ? lm->hidden : lm->inter;
-        if (qd > mc) mc = qd;
-        if (prog && sp.Hin > mc) mc = sp.Hin;
-        const size_t need = ((size_t)3 * (mc + 8) + 1) / 2 + 4;
-        if (need > (size_t)a.kv_floats) a.kv_floats = (int)((need + 3) & ~(size_t)3);
-    }
-    /* partial sums: [stages (row blocks x column chunks) of the widest phase of this launch][16 warps][8 rows] */
-    auto stages = [&](int rows, int cols, int per) { return (((rows + n - 1) / n + per - 1) / per) * ((cols + RING_KC - 1) / RING_KC); };
-    int pb = stages(qd + 2 * lm->kv_heads * lm->head_dim, lm->hidden, 8);
-    if (stages(lm->inter, lm->hidden, 4) > pb) pb = stages(lm->inter, lm->hidden, 4);
-    if (stages(lm->hidden, qd, 8) > pb) pb = stages(lm->hidden, qd, 8);
-    if (stages(lm->hidden, lm->inter, 8) > pb) pb = stages(lm->hidden, lm->inter, 8);
-    if (stages(head_rows, lm->hidden, 8) > pb) pb = stages(head_rows, lm->hidden, 8);
-    if (prog && stages(lm->hidden, sp.Hin, 8) > pb) pb = stages(lm->hidden, sp.Hin, 8);
-    const size_t part_floats = (size_t)(pb + 1) * RING_GW * 8;
-    size_t off = ((size_t)a.xs_floats + a.att_floats + a.kv_floats + part_floats) * 4;
-    off = (off + 127) & ~(size_t)127;
-    a.ring_off = (int)off;
-    if (off + 2 * RING_STAGE_BYTES > (size_t)g_ring_max_smem) { qtc_set_error("ring step: %zu bytes of shared memory before the ring", off); return -1; }
-    { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
-    a.nst = (int)(((size_t)g_ring_max_smem - off) / RING_STAGE_BYTES);
-    if (a.nst > RING_MAX_STAGES) a.nst = RING_MAX_STAGES;
-    { static int cap = -1; if (cap < 0) { const char *e = getenv("QTC_RING_STAGES"); cap = e ? atoi(e) : 0; } if (cap >= 2 && cap < a.nst) a.nst = cap; }
-    const size_t smem = off + (size_t)a.nst * RING_STAGE_BYTES;
-    void *args[] = {&a, &sp, (void *)lm};
-    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_ring, dim3(n), dim3(RING_THREADS), args, smem, c->stream));
-    c->launches++;
-    return 0;
-}
-/* mode 3: the fused step without grid barriers (qtc_ll.cuh) */
-static int g_ll_attr = 0, g_ll_max_smem = 0;
-static int ll_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
-                   const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog) {
-    if (!g_ll_attr) {
-        cudaFuncAttributes fa;
-        QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_ll));
-        g_ll_max_smem = 227 * 1024 - (int)fa.sharedSizeBytes;
-        QTC_CUDA(cudaFuncSetAttribute(k_lm_ll, cudaFuncAttributeMaxDynamicSharedMemorySize, g_ll_max_smem));
-        g_ll_attr = 1;
-    }
-    FusedArgs a;
-    memset(&a, 0, sizeof(a));
-    const int k = lm == &c->talker ? 0 : 1;
-    a.lm = k == 0 ? c->talker_dev : c->sub_dev;
-    a.x = b->x;
-    a.kc = b->k; a.vc = b->v; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
-    a.pos_ptr = pos_ptr; a.pos_add = pos_add;
-    a.head_w = head_w; a.head_rows = head_rows; a.logits = logits; a.st = st;
-    a.prof = (c->prof_sub ? lm == &c->sub : lm == &c->talker) ? c->prof : NULL; a.prof_layer = c->prof_layer;
-    { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
-    LLArgs ll;
-    ll.xa = c->ll_xa[k]; ll.xb = c->ll_xb[k]; ll.qkv = c->ll_qkv[k]; ll.g = c->ll_g[k]; ll.part = c->ll_part; ll.logits = c->ll_logits;
-    ll.epoch = c->ll_epoch; ll.err = c->ll_err;
-    const int qd = lm->heads * lm->head_dim;
-    int vec = lm->hidden > lm->inter ? lm->hidden : lm->inter;
-    if (qd > vec) vec = qd;
-    SubProg sp;
-    memset(&sp, 0, sizeof(sp));
-    if (prog) {
-        sp = *prog;
-        if (2 * sp.vocab > vec) vec = 2 * sp.vocab;
-        if (sp.Hin > vec) vec = sp.Hin;
-    }
-    int sc = (b->kv_max + c->num_sms / lm->heads - 1) / (c->num_sms / lm->heads > 0 ? c->num_sms / lm->heads : 1);
-    if (sc < 64) sc = 64;
-    const int attn = 5 * lm->head_dim + FUSED_THREADS + sc + 64 + 3 * lm->heads * FUSED_MAX_SPLIT;
-    a.xs_floats = (vec + 3) & ~3;
-    a.att_floats = (attn + 3) & ~3;
-    a.kv_floats = 2 * ATT_STAGE_MAX * lm->head_dim;
-    /* landing zone of the polled words: the widest staged vector, and as many attention splits' records as fit */
-    const size_t fixed = (size_t)(a.xs_floats + a.att_floats + a.kv_floats) * 4;
-    int need = lm->hidden > lm->inter ? lm->hidden : lm->inter;
-    if (prog && sp.vocab > need) need = sp.vocab;
-    const int rec1 = lm->heads * (lm->head_dim + 4);                 /* words of one split of every head */
-    if (rec1 > need) need = rec1;
-    if (fixed + (size_t)need * 8 > (size_t)g_ll_max_smem) { qtc_set_error("ll step: %zu bytes of shared memory needed, %d available", fixed + (size_t)need * 8, g_ll_max_smem); return -1; }
-    int words = (int)(((size_t)g_ll_max_smem - fixed) / 8);
-    if (words > rec1 * FUSED_MAX_SPLIT && rec1 * FUSED_MAX_SPLIT >= need) words = rec1 * FUSED_MAX_SPLIT;
-    a.ring_off = words & ~1;
-    const size_t smem = fixed + (size_t)a.ring_off * 8;
-    void *args[] = {&a, &sp, &ll};
-    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_ll, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
-    c->launches++;
-    return 0;
-}
 static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
                       const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog = NULL) {
-    if (ring_ok(c, lm, prog)) return ring_step(c, lm, b, pos_ptr, pos_add, head_w, head_rows, logits, st, prog);
-    if (c->mode == 3 && lm->vocab % 2 == 0) return ll_step(c, lm, b, pos_ptr, pos_add, head_w, head_rows, logits, st, prog);
     if (!g_fused_attr) {
         cudaFuncAttributes fa;
         QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_fused));
@@ -314,8 +175,13 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     if (attn < 2 * FUSED_WARPS + FUSED_WARPS * lm->head_dim) attn = 2 * FUSED_WARPS + FUSED_WARPS * lm->head_dim;   /* cta_attention_warps: 16 (max, sum, out[hd]) triples */
     a.xs_floats = (vec + 3) & ~3;
     a.att_floats = (attn + 3) & ~3;
-    const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
+    size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
     if (smem > (size_t)g_fused_max_smem) { qtc_set_error("fused step: %zu bytes of shared memory needed, %d available", smem, g_fused_max_smem); return -1; }
+    /* landing zone of the next phase's weights: whatever shared memory is left (QTC_FUSED_FLAGS & 128: off) */
+    a.lz_off = (int)((smem + 127) & ~(size_t)127);
+    a.lz_bytes = ((g_fused_max_smem - a.lz_off) / 1024) * 1024;
+    if (a.lz_bytes < 16 * 1024 || (a.flags & 128)) a.lz_bytes = 0;
+    if (a.lz_bytes > 0) smem = (size_t)a.lz_off + a.lz_bytes;
     void *args[] = {&a, &sp};
     QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
     c->launches++;

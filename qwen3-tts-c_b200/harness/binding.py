@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-CUDA_LIB = os.path.join(ROOT, "qwen3-tts-c_b200", "csrc", "libqwen_tts_cuda.so")
+CUDA_LIB = os.environ.get("QTC_LIB") or os.path.join(ROOT, "qwen3-tts-c_b200", "csrc", "libqwen_tts_cuda.so")   # QTC_LIB: A/B against an older build
 
 MAX_LM_LAYERS, MAX_CODEC_LAYERS, MAX_GROUPS, MAX_Q, MAX_NAMES = 32, 12, 32, 16, 64
 u16p, f32p, i32p = C.POINTER(C.c_uint16), C.POINTER(C.c_float), C.POINTER(C.c_int)
@@ -154,8 +154,6 @@ def load_cuda():
     lib.qwen_tts_cuda_snake_beta.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_matmul_f32.argtypes = [f32p, f32p, f32p, C.c_int, C.c_int, C.c_int]
     lib.qwen_tts_cuda_matmul_bf16.argtypes = [f32p, f32p, u16p, C.c_int, C.c_int, C.c_int]
-    lib.qwen_tts_cuda_exchange_error.argtypes = [vp]
-    lib.qwen_tts_cuda_exchange_error.restype = C.c_int
     lib.qwen_tts_cuda_bench_talker_step.restype = C.c_double
     lib.qwen_tts_cuda_bench_talker_step.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     lib.qwen_tts_cuda_bench_subtalker.restype = C.c_double

@@ -25,7 +25,7 @@ def main():
     hm = B.HostModel(spec, main_t, {})
     ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
     assert ctx
-    cuda.qwen_tts_cuda_set_mode(ctx, int(os.environ.get("QTC_MODE", "2")))
+    cuda.qwen_tts_cuda_set_mode(ctx, int(os.environ.get("QTC_MODE", "1")))
     cuda.qwen_tts_cuda_debug_phase_clocks.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_longlong)]
     out = np.zeros(148 * 32 * 2, dtype=np.int64)
     n = cuda.qwen_tts_cuda_debug_phase_clocks(ctx, pos, layer, out.ctypes.data_as(C.POINTER(C.c_longlong)))

@@ -1,5 +1,6 @@
-"""Modes 1, 2 and 3 (one persistent cooperative kernel per decoder-stack step; mode 2 streams the weights through
-the shared-memory TMA ring, mode 3 replaces the grid barriers by tagged 8-byte exchanges) against the same golden vectors and oracle as the per-op path.  Fast arithmetic: logits within 1e-2 relative (north_star), codes equal."""
+"""Mode 1 (one persistent cooperative kernel per decoder-stack step, weights of the next phase landing in shared memory
+across the grid barriers) against the same golden vectors and oracle as the per-op path, with the landing zone on and off
+(QTC_FUSED_FLAGS & 128).  Fast arithmetic: logits within 1e-2 relative (north_star), codes equal."""
 import ctypes as C
 import os
 
@@ -13,13 +14,12 @@ from test_gpu_parity import GEN_CASES, GOLD, TOK, _generate, _stage_run, snr_db
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module", params=[1, 2, 3], ids=["fused", "ring", "ll"])
+@pytest.fixture(scope="module", params=[1], ids=["fused"])
 def fused_ctx(request, cuda, tiny):
     ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 1)
     assert ctx, cuda.qwen_tts_cuda_last_error()
     assert cuda.qwen_tts_cuda_set_mode(ctx, request.param) == 0
     yield ctx
-    assert cuda.qwen_tts_cuda_exchange_error(ctx) == 0, cuda.qwen_tts_cuda_last_error()
     cuda.qwen_tts_cuda_release(ctx)
 
 
@@ -42,7 +42,7 @@ def test_fused_generate(cuda, fused_ctx, name, params, spk, lang):
     assert snr_db(want_pcm, pcm) >= 80.0
 
 
-@pytest.mark.parametrize("mode", [1, 2, 3], ids=["fused", "ring", "ll"])
+@pytest.mark.parametrize("mode", [1], ids=["fused"])
 def test_fused_long_context_splits(cuda, orc, mode):
     """KV length past 64 / 128 / ... positions exercises the split-KV attention and its combine step:
     teacher-forced talker steps on the `small` preset (16 Q / 8 KV heads of 128) against the oracle"""
@@ -68,6 +68,5 @@ def test_fused_long_context_splits(cuda, orc, mode):
         assert int(got.argmax()) == int(want.argmax()), i
     assert worst <= 5e-4, worst
     assert cuda.qwen_tts_cuda_get_kv_len(ctx) == n_pre + n_steps
-    assert cuda.qwen_tts_cuda_exchange_error(ctx) == 0, cuda.qwen_tts_cuda_last_error()
     orc.orc_destroy(s)
     cuda.qwen_tts_cuda_release(ctx)
