@@ -48,7 +48,6 @@ struct FusedArgs {
     int nst;                       /* ring stages (k_lm_ring) */
     int att_cap;                   /* positions the shared-memory KV stage holds */
     int kv_floats;                 /* size of the KV stage / sampler region */
-    int lz_off, lz_bytes;          /* landing zone of the next phase's weights: byte offset in dynamic shared memory (128-aligned), size (0 = off) */
     long long *prof; int prof_layer; /* optional: clock64 stamps of one layer, 16 slots per CTA (debug / profiles) */
 };
 
@@ -216,9 +215,6 @@ __device__ __forceinline__ void warp_dot2(const uint16_t *ra, const uint16_t *rb
 
 struct Seg3 { const uint16_t *w[3]; float *out[3]; int rows[3]; int n; };
 
-/* The dynamic index is deliberate: it keeps the phase descriptor (16 registers' worth) in local memory, one L1-resident
- * load per row pair, and leaves the registers to the eight 128-bit weight loads the streaming loop keeps in flight (with
- * constant indices ptxas holds Seg3 in registers and splits those loads into dependent groups of four: 12 % slower step). */
 __device__ __forceinline__ const uint16_t *seg_row(const Seg3 &s, int r, int cols, float *&dst) {
     int k = 0;
     while (k + 1 < s.n && r >= s.rows[k]) { r -= s.rows[k]; k++; }
@@ -253,9 +249,7 @@ __device__ __forceinline__ void prefetch_seg(const Seg3 &s, int cols, int cta, i
     if ((threadIdx.x >> 5) != FUSED_WARPS - 1) return;
     const int lane = threadIdx.x & 31;
     int base = 0;
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-        if (k >= s.n) break;
+    for (int k = 0; k < s.n; k++) {
         const int lo = r0 > base ? r0 - base : 0, hi = (r1 < base + s.rows[k] ? r1 : base + s.rows[k]) - base;
         if (hi > lo) {
             const char *p = reinterpret_cast<const char *>(s.w[k]) + (size_t)lo * cols * 2;
@@ -289,9 +283,9 @@ __device__ __forceinline__ void prefetch_swiglu(const uint16_t *gate, const uint
 }
 
 /* weight phase `k` of layer `l`: 0 QKV, 1 O, 2 gate+up (as two segments of I rows), 3 down */
-__device__ __forceinline__ bool phase_seg(const FusedArgs &a, const LmDev &lm, int l, int k, Seg3 &s, int &cols, const uint16_t *head_w, int head_rows) {
+__device__ __forceinline__ bool phase_seg(const FusedArgs &a, const LmDev &lm, int l, int k, Seg3 &s, int &cols) {
     if (l >= lm.layers) {
-        if (l == lm.layers && k == 0 && head_w) { s.n = 1; s.w[0] = head_w; s.out[0] = a.logits; s.rows[0] = head_rows; cols = lm.hidden; return true; }
+        if (l == lm.layers && k == 0 && a.head_w) { s.n = 1; s.w[0] = a.head_w; s.out[0] = a.logits; s.rows[0] = a.head_rows; cols = lm.hidden; return true; }
         return false;
     }
     const LmLayerDev &w = lm.layer[l];
@@ -305,7 +299,7 @@ __device__ __forceinline__ bool phase_seg(const FusedArgs &a, const LmDev &lm, i
 __device__ __forceinline__ void prefetch_phase(const FusedArgs &a, const LmDev &lm, int p, int cta, int ncta) {
     Seg3 s; int cols;
     if (a.flags & 1) return;
-    if (phase_seg(a, lm, p >> 2, p & 3, s, cols, a.head_w, a.head_rows)) prefetch_seg(s, cols, cta, ncta);
+    if (phase_seg(a, lm, p >> 2, p & 3, s, cols)) prefetch_seg(s, cols, cta, ncta);
 }
 
 /* gate/up: unit u = (gate row u, up row u) -> g[u] = silu(gate.x) * (up.x) */

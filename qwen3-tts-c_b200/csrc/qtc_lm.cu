@@ -175,13 +175,8 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     if (attn < 2 * FUSED_WARPS + FUSED_WARPS * lm->head_dim) attn = 2 * FUSED_WARPS + FUSED_WARPS * lm->head_dim;   /* cta_attention_warps: 16 (max, sum, out[hd]) triples */
     a.xs_floats = (vec + 3) & ~3;
     a.att_floats = (attn + 3) & ~3;
-    size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
+    const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
     if (smem > (size_t)g_fused_max_smem) { qtc_set_error("fused step: %zu bytes of shared memory needed, %d available", smem, g_fused_max_smem); return -1; }
-    /* landing zone of the next phase's weights: whatever shared memory is left (QTC_FUSED_FLAGS & 128: off) */
-    a.lz_off = (int)((smem + 127) & ~(size_t)127);
-    a.lz_bytes = ((g_fused_max_smem - a.lz_off) / 1024) * 1024;
-    if (a.lz_bytes < 16 * 1024 || (a.flags & 128)) a.lz_bytes = 0;
-    if (a.lz_bytes > 0) smem = (size_t)a.lz_off + a.lz_bytes;
     void *args[] = {&a, &sp};
     QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
     c->launches++;
