@@ -1,5 +1,5 @@
 """The reference's own CLI (unmodified c/main.c + c/*.c) with the backend switch linked in front of its outer API
-(adapter/qwen_tts_backend_switch.c, oracle/Makefile target _ref/qwen-tts-cuda) - SURVEY.md 8f rank 1.
+(adapter/qwen_tts_backend_switch.c, adapter/Makefile -> oracle/_ref/qwen-tts-cuda) - SURVEY.md 8f rank 1.
 CPU side: with the switch linked in, the CPU path still produces the plain CLI's bytes, and asking for cuda without a
 device falls back to it with a message.  GPU side: QWEN_TTS_BACKEND=cuda produces the same token trace through the
 stderr protocol the reference's scripts parse, and the same waveform within one 16-bit step."""
