@@ -379,6 +379,8 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")
     ap.add_argument("--greedy", action="store_true", help="greedy decoding (BASELINE config 1: --model 0.6b --frames 74 --greedy)")
     ap.add_argument("--codec-frames", type=int, default=0, help="> 0: codec decoder only on this many frames (BASELINE config 3: 3600)")
+    ap.add_argument("--stream-first", type=int, default=8, help="frames in the first PCM chunk of the streamed-latency utterances")
+    ap.add_argument("--stream-chunk", type=int, default=160, help="frames in later PCM chunks")
     ap.add_argument("--pieces", type=int, default=3, help="batched GEMM activations: 3 = exact bf16 split, 1 = bf16")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
@@ -426,7 +428,9 @@ def main():
     codes = np.zeros((frames, G), dtype=np.int32)
     perf = B.Perf()
 
-    def one_utterance():
+    lat = []
+
+    def one_utterance(record=True):
         ns, nf = C.c_int(0), C.c_int(0)
         t0 = time.perf_counter()
         ptr = cuda.qwen_tts_cuda_generate(ctx, CSV, b"aiden", b"english", C.byref(ns), B.iptr(codes), frames, C.byref(nf))
@@ -435,6 +439,8 @@ def main():
             raise RuntimeError("generate failed: " + cuda.qwen_tts_cuda_last_error().decode())
         cuda.qwen_tts_cuda_free_host(ptr)
         cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+        if record:
+            lat.append((perf.ttff_ms, perf.ttfa_ms, perf.frame_ms_p50, perf.frame_ms_p99, wall))
         return wall, perf.device_ms / 1e3, perf.talker_ms / 1e3, ns.value
 
     def barrier():
@@ -442,8 +448,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    # streaming latency (BASELINE config 2 is "streaming latency"): a few utterances with the chunked decode on (first PCM chunk
+    # after 8 frames, then 160-frame chunks), measured before the throughput region, which runs in the reference's
+    # decode-at-the-end order
+    cuda.qwen_tts_cuda_set_streaming(ctx, args.stream_first, args.stream_chunk)
+    for _ in range(3):
         one_utterance()
+    cuda.qwen_tts_cuda_set_streaming(ctx, 0, 0)
+    for _ in range(args.warmup):
+        one_utterance(record=False)
     cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
     launches0 = perf.kernel_launches
     sampler = ClockSampler(local)
@@ -453,7 +466,7 @@ def main():
     walls, devs, loops = [], [], []
     pcm_bytes = 0
     for _ in range(args.steps):
-        w, dv, lp, ns = one_utterance()
+        w, dv, lp, ns = one_utterance(record=False)
         walls.append(w); devs.append(dv); loops.append(lp)
         pcm_bytes = ns * 4
     barrier()
@@ -486,6 +499,14 @@ def main():
                            "mode": args.mode, "arith": "strict" if args.strict else "fast",
                            "l2": "weights per step (2.8 GB talker, 157 MB x16 sub-talker) exceed the 126 MB L2; the roofline probe flushes L2 between iterations"},
                 "ms_per_frame": sum(loops) / (args.steps * frames) * 1e3,
+                # streaming latency (config 2): device clock from the start of the prompt build, median over the timed utterances;
+                # see "note"
+                "latency": {"ttff_ms": float(np.median([x[0] for x in lat[1:]])), "ttfa_ms": float(np.median([x[1] for x in lat[1:]])),
+                            "frame_ms_p50": float(np.median([x[2] for x in lat[1:]])), "frame_ms_p99": float(np.median([x[3] for x in lat[1:]])),
+                            "first_chunk_frames": args.stream_first, "chunk_frames": args.stream_chunk,
+                            "e2e_streamed": frames * FRAME_S / float(np.median([x[4] for x in lat[1:]])),
+                            "note": "qwen_tts_cuda_set_streaming on: PCM chunks decoded between frames and copied to the host while the loop goes on; "
+                                    "value / e2e of this line are measured with it off (decode at the end, the reference's order)"},
                 "e2e": {"value": e2e, "unit": "audio_s/s", "h2d_bytes_per_step": len(CSV), "d2h_bytes_per_step": pcm_bytes + frames * G * 4},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "talker decode step (all kernels of one step)", "achieved": ach, "peak": hbm, "unit": "GB/s",

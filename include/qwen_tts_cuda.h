@@ -172,7 +172,14 @@ typedef struct {
     int    stop_step;
     long long kernel_launches;  /* kernels of this library launched so far on this context */
     double device_ms;           /* whole utterance on the device: prompt build .. last codec kernel (CUDA events) */
+    /* latency of the last qwen_tts_cuda_generate (device clock, from the start of the prompt build) */
+    double ttff_ms;             /* time to the first frame's 16 codes (prompt build + prefill + first frame) */
+    double ttfa_ms;             /* time to first audio: first PCM chunk in host memory (0 if the decode was not streamed) */
+    double frame_ms_p50, frame_ms_p99;   /* frame-to-frame interval (includes codec chunks that interleave) */
 } qtc_perf_t;
+
+/* streamed PCM: called as chunks land in host memory (see qwen_tts_cuda_set_stream_callback) */
+typedef void (*qtc_pcm_callback_t)(const float *pcm, int n_samples, int first_frame, void *user);
 
 typedef struct qtc_ctx qtc_ctx_t;   /* opaque device-side model + state */
 
@@ -234,6 +241,22 @@ int  qwen_tts_cuda_generate_frames(qtc_ctx_t *ctx,
 float *qwen_tts_cuda_generate(qtc_ctx_t *ctx, const char *text, const char *speaker,
                               const char *language, int *out_samples,
                               int *out_codes, int max_codes, int *out_n_frames);
+
+/* ---- streaming decode ---------------------------------
+ * The C reference decodes once after the last frame (c/qwen_tts.c:1399-1420); the Python package streams 300-frame chunks
+ * with 25 frames of left context (qwen_tts/core/tokenizer_12hz/modeling_qwen3_tts_tokenizer_v2.py:886-896).  Here every
+ * layer's causality is used for an EXACT chunked decode: streamed PCM equals the one-shot PCM bit for bit.
+ * With qwen_tts_cuda_set_streaming(ctx, first, chunk), qwen_tts_cuda_generate decodes chunks of finished frames between
+ * two frames of the loop (first chunk `first` frames, later ones `chunk`) and copies their PCM to the host while the loop
+ * goes on: time to first audio is prefill + `first` frames + one small decode instead of the whole utterance.  Every chunk
+ * pays the decoder's fixed cost once more, so throughput is a few per cent lower than with the default, chunk_frames <= 0:
+ * the reference's decode-at-the-end order. */
+int  qwen_tts_cuda_set_streaming(qtc_ctx_t *ctx, int first_frames, int chunk_frames);
+void qwen_tts_cuda_set_stream_callback(qtc_ctx_t *ctx, qtc_pcm_callback_t cb, void *user);
+/* stage-level: a decode session of up to max_frames frames fed chunk by chunk.  push: codes [n, num_quantizers] (host) are
+ * the NEXT n frames, pcm_out (host) receives exactly their n * 1920 samples; returns the sample count or -1. */
+int  qwen_tts_cuda_codec_stream_begin(qtc_ctx_t *ctx, int max_frames);
+int  qwen_tts_cuda_codec_stream_push(qtc_ctx_t *ctx, const int *codes, int n, float *pcm_out);
 
 /* ---- batched, request-sharded variant (BASELINE configs 4-5) ---------------
  * batch <= 64 independent utterances decoded in lock-step on this GPU (more: call again, or shard over GPUs);

@@ -108,6 +108,7 @@ static int alloc_lm_buffers(qtc_ctx *c, LmBuffers *b, const LmDev *lm) {
 extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     if (!c) return;
     cudaStreamSynchronize(c->stream);
+    if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->g_front) cudaGraphExecDestroy(c->g_front);
     if (c->g_talker) cudaGraphExecDestroy(c->g_talker);
     qtc_batch_release(c);
@@ -118,7 +119,10 @@ extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     cudaFree(c->codes); cudaFree(c->trailing); cudaFree(c->prefill);
     cudaFreeHost(c->state_host); cudaFreeHost(c->codes_host); cudaFreeHost(c->host_stage);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
-    cudaStreamDestroy(c->stream);
+    cudaFree(c->pcm_dev); cudaFreeHost(c->first_pcm_host);
+    for (cudaEvent_t e : c->frame_ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->chunk_ev) cudaEventDestroy(e);
+    cudaStreamDestroy(c->stream); cudaStreamDestroy(c->stream2);
     delete c;
 }
 
@@ -134,13 +138,18 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     memset(&c->tk, 0, sizeof(c->tk)); memset(&c->st, 0, sizeof(c->st)); memset(&c->perf, 0, sizeof(c->perf));
     memset(&c->talker, 0, sizeof(c->talker)); memset(&c->sub, 0, sizeof(c->sub));
     qwen_tts_cuda_default_params(&c->params);
+    /* two streams: the frame loop with the codec chunks inline (qtc_generate.cu:push_chunk says why), and the copies of
+     * finished PCM chunks to the host */
     bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) == cudaSuccess &&
               cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess &&
               cudaEventCreate(&c->ev2) == cudaSuccess && cudaEventCreate(&c->ev3) == cudaSuccess;
     c->host_stage_bytes = 1 << 20;
     ok = ok && cudaMallocHost(&c->state_host, sizeof(GenState)) == cudaSuccess &&
          cudaMallocHost(&c->host_stage, c->host_stage_bytes) == cudaSuccess;
     c->codes_host = NULL;
+    c->cstream = c->stream;
+    c->pcm_dev = NULL; c->pcm_cap = 0; c->first_pcm_host = NULL; c->stream_first = 8; c->stream_chunk = 0;      /* decode at the end unless qwen_tts_cuda_set_streaming asks for chunks */ c->stream_cb = NULL; c->stream_user = NULL;
     if (!ok) { qtc_set_error("stream/event/pinned allocation failed"); qwen_tts_cuda_release(c); return NULL; }
     if (c->G < 1 || c->G > QTC_MAX_GROUPS) { qtc_set_error("num_code_groups %d out of range", c->G); qwen_tts_cuda_release(c); return NULL; }
 

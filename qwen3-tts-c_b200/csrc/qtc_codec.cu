@@ -37,6 +37,12 @@ struct CodecDev {
     float *ws; size_t ws_bytes;
     int *codes_dev; int codes_cap;
     float *rope_cs, *rope_sn; int rope_T;
+    size_t ws_half;
+    /* streaming session (qtc_codec_stream_*): frames decoded so far, capacity, conv-stack context in frames */
+    int s_T, s_cap, s_ctx, s_max;
+    float *s_tf;                                    /* [cap, latent] transformer output rows, time-major */
+    float *s_k[QTC_MAX_CODEC_LAYERS], *s_v[QTC_MAX_CODEC_LAYERS];   /* [cap, kv_heads*hd] per layer, by absolute position */
+    int *s_codes;                                   /* [cap, nq] codes pushed so far */
 };
 
 /* transposed conv weight [cin, cout, k] -> rows (oc*s + p) x (ic*J + j): tap p + (J-1-j)*s (0 if >= k).
@@ -126,9 +132,11 @@ CodecDev *qtc_codec_upload(qtc_ctx *c, const qtc_codec_t *k) {
     return d;
 }
 
+static void stream_free(CodecDev *d);
 void qtc_codec_release(CodecDev *d) {
     if (!d) return;
     cudaFree(d->ws); cudaFree(d->codes_dev); cudaFree(d->rope_cs); cudaFree(d->rope_sn);
+    stream_free(d);
     delete d;
 }
 
@@ -157,15 +165,15 @@ int qtc_conv(qtc_ctx *c, float *out, const float *in, const float *w, const floa
     if (w64 < w96 && w64 < w128) {
         const int sm = conv_smem_bytes(64, K, dil);
         if (sm > 200 * 1024) { qtc_set_error("conv: dilation too large for the tile"); return -1; }
-        k_conv_tile<64><<<dim3(gx, w64 / 64), 128, sm, c->stream>>>(a);
+        k_conv_tile<64><<<dim3(gx, w64 / 64), 128, sm, c->cstream>>>(a);
     } else if (w96 < w128) {
         const int sm = conv_smem_bytes(96, K, dil);
         if (sm > 200 * 1024) { qtc_set_error("conv: dilation too large for the tile"); return -1; }
-        k_conv_tile<96><<<dim3(gx, w96 / 96), 192, sm, c->stream>>>(a);
+        k_conv_tile<96><<<dim3(gx, w96 / 96), 192, sm, c->cstream>>>(a);
     } else {
         const int sm = conv_smem_bytes(128, K, dil);
         if (sm > 200 * 1024) { qtc_set_error("conv: dilation too large for the tile"); return -1; }
-        k_conv_tile<128><<<dim3(gx, w128 / 128), 256, sm, c->stream>>>(a);
+        k_conv_tile<128><<<dim3(gx, w128 / 128), 256, sm, c->cstream>>>(a);
     }
     CLAUNCH(c);
     return 0;
@@ -177,30 +185,30 @@ int qtc_sgemm(qtc_ctx *c, float *C, const float *A, const float *B, int M, int N
     if (M <= 0 || N <= 0) return 0;
     GemmEpi e;
     e.bias = bias; e.scale = scale; e.res = res; e.gelu = gelu; e.transposed = transposed; e.ldc = ldc;
-    k_sgemm_nt<<<dim3((N + SG_BN - 1) / SG_BN, (M + SG_BM - 1) / SG_BM), 256, 0, c->stream>>>(C, A, B, M, N, K, e);
+    k_sgemm_nt<<<dim3((N + SG_BN - 1) / SG_BN, (M + SG_BM - 1) / SG_BM), 256, 0, c->cstream>>>(C, A, B, M, N, K, e);
     CLAUNCH(c);
     return 0;
 }
 
 int qtc_conv_grouped(qtc_ctx *c, float *out, const float *in, const float *w, const float *bias, int cin, int cout, int K, int L, int dil, int groups) {
-    k_conv_grouped<<<dim3((L + 127) / 128, cout), 128, 0, c->stream>>>(out, in, w, bias, cin, cout, K, L, dil, groups);
+    k_conv_grouped<<<dim3((L + 127) / 128, cout), 128, 0, c->cstream>>>(out, in, w, bias, cin, cout, K, L, dil, groups);
     CLAUNCH(c);
     return 0;
 }
 int qtc_snake(qtc_ctx *c, float *out, const float *x, const float *alpha, const float *inv_beta, int C, int L) {
     const size_t n = (size_t)C * L;
-    k_snake<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(out, x, alpha, inv_beta, C, (size_t)L);
+    k_snake<<<(unsigned)((n + 255) / 256), 256, 0, c->cstream>>>(out, x, alpha, inv_beta, C, (size_t)L);
     CLAUNCH(c);
     return 0;
 }
 
 static int transpose(qtc_ctx *c, float *dst, const float *src, int rows, int cols) {
-    k_transpose<<<dim3((cols + 31) / 32, (rows + 31) / 32), dim3(32, 8), 0, c->stream>>>(dst, src, rows, cols);
+    k_transpose<<<dim3((cols + 31) / 32, (rows + 31) / 32), dim3(32, 8), 0, c->cstream>>>(dst, src, rows, cols);
     CLAUNCH(c);
     return 0;
 }
 static int row_norm(qtc_ctx *c, float *out, const float *x, const float *w, const float *b, int rows, int n, float eps, int mode) {
-    k_row_norm<<<rows, 256, 0, c->stream>>>(out, x, w, b, n, eps, mode);
+    k_row_norm<<<rows, 256, 0, c->cstream>>>(out, x, w, b, n, eps, mode);
     CLAUNCH(c);
     return 0;
 }
@@ -230,29 +238,54 @@ static size_t codec_half_bytes(const qtc_codec_t *k, int T) {
     return need * 4 + 64 * 256;       /* + alignment slack for the bump allocator */
 }
 
-/* codes_dev [T, nq] on device.  Returns malloc'd host PCM (caller frees); *dev_out (optional) receives the
- * device pointer of the PCM inside the workspace (valid until the next decode). */
-float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_samples, float **dev_out) {
+/* ---- streaming state ------------------------------------------------------------------------------------------
+ * Every layer of the decoder is causal, so frames can be decoded in chunks with EXACTLY the one-shot result:
+ *   - the transformer keeps its per-layer K (after RoPE) and V rows by absolute position and attends over the window of
+ *     72 frames across chunk borders; its output rows are kept time-major in `tf`;
+ *   - everything after it is convolutions whose total receptive field is < 10 frames (ctx_frames below): a chunk re-runs
+ *     the conv stack on [T - ctx, T + n) and drops the first ctx frames of PCM.  Products and summation order of every kept
+ *     sample are those of the one-shot decode (accumulation order in k_conv_tile / k_sgemm_nt does not depend on the tile
+ *     position), so streamed PCM == one-shot PCM bit for bit (tests/test_gpu_stream.py).
+ * The Python reference streams 300-frame chunks with 25 frames of left context and accepts the seam
+ * (qwen_tts/core/tokenizer_12hz/modeling_qwen3_tts_tokenizer_v2.py:886-896); the C reference decodes once at the end. */
+static int ctx_frames(const qtc_codec_t *k) {
+    double f = 0.0, rate = 1.0;
+    for (int s = 0; s < 2; s++) { rate *= k->upsampling_ratios[s]; f += 6.0 / rate; }          /* ConvNeXt dwconv k=7 (the k=s transposed conv has no halo) */
+    f += 6.0 / rate;                                                                             /* vocoder pre-conv k=7 */
+    for (int b = 0; b < 4; b++) { f += 1.0 / rate; rate *= k->upsample_rates[b]; f += (6.0 + 18.0 + 54.0) / rate; }   /* tconv k=2r: one input back; ResUnits dil 1,3,9 */
+    f += 6.0 / rate;                                                                             /* final conv k=7 */
+    return (int)ceil(f) + 1;
+}
+
+static void stream_free(CodecDev *d) {
+    cudaFree(d->s_tf); cudaFree(d->s_codes);
+    for (int l = 0; l < QTC_MAX_CODEC_LAYERS; l++) { cudaFree(d->s_k[l]); cudaFree(d->s_v[l]); d->s_k[l] = d->s_v[l] = NULL; }
+    d->s_tf = NULL; d->s_codes = NULL; d->s_cap = 0; d->s_T = 0;
+}
+
+/* start a decode of up to max_frames frames (one-shot decodes are a session of one chunk) */
+int qtc_codec_stream_begin(qtc_ctx *c, int max_frames) {
     CodecDev *d = c->codec;
-    if (out_samples) *out_samples = 0;
-    if (!d || !codes_dev || T <= 0 || !out_samples) return NULL;
+    if (!d || max_frames <= 0) { qtc_set_error("codec stream: no codec / bad frame count"); return -1; }
     const qtc_codec_t *k = &d->h;
-    const int lat = k->latent, Hc = k->hidden, I = k->intermediate, nh = k->heads, nkv = k->kv_heads, hd = Hc / nh;
-    const int qd = nh * hd, kvd = nkv * hd, vq = k->codebook_dim / 2, half = lat / 2;
-    if (k->sliding_window > 128 || hd > 256 || hd % 4) { qtc_set_error("codec: window %d / head_dim %d unsupported", k->sliding_window, hd); return NULL; }
-    if (k->codebook_dim != half * 1 && k->codebook_dim != lat / 2) { qtc_set_error("codec: codebook_dim must equal latent/2 (SURVEY 7.0)"); return NULL; }
-    const size_t half_bytes = (codec_half_bytes(k, T) + 255) & ~(size_t)255;
-    const size_t need = 2 * half_bytes;
-    if (need > d->ws_bytes) {
-        cudaStreamSynchronize(c->stream);
-        cudaFree(d->ws); d->ws = NULL; d->ws_bytes = 0;
-        if (cudaMalloc(&d->ws, need) != cudaSuccess) { qtc_set_error("codec: workspace of %.1f MB failed", need / 1e6); return NULL; }
-        d->ws_bytes = need;
+    const int Hc = k->hidden, hd = Hc / k->heads, kvd = k->kv_heads * hd;
+    if (k->sliding_window > 128 || hd > 256 || hd % 4) { qtc_set_error("codec: window %d / head_dim %d unsupported", k->sliding_window, hd); return -1; }
+    if (k->codebook_dim != k->latent / 2) { qtc_set_error("codec: codebook_dim must equal latent/2 (SURVEY 7.0)"); return -1; }
+    if (max_frames > d->s_cap) {
+        cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
+        stream_free(d);
+        const int cap = max_frames + 64;
+        bool ok = cudaMalloc(&d->s_tf, (size_t)cap * k->latent * 4) == cudaSuccess && cudaMalloc(&d->s_codes, (size_t)cap * k->num_quantizers * 4) == cudaSuccess;
+        for (int l = 0; l < k->layers && ok; l++)
+            ok = cudaMalloc(&d->s_k[l], (size_t)cap * kvd * 4) == cudaSuccess && cudaMalloc(&d->s_v[l], (size_t)cap * kvd * 4) == cudaSuccess;
+        if (!ok) { stream_free(d); qtc_set_error("codec stream: state for %d frames failed", cap); return -1; }
+        d->s_cap = cap;
     }
-    if (T > d->rope_T) {          /* codec RoPE: theta 10000 hard-coded (c/qwen_tts_codec.c:309), host libm */
-        cudaStreamSynchronize(c->stream);
+    if (max_frames > d->rope_T) {          /* codec RoPE: theta 10000 hard-coded (c/qwen_tts_codec.c:309), host libm */
+        cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
         cudaFree(d->rope_cs); cudaFree(d->rope_sn);
-        const int n = T + 256;
+        d->rope_cs = d->rope_sn = NULL; d->rope_T = 0;
+        const int n = max_frames + 256;
         std::vector<float> cs((size_t)n * hd), sn((size_t)n * hd);
         for (int t = 0; t < n; t++)
             for (int i = 0; i < hd / 2; i++) {
@@ -260,64 +293,102 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
                 cs[(size_t)t * hd + i] = cs[(size_t)t * hd + i + hd / 2] = cosf(ang);
                 sn[(size_t)t * hd + i] = sn[(size_t)t * hd + i + hd / 2] = sinf(ang);
             }
-        if (cudaMalloc(&d->rope_cs, cs.size() * 4) != cudaSuccess || cudaMalloc(&d->rope_sn, sn.size() * 4) != cudaSuccess) return NULL;
+        if (cudaMalloc(&d->rope_cs, cs.size() * 4) != cudaSuccess || cudaMalloc(&d->rope_sn, sn.size() * 4) != cudaSuccess) { qtc_set_error("codec: rope tables"); return -1; }
         cudaMemcpy(d->rope_cs, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice);
         cudaMemcpy(d->rope_sn, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice);
         d->rope_T = n;
     }
-#define CK(x) do { if ((x) != 0) return NULL; } while (0)
+    d->s_T = 0; d->s_max = max_frames;
+    d->s_ctx = ctx_frames(k);
+    return 0;
+}
+
+/* workspace for chunks of at most `chunk` new frames; call before enqueueing chunks that overlap other work */
+int qtc_codec_stream_reserve(qtc_ctx *c, int chunk) {
+    CodecDev *d = c->codec;
+    const size_t half_bytes = (codec_half_bytes(&d->h, chunk + d->s_ctx + 2) + 255) & ~(size_t)255;
+    if (2 * half_bytes > d->ws_bytes) {
+        cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
+        cudaFree(d->ws); d->ws = NULL; d->ws_bytes = 0;
+        if (cudaMalloc(&d->ws, 2 * half_bytes) != cudaSuccess) { qtc_set_error("codec: workspace of %.1f MB failed", 2 * half_bytes / 1e6); return -1; }
+        d->ws_bytes = 2 * half_bytes;
+    }
+    d->ws_half = d->ws_bytes / 2;
+    return 0;
+}
+
+/* decode the next n frames.  codes_dev [n, nq] (device) are the codes of frames [T, T+n).  All work is enqueued on c->cstream.
+ * *pcm_dev receives the device pointer of the n*1920 new samples (inside the workspace: valid until the next push). */
+int qtc_codec_stream_push(qtc_ctx *c, const int *codes_dev, int n, float **pcm_dev) {
+    CodecDev *d = c->codec;
+    if (!d || !codes_dev || n <= 0) return -1;
+    const qtc_codec_t *k = &d->h;
+    const int T0 = d->s_T, T1 = T0 + n;
+    if (T1 > d->s_max || T1 > d->s_cap) { qtc_set_error("codec stream: %d frames pushed, session opened for %d", T1, d->s_max); return -1; }
+    const int lat = k->latent, Hc = k->hidden, I = k->intermediate, nh = k->heads, nkv = k->kv_heads, hd = Hc / nh;
+    const int qd = nh * hd, kvd = nkv * hd, vq = k->codebook_dim / 2, half = lat / 2, nq = k->num_quantizers;
+    if (qtc_codec_stream_reserve(c, n)) return -1;
+    const size_t half_bytes = d->ws_half;
+    cudaStream_t st = c->cstream;
+#define CK(x) do { if ((x) != 0) return -1; } while (0)
+    if (cudaMemcpyAsync(d->s_codes + (size_t)T0 * nq, codes_dev, (size_t)n * nq * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess) { qtc_set_error("codec stream: codes copy"); return -1; }
     Arena ar = {(char *)d->ws, 0, half_bytes};
-    /* ---- RVQ + pre-conv + transformer ---- */
-    float *sem = ar.take((size_t)T * vq), *aco = ar.take((size_t)T * vq);
-    float *h0 = ar.take((size_t)half * T), *pre = ar.take((size_t)lat * T), *seq = ar.take((size_t)T * lat);
-    float *x = ar.take((size_t)T * Hc), *xn = ar.take((size_t)T * Hc), *q = ar.take((size_t)T * qd), *kk = ar.take((size_t)T * kvd);
-    float *v = ar.take((size_t)T * kvd), *att = ar.take((size_t)T * qd), *g = ar.take((size_t)T * I), *u = ar.take((size_t)T * I);
+    /* ---- RVQ + pre-conv (k = 3: two frames of left context, recomputed from the codes) + transformer on the n new frames ---- */
+    const int r0 = T0 >= 2 ? T0 - 2 : 0, m = T1 - r0, skip = T0 - r0;
+    float *sem = ar.take((size_t)m * vq), *aco = ar.take((size_t)m * vq);
+    float *h0 = ar.take((size_t)half * m), *pre = ar.take((size_t)lat * m), *seq = ar.take((size_t)m * lat);
+    float *x = ar.take((size_t)n * Hc), *xn = ar.take((size_t)n * Hc), *q = ar.take((size_t)n * qd);
+    float *att = ar.take((size_t)n * qd), *g = ar.take((size_t)n * I), *u = ar.take((size_t)n * I);
+    if (ar.off > half_bytes) { qtc_set_error("codec: workspace underestimated (transformer)"); return -1; }
     {
         RvqArgs ra;
-        for (int qi = 0; qi < k->num_quantizers; qi++) ra.cb[qi] = d->cb[qi];
-        ra.codes = codes_dev; ra.sem = sem; ra.aco = aco; ra.T = T; ra.nq = k->num_quantizers; ra.vq = vq; ra.cb_size = k->codebook_size;
-        k_rvq_gather<<<T, 128, 0, c->stream>>>(ra);
+        for (int qi = 0; qi < nq; qi++) ra.cb[qi] = d->cb[qi];
+        ra.codes = d->s_codes + (size_t)r0 * nq; ra.sem = sem; ra.aco = aco; ra.T = m; ra.nq = nq; ra.vq = vq; ra.cb_size = k->codebook_size;
+        k_rvq_gather<<<m, 128, 0, st>>>(ra);
         c->launches++;
     }
-    CK(qtc_sgemm(c, h0, sem, d->sem_proj, T, half, vq, NULL, NULL, NULL, 0, 1, T));           /* -> [half, T] */
-    CK(qtc_sgemm(c, h0, aco, d->aco_proj, T, half, vq, NULL, NULL, h0, 0, 1, T));
-    CK(qtc_conv(c, pre, h0, d->pre_w, d->pre_b, NULL, NULL, NULL, k->codebook_dim, lat, 3, 1, T, 1));
-    CK(transpose(c, seq, pre, lat, T));                                                         /* [T, lat] */
-    CK(qtc_sgemm(c, x, seq, d->in_w, T, Hc, lat, d->in_b, NULL, NULL, 0, 0, Hc));
+    CK(qtc_sgemm(c, h0, sem, d->sem_proj, m, half, vq, NULL, NULL, NULL, 0, 1, m));           /* -> [half, m] */
+    CK(qtc_sgemm(c, h0, aco, d->aco_proj, m, half, vq, NULL, NULL, h0, 0, 1, m));
+    CK(qtc_conv(c, pre, h0, d->pre_w, d->pre_b, NULL, NULL, NULL, k->codebook_dim, lat, 3, 1, m, 1));
+    CK(transpose(c, seq, pre, lat, m));                                                         /* [m, lat] */
+    CK(qtc_sgemm(c, x, seq + (size_t)skip * lat, d->in_w, n, Hc, lat, d->in_b, NULL, NULL, 0, 0, Hc));
     const float scale = 1.0f / sqrtf((float)hd);
     for (int l = 0; l < k->layers; l++) {
         const CodecLayerDev *w = &d->layer[l];
-        CK(row_norm(c, xn, x, w->in_norm, NULL, T, Hc, k->rms_eps, 0));
-        CK(qtc_sgemm(c, q, xn, w->wq, T, qd, Hc, NULL, NULL, NULL, 0, 0, qd));
-        CK(qtc_sgemm(c, kk, xn, w->wk, T, kvd, Hc, NULL, NULL, NULL, 0, 0, kvd));
-        CK(qtc_sgemm(c, v, xn, w->wv, T, kvd, Hc, NULL, NULL, NULL, 0, 0, kvd));
-        k_rope_rows<<<T, 256, 0, c->stream>>>(q, kk, d->rope_cs, d->rope_sn, T, nh, nkv, hd);
+        float *kk = d->s_k[l] + (size_t)T0 * kvd, *v = d->s_v[l] + (size_t)T0 * kvd;          /* rows of this chunk in the persistent caches */
+        CK(row_norm(c, xn, x, w->in_norm, NULL, n, Hc, k->rms_eps, 0));
+        CK(qtc_sgemm(c, q, xn, w->wq, n, qd, Hc, NULL, NULL, NULL, 0, 0, qd));
+        CK(qtc_sgemm(c, kk, xn, w->wk, n, kvd, Hc, NULL, NULL, NULL, 0, 0, kvd));
+        CK(qtc_sgemm(c, v, xn, w->wv, n, kvd, Hc, NULL, NULL, NULL, 0, 0, kvd));
+        k_rope_rows<<<n, 256, 0, st>>>(q, kk, d->rope_cs + (size_t)T0 * hd, d->rope_sn + (size_t)T0 * hd, n, nh, nkv, hd);
         c->launches++;
-        k_window_attn<<<(T * nh + 3) / 4, 128, 0, c->stream>>>(att, q, kk, v, T, nh, nkv, hd, k->sliding_window, scale);
+        k_window_attn<<<(n * nh + 3) / 4, 128, 0, st>>>(att, q, d->s_k[l], d->s_v[l], n, nh, nkv, hd, k->sliding_window, scale, T0);
         c->launches++;
-        CK(qtc_sgemm(c, x, att, w->wo, T, Hc, qd, NULL, w->attn_scale, x, 0, 0, Hc));
-        CK(row_norm(c, xn, x, w->post_norm, NULL, T, Hc, k->rms_eps, 0));
-        CK(qtc_sgemm(c, g, xn, w->gate, T, I, Hc, NULL, NULL, NULL, 0, 0, I));
-        CK(qtc_sgemm(c, u, xn, w->up, T, I, Hc, NULL, NULL, NULL, 0, 0, I));
-        k_swiglu_mul<<<(unsigned)(((size_t)T * I + 255) / 256), 256, 0, c->stream>>>(g, u, (size_t)T * I);
+        CK(qtc_sgemm(c, x, att, w->wo, n, Hc, qd, NULL, w->attn_scale, x, 0, 0, Hc));
+        CK(row_norm(c, xn, x, w->post_norm, NULL, n, Hc, k->rms_eps, 0));
+        CK(qtc_sgemm(c, g, xn, w->gate, n, I, Hc, NULL, NULL, NULL, 0, 0, I));
+        CK(qtc_sgemm(c, u, xn, w->up, n, I, Hc, NULL, NULL, NULL, 0, 0, I));
+        k_swiglu_mul<<<(unsigned)(((size_t)n * I + 255) / 256), 256, 0, st>>>(g, u, (size_t)n * I);
         c->launches++;
-        CK(qtc_sgemm(c, x, g, w->down, T, Hc, I, NULL, w->mlp_scale, x, 0, 0, Hc));
+        CK(qtc_sgemm(c, x, g, w->down, n, Hc, I, NULL, w->mlp_scale, x, 0, 0, Hc));
     }
-    if (d->final_norm) CK(row_norm(c, x, x, d->final_norm, NULL, T, Hc, k->rms_eps, 0));
-    CK(qtc_sgemm(c, pre, x, d->out_w, T, lat, Hc, d->out_b, NULL, NULL, 0, 1, T));            /* -> [lat, T] */
+    if (d->final_norm) CK(row_norm(c, x, x, d->final_norm, NULL, n, Hc, k->rms_eps, 0));
+    CK(qtc_sgemm(c, d->s_tf + (size_t)T0 * lat, x, d->out_w, n, lat, Hc, d->out_b, NULL, NULL, 0, 0, lat));   /* time-major rows [T0, T1) */
 
-    /* ---- 2 x (transposed conv + ConvNeXt) ---- */
-    int L = T, side = 1;                 /* the transformer stage used half 0; `side` = half the next stage writes */
-    float *cur = pre;
+    /* ---- conv stack on the window [w0, T1): 2 x (transposed conv + ConvNeXt), vocoder ---- */
+    const int w0 = T0 > d->s_ctx ? T0 - d->s_ctx : 0, W = T1 - w0;
+    float *cur = pre;                                                                           /* half 0, free again: [lat, W] */
+    CK(transpose(c, cur, d->s_tf + (size_t)w0 * lat, W, lat));
+    int L = W, side = 1;                 /* the transformer stage used half 0; `side` = half the next stage writes */
     auto half_arena = [&](int sd) { Arena a = {(char *)d->ws + (size_t)sd * half_bytes, 0, half_bytes}; return a; };
     for (int s = 0; s < 2; s++) {
         const int f = k->upsampling_ratios[s], Lo = L * f;
         Arena a2 = half_arena(side);
         float *up = a2.take((size_t)lat * Lo), *cv = a2.take((size_t)lat * Lo), *ld = a2.take((size_t)Lo * lat), *pw = a2.take((size_t)Lo * 4 * lat);
-        if (a2.off > half_bytes) { qtc_set_error("codec: workspace underestimated (upsample)"); return NULL; }
+        if (a2.off > half_bytes) { qtc_set_error("codec: workspace underestimated (upsample)"); return -1; }
         CK(tconv(c, up, cur, d->up_tconv[s], NULL, NULL, L));
         const ConvNextDev *b = &d->cnx[s];
-        k_dwconv<<<dim3((Lo + 255) / 256, lat), 256, 0, c->stream>>>(cv, up, b->dw_w, b->dw_b, lat, 7, Lo, 1);
+        k_dwconv<<<dim3((Lo + 255) / 256, lat), 256, 0, st>>>(cv, up, b->dw_w, b->dw_b, lat, 7, Lo, 1);
         c->launches++;
         CK(transpose(c, ld, cv, lat, Lo));                                                      /* [Lo, lat] */
         CK(row_norm(c, ld, ld, b->norm_w, b->norm_b, Lo, lat, 1e-6f, 1));
@@ -325,11 +396,10 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
         CK(qtc_sgemm(c, up, pw, b->pw2_w, Lo, lat, 4 * lat, b->pw2_b, b->gamma, up, 0, 1, Lo)); /* h[c,t] += gamma*(..) */
         cur = up; L = Lo; side ^= 1;
     }
-    /* ---- vocoder ---- */
     int dim = k->decoder_dim;
     Arena a3 = half_arena(side);
     float *voc = a3.take((size_t)dim * L);
-    if (a3.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder pre-conv)"); return NULL; }
+    if (a3.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder pre-conv)"); return -1; }
     CK(qtc_conv(c, voc, cur, d->voc_pre_w, d->voc_pre_b, NULL, NULL, NULL, lat, dim, 7, 1, L, 1));
     side ^= 1;
     static const int dil[3] = {1, 3, 9};
@@ -337,7 +407,7 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
         const int r = k->upsample_rates[b], od = dim / 2, Lo = L * r;
         Arena a4 = half_arena(side);
         float *hh = a4.take((size_t)od * Lo), *t1 = a4.take((size_t)od * Lo);
-        if (a4.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder)"); return NULL; }
+        if (a4.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder)"); return -1; }
         CK(tconv(c, hh, voc, d->block[b].tc, d->block[b].alpha, d->block[b].beta, L));
         for (int uu = 0; uu < 3; uu++) {
             const ResUnitDev *ru = &d->block[b].ru[uu];
@@ -348,14 +418,29 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
     }
     Arena a5 = half_arena(side);
     float *wav = a5.take((size_t)L);
-    k_conv_to_mono<<<(L + 255) / 256, 256, 0, c->stream>>>(wav, voc, d->fin_w, d->fin_b, d->fin_alpha, d->fin_beta, dim, 7, L, 1);
+    k_conv_to_mono<<<(L + 255) / 256, 256, 0, st>>>(wav, voc, d->fin_w, d->fin_b, d->fin_alpha, d->fin_beta, dim, 7, L, 1);
     c->launches++;
 #undef CK
-    cudaEventRecord(c->ev3, c->stream);              /* end of device work; what follows is the D2H of the PCM */
+    d->s_T = T1;
+    if (pcm_dev) *pcm_dev = wav + (size_t)(T0 - w0) * (L / W);
+    return n * (L / W);
+}
+
+/* codes_dev [T, nq] on device.  Returns malloc'd host PCM (caller frees); *dev_out (optional) receives the
+ * device pointer of the PCM inside the workspace (valid until the next decode).  A session of one chunk. */
+float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_samples, float **dev_out) {
+    CodecDev *d = c->codec;
+    if (out_samples) *out_samples = 0;
+    if (!d || !codes_dev || T <= 0 || !out_samples) return NULL;
+    float *wav = NULL;
+    if (qtc_codec_stream_begin(c, T)) return NULL;
+    const int L = qtc_codec_stream_push(c, codes_dev, T, &wav);
+    if (L <= 0) return NULL;
+    cudaEventRecord(c->ev3, c->cstream);             /* end of device work; what follows is the D2H of the PCM */
     float *host = (float *)malloc((size_t)L * 4);
     if (!host) return NULL;
-    if (cudaMemcpyAsync(host, wav, (size_t)L * 4, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
-        cudaStreamSynchronize(c->stream) != cudaSuccess) {
+    if (cudaMemcpyAsync(host, wav, (size_t)L * 4, cudaMemcpyDeviceToHost, c->cstream) != cudaSuccess ||
+        cudaStreamSynchronize(c->cstream) != cudaSuccess) {
         qtc_set_error("codec: device error %s", cudaGetErrorString(cudaGetLastError()));
         free(host);
         return NULL;
@@ -365,6 +450,36 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
     return host;
 }
 
+/* ---- streaming through the C ABI (host buffers): SURVEY.md 8f rank 3 ------------------------------------------------ */
+extern "C" int qwen_tts_cuda_codec_stream_begin(qtc_ctx_t *c, int max_frames) {
+    if (!c || !c->codec) { qtc_set_error("codec_stream_begin: context has no codec"); return -1; }
+    return qtc_codec_stream_begin(c, max_frames);
+}
+/* codes [n, nq] (host): the next n frames; pcm_out (host, n * 1920 floats) receives exactly their samples.  Returns the
+ * sample count or -1. */
+extern "C" int qwen_tts_cuda_codec_stream_push(qtc_ctx_t *c, const int *codes, int n, float *pcm_out) {
+    if (!c || !c->codec) { qtc_set_error("codec_stream_push: context has no codec"); return -1; }
+    if (!codes || n <= 0 || !pcm_out) { qtc_set_error("codec_stream_push: null or empty argument"); return -1; }
+    CodecDev *d = c->codec;
+    const int nq = d->h.num_quantizers;
+    if (n > d->codes_cap) {
+        cudaStreamSynchronize(c->cstream);
+        cudaFree(d->codes_dev);
+        d->codes_dev = NULL; d->codes_cap = 0;
+        if (cudaMalloc(&d->codes_dev, (size_t)(n + 64) * nq * 4) != cudaSuccess) { qtc_set_error("codec: codes buffer"); return -1; }
+        d->codes_cap = n + 64;
+    }
+    if (cudaMemcpyAsync(d->codes_dev, codes, (size_t)n * nq * 4, cudaMemcpyHostToDevice, c->cstream) != cudaSuccess) return -1;
+    float *wav = NULL;
+    const int L = qtc_codec_stream_push(c, d->codes_dev, n, &wav);
+    if (L <= 0) return -1;
+    if (cudaMemcpyAsync(pcm_out, wav, (size_t)L * 4, cudaMemcpyDeviceToHost, c->cstream) != cudaSuccess || cudaStreamSynchronize(c->cstream) != cudaSuccess) {
+        qtc_set_error("codec stream: device error %s", cudaGetErrorString(cudaGetLastError()));
+        return -1;
+    }
+    return L;
+}
+
 extern "C" float *qwen_tts_cuda_codec_decode(qtc_ctx_t *c, const int *codes, int T, int *out_samples) {
     if (out_samples) *out_samples = 0;
     if (!c || !c->codec) { qtc_set_error("codec_decode: context has no codec"); return NULL; }
@@ -372,15 +487,16 @@ extern "C" float *qwen_tts_cuda_codec_decode(qtc_ctx_t *c, const int *codes, int
     CodecDev *d = c->codec;
     const int nq = d->h.num_quantizers;
     if (T > d->codes_cap) {
-        cudaStreamSynchronize(c->stream);
+        cudaStreamSynchronize(c->cstream);
         cudaFree(d->codes_dev);
+        d->codes_dev = NULL; d->codes_cap = 0;
         if (cudaMalloc(&d->codes_dev, (size_t)(T + 64) * nq * 4) != cudaSuccess) { qtc_set_error("codec: codes buffer"); return NULL; }
         d->codes_cap = T + 64;
     }
-    cudaEventRecord(c->ev0, c->stream);
-    if (cudaMemcpyAsync(d->codes_dev, codes, (size_t)T * nq * 4, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) return NULL;
+    cudaEventRecord(c->ev0, c->cstream);
+    if (cudaMemcpyAsync(d->codes_dev, codes, (size_t)T * nq * 4, cudaMemcpyHostToDevice, c->cstream) != cudaSuccess) return NULL;
     float *pcm = qtc_codec_decode_dev(c, d->codes_dev, T, out_samples, NULL);
-    cudaEventRecord(c->ev1, c->stream);
+    cudaEventRecord(c->ev1, c->cstream);
     cudaEventSynchronize(c->ev1);
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);

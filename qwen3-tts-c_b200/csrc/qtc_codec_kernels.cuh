@@ -324,16 +324,18 @@ __global__ void k_rope_rows(float *q, float *k, const float *cs, const float *sn
     }
 }
 
-/* sliding-window causal attention (c/qwen_tts_codec.c:355-383): one warp per (query, head), window <= 128 */
+/* sliding-window causal attention (c/qwen_tts_codec.c:355-383): one warp per (query, head), window <= 128.
+ * q / out hold T queries whose absolute positions are q0 .. q0+T-1; k / v are indexed by absolute position (the streaming
+ * decoder keeps them across chunks), so a chunk attends to keys of earlier chunks exactly as a one-shot decode does. */
 __global__ void __launch_bounds__(128) k_window_attn(float *out, const float *q, const float *k, const float *v, int T, int nh, int nkv,
-                                                      int hd, int W, float scale) {
+                                                      int hd, int W, float scale, int q0) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * 4 + warp;
     if (item >= T * nh) return;
-    const int qi = item / nh, h = item - qi * nh, g = h / (nh / nkv);
+    const int ql = item / nh, h = item - ql * nh, g = h / (nh / nkv), qi = q0 + ql;
     int start = qi - W + 1; if (start < 0) start = 0;
     const int n = qi - start + 1;
-    const float *qh = q + ((size_t)qi * nh + h) * hd;
+    const float *qh = q + ((size_t)ql * nh + h) * hd;
     float sc[4];
     float mx = -3.402823466e+38f;
 #pragma unroll
@@ -367,9 +369,15 @@ __global__ void __launch_bounds__(128) k_window_attn(float *out, const float *q,
 #pragma unroll
         for (int u = 0; u < 8; u++) { const int e = lane + 32 * u; if (e < hd) o[u] = fmaf(p, vh[e], o[u]); }
     }
-    float *oh = out + ((size_t)qi * nh + h) * hd;
+    float *oh = out + ((size_t)ql * nh + h) * hd;
 #pragma unroll
     for (int u = 0; u < 8; u++) { const int e = lane + 32 * u; if (e < hd) oh[e] = o[u]; }
+}
+
+/* dst[i] = src[i]: PCM of a streamed chunk into the utterance's device buffer */
+__global__ void k_copy_pcm(float *dst, const float *src, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
 }
 
 /* g[i] = silu(g[i]) * u[i] (c/qwen_tts_codec.c:411-414) */

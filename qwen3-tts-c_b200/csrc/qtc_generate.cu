@@ -6,6 +6,7 @@
  */
 #include "qtc_internal.h"
 
+#include <algorithm>
 #include <strings.h>
 #include <sys/time.h>
 
@@ -190,8 +191,54 @@ static int count_launches(qtc_ctx *c, int (*body)(qtc_ctx *), long long *out) {
     return (rc == 0 && e == cudaSuccess) ? 0 : -1;
 }
 
-/* The loop proper.  c->prefill [plen,H], c->trailing [ntr,H], c->tts_pad [H] are already in HBM. */
-int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit) {
+static int samples_per_frame(const qtc_ctx *c) {
+    const qtc_codec_t *k = &c->host.codec;
+    int s = 1;
+    for (int i = 0; i < 2; i++) s *= k->upsampling_ratios[i];
+    for (int i = 0; i < 4; i++) s *= k->upsample_rates[i];
+    return s;
+}
+
+/* streamed decode of frames [so->decoded, upto): the chunk's kernels are enqueued on the frame loop's OWN stream, between two
+ * frames.  The loop's cooperative kernels occupy every SM, so nothing can run beside them; on a second stream a chunk's ~400
+ * small dependent kernels got one kernel per gap between two of the loop's kernels, whatever the stream priorities (the next
+ * chunk kernel becomes ready a few microseconds after its predecessor ends, and by then the loop's next kernel - always ready -
+ * has taken the SMs): time to first audio 220 ms and a 20 % slower loop (profiles/r02_bench_stream_2streams_*.json).  Inline, a
+ * chunk costs its own run time once.  Only the PCM copy to the (page-locked) host buffer goes to the second stream. */
+static int push_chunk(qtc_ctx *c, StreamOut *so, int upto) {
+    const int n = upto - so->decoded, G = c->G;
+    if (n <= 0) return 0;
+    if (so->nchunks > 0) QTC_CUDA(cudaStreamWaitEvent(c->stream, c->chunk_ev[so->nchunks - 1], 0));   /* the previous chunk's PCM has left the workspace */
+    float *wav = NULL;
+    const int ns = qtc_codec_stream_push(c, c->codes + (size_t)so->decoded * G, n, &wav);
+    if (ns != n * so->spf) return -1;
+    if ((size_t)so->nchunks >= c->chunk_ev.size()) { cudaEvent_t e; QTC_CUDA(cudaEventCreate(&e)); c->chunk_ev.push_back(e); }
+    QTC_CUDA(cudaEventRecord(c->ev3, c->stream));                                   /* last codec kernel so far */
+    QTC_CUDA(cudaStreamWaitEvent(c->stream2, c->ev3, 0));
+    float *dst = so->host + (size_t)so->decoded * so->spf;
+    QTC_CUDA(cudaMemcpyAsync(dst, wav, (size_t)ns * 4, cudaMemcpyDeviceToHost, c->stream2));
+    QTC_CUDA(cudaEventRecord(c->chunk_ev[so->nchunks], c->stream2));
+    so->chunk_end[so->nchunks] = upto;
+    so->nchunks++;
+    so->decoded = upto;
+    return 0;
+}
+/* chunks whose PCM has landed are handed to the callback (in order, on the caller's thread) */
+static void deliver_chunks(qtc_ctx *c, StreamOut *so, bool wait) {
+    while (so->delivered < so->nchunks) {
+        cudaEvent_t e = c->chunk_ev[so->delivered];
+        if (wait) cudaEventSynchronize(e);
+        else if (cudaEventQuery(e) != cudaSuccess) break;
+        const int t0 = so->delivered ? so->chunk_end[so->delivered - 1] : 0, t1 = so->chunk_end[so->delivered];
+        if (c->stream_cb) c->stream_cb(so->host + (size_t)t0 * so->spf, (t1 - t0) * so->spf, t0, c->stream_user);
+        so->delivered++;
+    }
+}
+
+/* The loop proper.  c->prefill [plen,H], c->trailing [ntr,H], c->tts_pad [H] are already in HBM.
+ * so != NULL: the codec decodes chunks of finished frames on the second stream while the loop goes on (first chunk
+ * c->stream_first frames, then c->stream_chunk), PCM lands in so->host. */
+int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit, StreamOut *so) {
     const int H = c->H, G = c->G;
     const int fixed = c->params.fixed_codec_tokens > 0 ? c->params.fixed_codec_tokens : 0;
     if (limit <= 0) return 0;
@@ -221,6 +268,13 @@ int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, in
     if (ensure_graphs(c)) return -1;
     long long lf = 0, lt = 0;
     if (count_launches(c, body_front, &lf) || count_launches(c, body_talker, &lt)) return -1;
+    while ((int)c->frame_ev.size() < limit) { cudaEvent_t e; QTC_CUDA(cudaEventCreate(&e)); c->frame_ev.push_back(e); }
+    if (so) {
+        if (qtc_codec_stream_begin(c, limit)) return -1;
+        const int big = (c->stream_first > c->stream_chunk ? c->stream_first : c->stream_chunk) + 8;   /* + one EOS poll interval */
+        if (qtc_codec_stream_reserve(c, big < limit ? big : limit)) return -1;
+        so->chunk_end.assign((size_t)limit + 1, 0);
+    }
     QTC_CUDA(cudaEventRecord(c->ev0, c->stream));
     int launched = 0;
     const int poll = fixed > 0 ? limit : 8;          /* without a fixed budget, look for EOS every 8 frames */
@@ -229,14 +283,49 @@ int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, in
         for (; launched < upto; launched++) {
             QTC_CUDA(cudaGraphLaunch(c->g_front, c->stream));
             c->launches += lf;
+            QTC_CUDA(cudaEventRecord(c->frame_ev[launched], c->stream));       /* frame `launched` has its 16 codes */
+            if (so && fixed > 0) {
+                /* fixed budget: every frame is real, chunks are enqueued as the loop is (the host runs ahead of the device) */
+                const int want = so->decoded == 0 ? c->stream_first : c->stream_chunk, have = launched + 1 - so->decoded;
+                if (have >= want || launched + 1 == limit) { if (push_chunk(c, so, launched + 1)) return -1; }
+                deliver_chunks(c, so, false);
+            }
             if (launched + 1 < limit) { QTC_CUDA(cudaGraphLaunch(c->g_talker, c->stream)); c->launches += lt; }
         }
         if (pull_state(c)) return -1;
+        if (so && fixed == 0) {
+            /* EOS mode: only frames the device has confirmed (state.step) are decoded */
+            const int valid = c->state_host->step, want = so->decoded == 0 ? c->stream_first : c->stream_chunk;
+            if (valid - so->decoded >= want || (c->state_host->done && valid > so->decoded) || (launched >= limit && valid > so->decoded)) {
+                if (push_chunk(c, so, valid)) return -1;
+            }
+            deliver_chunks(c, so, false);
+        }
         if (c->state_host->done) break;
     }
     QTC_CUDA(cudaEventRecord(c->ev1, c->stream));
     if (pull_state(c)) return -1;
     const int n = c->state_host->step;
+    if (so && so->decoded < n) { if (push_chunk(c, so, n)) return -1; }
+    if (so) {
+        deliver_chunks(c, so, true);
+        QTC_CUDA(cudaStreamSynchronize(c->stream2));
+        so->samples = so->decoded * so->spf;
+    }
+    /* latency distribution of this utterance (device clock): first frame from the start of the prompt build, then frame to frame */
+    if (n > 0) {
+        QTC_CUDA(cudaEventSynchronize(c->frame_ev[n - 1]));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev2, c->frame_ev[0]);
+        c->perf.ttff_ms = ms;
+        std::vector<float> dt;
+        for (int i = 1; i < n; i++) { float d = 0; cudaEventElapsedTime(&d, c->frame_ev[i - 1], c->frame_ev[i]); dt.push_back(d); }
+        std::sort(dt.begin(), dt.end());
+        c->perf.frame_ms_p50 = dt.empty() ? ms : dt[dt.size() / 2];
+        c->perf.frame_ms_p99 = dt.empty() ? ms : dt[(size_t)((dt.size() - 1) * 0.99)];
+        c->perf.ttfa_ms = 0.0;
+        if (so && so->nchunks > 0) { float a = 0; cudaEventElapsedTime(&a, c->ev2, c->chunk_ev[0]); c->perf.ttfa_ms = a; }
+    }
     if (n > 0 && out_codes) {
         QTC_CUDA(cudaMemcpyAsync(c->codes_host, c->codes, (size_t)n * G * 4, cudaMemcpyDeviceToHost, c->stream));
         QTC_CUDA(cudaStreamSynchronize(c->stream));
@@ -269,7 +358,8 @@ extern "C" int qwen_tts_cuda_generate_frames(qtc_ctx_t *c, const float *prefill_
     QTC_CUDA(cudaMemcpyAsync(c->prefill, prefill_embeds, (size_t)prefill_len * H * 4, cudaMemcpyHostToDevice, c->stream));
     QTC_CUDA(cudaMemcpyAsync(c->trailing, trailing_text, (size_t)n_trailing * H * 4, cudaMemcpyHostToDevice, c->stream));
     QTC_CUDA(cudaMemcpyAsync(c->tts_pad, tts_pad, (size_t)H * 4, cudaMemcpyHostToDevice, c->stream));
-    return qtc_generate_frames_resident(c, prefill_len, n_trailing, out_codes, limit);
+    cudaEventRecord(c->ev2, c->stream);
+    return qtc_generate_frames_resident(c, prefill_len, n_trailing, out_codes, limit, NULL);
 }
 
 /* ---- whole utterance ----------------------------------------------------------- */
@@ -350,19 +440,51 @@ extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const c
     const int fixed = c->params.fixed_codec_tokens > 0 ? c->params.fixed_codec_tokens : 0;
     const int limit = fixed > 0 ? fixed : c->params.max_new_tokens;
     std::vector<int> codes((size_t)(limit > 0 ? limit : 1) * c->G);
-    const int n = qtc_generate_frames_resident(c, plen, ntr, codes.data(), limit);
-    if (n < 0) return NULL;
-    if (out_codes) memcpy(out_codes, codes.data(), (size_t)(n < max_codes ? n : max_codes) * c->G * 4);
-    if (out_n_frames) *out_n_frames = n;
+    if (!c->codec) { qtc_set_error("generate: context has no codec weights"); return NULL; }
     float *pcm = NULL;
-    const double t_codec = now_ms();
-    if (n > 0) {
-        if (!c->codec) { qtc_set_error("generate: context has no codec weights"); return NULL; }
-        pcm = qtc_codec_decode_dev(c, c->codes, n, out_samples, NULL);
+    int n = 0;
+    double t_codec = 0.0;
+    if (c->stream_chunk > 0 && limit > 0) {
+        /* codec chunks decode on the second stream while frames are produced; PCM lands in the caller's buffer, page-locked
+         * for the duration of the call so that the copies are asynchronous */
+        StreamOut so;
+        so.spf = samples_per_frame(c);
+        const size_t bytes = (size_t)limit * so.spf * 4;
+        so.host = (float *)malloc(bytes);
+        if (!so.host) { qtc_set_error("generate: PCM buffer of %zu bytes", bytes); return NULL; }
+        if (cudaHostRegister(so.host, bytes, cudaHostRegisterDefault) != cudaSuccess) {
+            cudaGetLastError(); free(so.host); qtc_set_error("generate: cudaHostRegister of the PCM buffer failed"); return NULL;
+        }
+        n = qtc_generate_frames_resident(c, plen, ntr, codes.data(), limit, &so);
+        cudaHostUnregister(so.host);
+        t_codec = now_ms();
+        if (n <= 0) { free(so.host); if (n < 0) return NULL; }
+        else { pcm = so.host; *out_samples = so.samples; }
+    } else {
+        n = qtc_generate_frames_resident(c, plen, ntr, codes.data(), limit, NULL);
+        if (n < 0) return NULL;
+        t_codec = now_ms();
+        if (n > 0) pcm = qtc_codec_decode_dev(c, c->codes, n, out_samples, NULL);
     }
+    if (out_codes && n > 0) memcpy(out_codes, codes.data(), (size_t)(n < max_codes ? n : max_codes) * c->G * 4);
+    if (out_n_frames) *out_n_frames = n > 0 ? n : 0;
     const double t_end = now_ms();
-    c->perf.codec_ms = t_end - t_codec;
+    c->perf.codec_ms = t_end - t_codec;         /* streamed: only what was left after the last frame */
     if (pcm) { float dms = 0; cudaEventElapsedTime(&dms, c->ev2, c->ev3); c->perf.device_ms = dms; }
     c->perf.total_ms = t_end - t_start;
     return pcm;
+}
+
+/* chunk schedule of the streamed decode inside qwen_tts_cuda_generate: first chunk / later chunks in frames;
+ * chunk_frames <= 0: decode once after the last frame (the reference's order, c/qwen_tts.c:1399-1420) */
+extern "C" int qwen_tts_cuda_set_streaming(qtc_ctx_t *c, int first_frames, int chunk_frames) {
+    if (!c) return -1;
+    c->stream_chunk = chunk_frames;
+    c->stream_first = first_frames > 0 ? first_frames : (chunk_frames > 0 ? chunk_frames : 1);
+    return 0;
+}
+/* cb(pcm, n_samples, first_frame, user) is called on the caller's thread, in order, as chunks land in host memory during
+ * qwen_tts_cuda_generate (pcm points into the buffer the call will return).  NULL: off. */
+extern "C" void qwen_tts_cuda_set_stream_callback(qtc_ctx_t *c, qtc_pcm_callback_t cb, void *user) {
+    if (c) { c->stream_cb = cb; c->stream_user = user; }
 }

@@ -141,9 +141,17 @@ struct qtc_ctx {
     int mode;                     /* 0 per-op kernels, 1 fused persistent kernels (default) */
     int arith;                    /* QTC_FAST / QTC_STRICT */
     cudaStream_t stream;
+    cudaStream_t cstream;         /* stream the codec kernels are enqueued on: == stream, or stream2 while a generate overlaps decode and frame loop */
+    cudaStream_t stream2;
     cudaEvent_t ev0, ev1, ev2, ev3;   /* ev2..ev3: device span of a whole utterance (prompt build .. last codec kernel) */
     std::vector<void *> allocs;   /* everything cudaMalloc'd, for release() */
     long long launches;
+    /* streamed decode inside generate: PCM of the whole utterance on the device, chunk schedule, per-frame / per-chunk events */
+    float *pcm_dev; size_t pcm_cap;          /* [frames * samples_per_frame] */
+    float *first_pcm_host;                   /* pinned landing buffer of the first chunk (time to first audio is measured on its arrival) */
+    int stream_first, stream_chunk;          /* frames in the first chunk / in later chunks; stream_chunk <= 0: decode once at the end */
+    qtc_pcm_callback_t stream_cb; void *stream_user;
+    std::vector<cudaEvent_t> frame_ev, chunk_ev;
     /* CUDA graphs of the frame loop (built lazily, keyed by params) */
     cudaGraphExec_t g_front, g_talker;
     int graph_key;
@@ -168,7 +176,12 @@ int qtc_talker_forward_dev(qtc_ctx *c, const float *embed_dev);   /* one decode 
 int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code_ptr, int *codes_out_dev);
 int qtc_sample_talker(qtc_ctx *c);
 int qtc_frame_front(qtc_ctx *c);    /* sample + sub-talker + next embedding, device resident */
-int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit);
+struct StreamOut {                 /* streamed decode of one utterance */
+    float *host; int spf, samples;     /* page-locked PCM buffer, samples per frame, samples written */
+    int decoded = 0, nchunks = 0, delivered = 0;
+    std::vector<int> chunk_end;        /* frame index each chunk ends at */
+};
+int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, int *out_codes, int limit, StreamOut *so);
 int qtc_build_prompt_dev(qtc_ctx *c, const int *tok, int ntok, int spk, int lang, float *pre, int *plen_out, float *trailing, int *ntr_out, float *pad);
 void qtc_batch_release(qtc_ctx *c);
 void qtc_batch_invalidate_graphs(qtc_ctx *c);
@@ -180,6 +193,9 @@ template <class T> T *qtc_upload(qtc_ctx *c, const T *host, size_t n);
 CodecDev *qtc_codec_upload(qtc_ctx *c, const qtc_codec_t *k);
 void qtc_codec_release(CodecDev *cd);
 float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_samples, float **dev_out);
+int qtc_codec_stream_begin(qtc_ctx *c, int max_frames);
+int qtc_codec_stream_reserve(qtc_ctx *c, int chunk);
+int qtc_codec_stream_push(qtc_ctx *c, const int *codes_dev, int n, float **pcm_dev);
 
 /* small launchers (qtc_lm.cu) */
 int qtc_copy(qtc_ctx *c, float *dst, const float *src, int n);

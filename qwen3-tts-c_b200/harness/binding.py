@@ -93,7 +93,11 @@ class Perf(C.Structure):
     _fields_ = [("total_ms", C.c_double), ("talker_ms", C.c_double), ("codec_ms", C.c_double),
                 ("prefill_ms", C.c_double), ("codec_tokens", C.c_int), ("stop_reason", C.c_int),
                 ("stop_step", C.c_int), ("kernel_launches", C.c_longlong),
-                ("device_ms", C.c_double)]
+                ("device_ms", C.c_double), ("ttff_ms", C.c_double), ("ttfa_ms", C.c_double),
+                ("frame_ms_p50", C.c_double), ("frame_ms_p99", C.c_double)]
+
+
+PcmCallback = C.CFUNCTYPE(None, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p)
 
 
 def default_params(**kw) -> GenParams:
@@ -144,6 +148,11 @@ def load_cuda():
     lib.qwen_tts_cuda_generate_frames.argtypes = [vp, f32p, C.c_int, f32p, C.c_int, f32p, i32p, C.c_int]
     lib.qwen_tts_cuda_generate.restype = vp
     lib.qwen_tts_cuda_generate.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p, i32p, i32p, C.c_int, i32p]
+    lib.qwen_tts_cuda_set_streaming.argtypes = [vp, C.c_int, C.c_int]
+    lib.qwen_tts_cuda_set_stream_callback.argtypes = [vp, PcmCallback, vp]
+    lib.qwen_tts_cuda_set_stream_callback.restype = None
+    lib.qwen_tts_cuda_codec_stream_begin.argtypes = [vp, C.c_int]
+    lib.qwen_tts_cuda_codec_stream_push.argtypes = [vp, i32p, C.c_int, f32p]
     lib.qwen_tts_cuda_generate_batch.argtypes = [vp, C.c_int, i32p, i32p, i32p, i32p, i32p, i32p, f32p, C.c_int]
     lib.qwen_tts_cuda_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_swiglu_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
