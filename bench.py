@@ -404,7 +404,7 @@ def main():
     if cuda.qwen_tts_cuda_init(local) != 0:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
     spec, main_t, cod, hm = build_model(args.model)
-    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), max(1, args.batch))     # max_batch sizes the paged KV pool
     if not ctx:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
     cuda.qwen_tts_cuda_set_mode(ctx, args.mode)

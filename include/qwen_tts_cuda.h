@@ -176,6 +176,10 @@ typedef struct {
     double ttff_ms;             /* time to the first frame's 16 codes (prompt build + prefill + first frame) */
     double ttfa_ms;             /* time to first audio: first PCM chunk in host memory (0 if the decode was not streamed) */
     double frame_ms_p50, frame_ms_p99;   /* frame-to-frame interval (includes codec chunks that interleave) */
+    /* memory: the talker's paged KV pool (pages of 64 positions, allocated once at upload) and every cudaMalloc after upload */
+    long long device_mallocs;   /* cudaMalloc calls since upload returned: workspaces grown on first use; 0 in steady state */
+    long long kv_page_allocs;   /* pages handed out by the pool's free list so far */
+    int    kv_pool_pages, kv_pages_in_use;
 } qtc_perf_t;
 
 /* streamed PCM: called as chunks land in host memory (see qwen_tts_cuda_set_stream_callback) */

@@ -116,6 +116,7 @@ extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     for (void *p : c->allocs) { qtc_gemm_tc_forget(p); cudaFree(p); }
     LmBuffers *bs[2] = {&c->tk, &c->st};
     for (LmBuffers *b : bs) { cudaFree(b->k); cudaFree(b->v); cudaFree(b->cos); cudaFree(b->sin); }
+    cudaFree(c->kv.tables); cudaFreeHost(c->kv.tables_host);
     cudaFree(c->codes); cudaFree(c->trailing); cudaFree(c->prefill);
     cudaFreeHost(c->state_host); cudaFreeHost(c->codes_host); cudaFreeHost(c->host_stage);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
@@ -132,7 +133,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     qtc_ctx *c = new qtc_ctx();
     c->host = *desc;
     c->H = desc->talker.hidden; c->G = desc->num_code_groups; c->max_batch = max_batch > 0 ? max_batch : 1;
-    c->bb = NULL; c->batch_pieces = 3;
+    c->bb = NULL; c->batch_pieces = 3; c->dev_mallocs = 0;
     c->mode = 1; c->arith = 0; c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
     c->codec = NULL; c->codes = NULL; c->trailing = NULL; c->prefill = NULL; c->codes_cap = c->trailing_cap = c->prefill_cap = 0;
     memset(&c->tk, 0, sizeof(c->tk)); memset(&c->st, 0, sizeof(c->st)); memset(&c->perf, 0, sizeof(c->perf));
@@ -173,7 +174,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
         c->sub_in_w = qtc_upload(c, desc->sub_input_proj_w, (size_t)desc->sub.hidden * H);
         c->sub_in_b = qtc_upload(c, desc->sub_input_proj_b, desc->sub.hidden);
         if (alloc_lm_buffers(c, &c->tk, &c->talker) || alloc_lm_buffers(c, &c->st, &c->sub)) { qwen_tts_cuda_release(c); return NULL; }
-        if (qtc_ensure_kv(c, &c->st, &c->sub, c->G + 2) || qtc_ensure_kv(c, &c->tk, &c->talker, 512)) { qwen_tts_cuda_release(c); return NULL; }
+        if (qtc_ensure_kv(c, &c->st, &c->sub, c->G + 2) || qtc_kv_pool_init(c, c->max_batch)) { qwen_tts_cuda_release(c); return NULL; }
     } else {
         c->talker.vocab = desc->talker.vocab; c->talker.hidden = desc->talker.hidden;
         c->sub.vocab = desc->sub.vocab; c->sub.hidden = desc->sub.hidden;
@@ -216,11 +217,21 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
         if (!c->codec) { qwen_tts_cuda_release(c); return NULL; }
     }
     if (cudaDeviceSynchronize() != cudaSuccess) { qtc_set_error("upload: device error"); qwen_tts_cuda_release(c); return NULL; }
+    c->dev_mallocs = 0;           /* from here on every cudaMalloc is counted (qtc_perf_t.device_mallocs) */
     return c;
 }
 
 extern "C" void qwen_tts_cuda_set_params(qtc_ctx_t *c, const qtc_gen_params_t *p) { if (c && p) { c->params = *p; c->graph_key = -1; } }
-extern "C" void qwen_tts_cuda_get_perf(const qtc_ctx_t *c, qtc_perf_t *out) { if (c && out) { *out = c->perf; out->kernel_launches = c->launches; } }
+extern "C" void qwen_tts_cuda_get_perf(const qtc_ctx_t *c, qtc_perf_t *out) {
+    if (!c || !out) return;
+    *out = c->perf;
+    out->kernel_launches = c->launches;
+    out->device_mallocs = c->dev_mallocs;
+    out->kv_pool_pages = c->kv.pages; out->kv_page_allocs = c->kv.page_allocs;
+    int used = 0;
+    for (int u : c->kv.used) used += u;
+    out->kv_pages_in_use = used;
+}
 extern "C" int qwen_tts_cuda_set_mode(qtc_ctx_t *c, int mode) {
     if (!c || mode < 0 || mode > 1) return -1;
     c->mode = mode; c->graph_key = -1;

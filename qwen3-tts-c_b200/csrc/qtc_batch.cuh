@@ -113,8 +113,9 @@ __global__ void k_b_swiglu(uint16_t *xb, const float *gu, int I, int pieces) {
 struct BAttnArgs {
     const float *qkv;              /* [B, qd + 2 kvd]: q | k | v of the new token */
     const float *q_norm, *k_norm, *cos, *sin;
-    float *kc, *vc;                /* this layer's cache, utterance stride kv_stride floats: [B][..][kv_max, kvd] */
+    float *kc, *vc;                /* this layer's cache: the pool slice (paged: tables != NULL) or [B][..][kv_max, kvd] with utterance stride kv_stride */
     size_t kv_stride;
+    const int *tables; int table_stride;   /* page tables [B][table_stride] of the utterances, or NULL */
     uint16_t *xb;                  /* out: attention output as bf16 pieces [.., qd] */
     const int *pos; int pos_add;   /* position of utterance b = pos[b] + pos_add (pos == NULL: pos_add) */
     int heads, kv_heads, hd, pieces;
@@ -133,7 +134,8 @@ __global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
     float *qs = sm, *ks = sm + hd, *sc = sm + 2 * hd;
     const float *row = a.qkv + (size_t)b * (qd + 2 * kvd), *qr = row + h * hd, *kr = row + qd + g * hd, *vr = row + qd + kvd + g * hd;
     const float *cs = a.cos + (size_t)pos * hd, *sn = a.sin + (size_t)pos * hd;
-    float *kc = a.kc + (size_t)b * a.kv_stride, *vc = a.vc + (size_t)b * a.kv_stride;
+    const int *tab = a.tables ? a.tables + (size_t)b * a.table_stride : NULL;
+    float *kc = a.kc + (tab ? 0 : (size_t)b * a.kv_stride), *vc = a.vc + (tab ? 0 : (size_t)b * a.kv_stride);
     float s1 = 0.0f, s2 = 0.0f;
     for (int i = threadIdx.x; i < hd; i += blockDim.x) { s1 = fmaf(qr[i], qr[i], s1); s2 = fmaf(kr[i], kr[i], s2); }
     s1 = block_sum(s1, red);
@@ -151,10 +153,10 @@ __global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
     if (threadIdx.x < half) { qs[threadIdx.x] = rq0; qs[threadIdx.x + half] = rq1; ks[threadIdx.x] = rk0; ks[threadIdx.x + half] = rk1; }
     __syncthreads();
     if (h % rep == 0)
-        for (int i = threadIdx.x; i < hd; i += blockDim.x) { kc[(size_t)pos * kvd + g * hd + i] = ks[i]; vc[(size_t)pos * kvd + g * hd + i] = vr[i]; }
+        for (int i = threadIdx.x; i < hd; i += blockDim.x) { kc[kv_off(tab, pos, kvd) + g * hd + i] = ks[i]; vc[kv_off(tab, pos, kvd) + g * hd + i] = vr[i]; }
     const int n = pos + 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int t = warp; t < n; t += nw) {
-        const float *kt = t < pos ? kc + (size_t)t * kvd + g * hd : ks;
+        const float *kt = t < pos ? kc + kv_off(tab, t, kvd) + g * hd : ks;
         float d = 0.0f;
         for (int i = lane; i < hd; i += 32) d = fmaf(qs[i], kt[i], d);
         d = warp_sum(d);
@@ -173,8 +175,8 @@ __global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
         float o = 0.0f, o1 = 0.0f;
         const float *vcol = vc + g * hd + i;
         int t = 0;
-        for (; t + 1 < pos; t += 2) { o = fmaf(sc[t], vcol[(size_t)t * kvd], o); o1 = fmaf(sc[t + 1], vcol[(size_t)(t + 1) * kvd], o1); }
-        for (; t < pos; t++) o = fmaf(sc[t], vcol[(size_t)t * kvd], o);
+        for (; t + 1 < pos; t += 2) { o = fmaf(sc[t], vcol[kv_off(tab, t, kvd)], o); o1 = fmaf(sc[t + 1], vcol[kv_off(tab, t + 1, kvd)], o1); }
+        for (; t < pos; t++) o = fmaf(sc[t], vcol[kv_off(tab, t, kvd)], o);
         o = fmaf(sc[pos], vr[i], o + o1);
         store_pieces(a.xb, b, h * hd + i, qd, a.pieces, o * inv);
     }
@@ -194,7 +196,8 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
     float *qs = scr[warp][0], *ks = scr[warp][1];
     const float *row = a.qkv + (size_t)b * (qd + 2 * kvd), *qr = row + h * hd, *kr = row + qd + g * hd, *vr = row + qd + kvd + g * hd;
     const float *cs = a.cos + (size_t)pos * hd, *sn = a.sin + (size_t)pos * hd;
-    float *kc = a.kc + (size_t)b * a.kv_stride, *vc = a.vc + (size_t)b * a.kv_stride;
+    const int *tab = a.tables ? a.tables + (size_t)b * a.table_stride : NULL;
+    float *kc = a.kc + (tab ? 0 : (size_t)b * a.kv_stride), *vc = a.vc + (tab ? 0 : (size_t)b * a.kv_stride);
     float sq = 0.0f, sk = 0.0f;
     for (int i = lane; i < hd; i += 32) { const float vq = qr[i], vk = kr[i]; qs[i] = vq; ks[i] = vk; sq = fmaf(vq, vq, sq); sk = fmaf(vk, vk, sk); }
     const float4 v_new = act ? *reinterpret_cast<const float4 *>(vr + lane * 4) : make_float4(0, 0, 0, 0);
@@ -212,8 +215,8 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
     const float4 q4 = act ? *reinterpret_cast<const float4 *>(qs + lane * 4) : make_float4(0, 0, 0, 0);
     const float4 k_new = act ? *reinterpret_cast<const float4 *>(ks + lane * 4) : make_float4(0, 0, 0, 0);
     if (act && h % rep == 0) {
-        *reinterpret_cast<float4 *>(kc + (size_t)pos * kvd + g * hd + lane * 4) = k_new;
-        *reinterpret_cast<float4 *>(vc + (size_t)pos * kvd + g * hd + lane * 4) = v_new;
+        *reinterpret_cast<float4 *>(kc + kv_off(tab, pos, kvd) + g * hd + lane * 4) = k_new;
+        *reinterpret_cast<float4 *>(vc + kv_off(tab, pos, kvd) + g * hd + lane * 4) = v_new;
     }
     float sc = -3.402823466e+38f;
     for (int t0 = 0; t0 < n; t0 += 8) {
@@ -222,7 +225,7 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
         for (int u = 0; u < 8; u++) {
             const int t = t0 + u;
             float4 kv = make_float4(0, 0, 0, 0);
-            if (t < pos) { if (act) kv = *reinterpret_cast<const float4 *>(kc + (size_t)t * kvd + g * hd + lane * 4); }
+            if (t < pos) { if (act) kv = *reinterpret_cast<const float4 *>(kc + kv_off(tab, t, kvd) + g * hd + lane * 4); }
             else if (t == pos) kv = k_new;
             d[u] = fmaf(q4.w, kv.w, fmaf(q4.z, kv.z, fmaf(q4.y, kv.y, q4.x * kv.x)));
         }
@@ -247,7 +250,7 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
         for (int u = 0; u < 8; u++) {
             const int t = t0 + u;
             vv[u] = make_float4(0, 0, 0, 0);
-            if (t < pos) { if (act) vv[u] = *reinterpret_cast<const float4 *>(vc + (size_t)t * kvd + g * hd + lane * 4); }
+            if (t < pos) { if (act) vv[u] = *reinterpret_cast<const float4 *>(vc + kv_off(tab, t, kvd) + g * hd + lane * 4); }
             else if (t == pos) vv[u] = v_new;
         }
 #pragma unroll
@@ -335,10 +338,12 @@ struct BatchBuf {
     int graph_key, graph_B;
     long long n_front, n_talker;  /* kernel launches inside each captured graph */
     std::vector<void *> allocs;
+    long long mallocs = 0;
 };
 
 static void *balloc(BatchBuf *bb, size_t bytes) {
     void *p = NULL;
+    bb->mallocs++;
     if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) { qtc_set_error("batch: cudaMalloc of %.1f MB failed", bytes / 1e6); return NULL; }
     cudaMemset(p, 0, bytes ? bytes : 16);
     bb->allocs.push_back(p);
@@ -357,16 +362,22 @@ void qtc_batch_release(qtc_ctx *c) {
     c->bb = NULL;
 }
 
+/* kv_max > 0: the stack keeps its own contiguous cache [B][layers][kv_max][kvd] (sub-talker); 0: the talker's rows live in the
+ * paged pool of the context */
 static int bstack_alloc(BatchBuf *bb, BStack *s, const LmDev *lm, int B, int kv_max) {
     const size_t qd = (size_t)lm->heads * lm->head_dim, kvd = (size_t)lm->kv_heads * lm->head_dim;
     s->x = (float *)balloc(bb, (size_t)B * lm->hidden * 4);
     s->qkv = (float *)balloc(bb, (size_t)B * (qd + 2 * kvd) * 4);
     s->gu = (float *)balloc(bb, (size_t)B * 2 * lm->inter * 4);
     s->logits = (float *)balloc(bb, (size_t)B * lm->vocab * 4);
-    s->kc = (float *)balloc(bb, (size_t)B * lm->layers * kv_max * kvd * 4);
-    s->vc = (float *)balloc(bb, (size_t)B * lm->layers * kv_max * kvd * 4);
+    s->kc = s->vc = NULL;
+    if (kv_max > 0) {
+        s->kc = (float *)balloc(bb, (size_t)B * lm->layers * kv_max * kvd * 4);
+        s->vc = (float *)balloc(bb, (size_t)B * lm->layers * kv_max * kvd * 4);
+        if (!s->kc || !s->vc) return -1;
+    }
     s->kv_max = kv_max;
-    if (!(s->x && s->qkv && s->gu && s->logits && s->kc && s->vc)) return -1;
+    if (!(s->x && s->qkv && s->gu && s->logits)) return -1;
     s->xh = (uint16_t *)balloc(bb, (size_t)bb->pieces * BROWS * lm->inter * 2);
     if (!s->xh) return -1;
     const size_t H = lm->hidden, I = lm->inter;
@@ -391,7 +402,12 @@ static int bstack_alloc(BatchBuf *bb, BStack *s, const LmDev *lm, int B, int kv_
 static int batch_ensure(qtc_ctx *c, int B, int kv_need, int frames, int pre_rows, int tr_rows) {
     BatchBuf *bb = c->bb;
     const int pieces = c->batch_pieces == 1 ? 1 : 3;
-    if (bb && bb->B >= B && bb->tk.kv_max >= kv_need && bb->codes_cap >= frames && bb->prefill_cap >= pre_rows && bb->trailing_cap >= tr_rows &&
+    /* the talker's KV: every row takes pages for kv_need positions from the pool (slots 0..B-1), page by page across the rows, so
+     * the tables interleave and no row's cache is contiguous */
+    qtc_kv_release_all(c);
+    for (int pg = 1; pg <= (kv_need + QTC_KV_PAGE_POS - 1) / QTC_KV_PAGE_POS; pg++)
+        for (int b = 0; b < B; b++) if (qtc_kv_reserve(c, b, pg * QTC_KV_PAGE_POS)) return -1;
+    if (bb && bb->B >= B && bb->codes_cap >= frames && bb->prefill_cap >= pre_rows && bb->trailing_cap >= tr_rows &&
         bb->pieces == pieces) return 0;
     qtc_batch_release(c);
     bb = new BatchBuf();
@@ -404,9 +420,8 @@ static int batch_ensure(qtc_ctx *c, int B, int kv_need, int frames, int pre_rows
     if (st->inter > maxK) maxK = st->inter;
     if (st->heads * st->head_dim > maxK) maxK = st->heads * st->head_dim;
     bb->maxK = maxK;
-    const int kv_max = ((kv_need + 63) / 64) * 64;
     bb->xb = (uint16_t *)balloc(bb, (size_t)pieces * BROWS * maxK * 2);
-    if (!bb->xb || bstack_alloc(bb, &bb->tk, tk, B, kv_max) || bstack_alloc(bb, &bb->st, st, B, G + 2)) return -1;
+    if (!bb->xb || bstack_alloc(bb, &bb->tk, tk, B, 0) || bstack_alloc(bb, &bb->st, st, B, G + 2)) return -1;
     bb->hidden = (float *)balloc(bb, (size_t)B * H * 4);
     bb->sub_in = (float *)balloc(bb, (size_t)B * H * 4);
     bb->pos = (int *)balloc(bb, (size_t)B * 4);
@@ -427,8 +442,7 @@ static int batch_ensure(qtc_ctx *c, int B, int kv_need, int frames, int pre_rows
     if (!bb->hidden || !bb->sub_in || !bb->pos || !bb->state || !bb->hist || !bb->frame_codes || !bb->codes || !bb->next_embed || !bb->prefill ||
         !bb->trailing || !bb->sub_rng || !bb->seeds || !bb->scratch_f || !bb->scratch_i) return -1;
     if (cudaMallocHost(&bb->state_host, (size_t)B * sizeof(GenState)) != cudaSuccess) { qtc_set_error("batch: pinned state"); return -1; }
-    /* RoPE tables of both stacks must cover the positions (they are shared with the batch-1 path) */
-    if (qtc_ensure_kv(c, &c->tk, &c->talker, kv_max) || qtc_ensure_kv(c, &c->st, &c->sub, G + 2)) return -1;
+    c->dev_mallocs += bb->mallocs;
     /* balloc's memsets and the weight re-layout copies ran on the legacy default stream, which c->stream (non-blocking) does
      * not order against: nothing on c->stream may touch these buffers before they have landed */
     QTC_CUDA(cudaDeviceSynchronize());
@@ -450,11 +464,12 @@ static int b_lm_step(qtc_ctx *c, BatchBuf *bb, const LmDev *lm, BStack *s, const
         if (qtc_gemm_tc(c, s->qkv, ldq, bb->xb, s->wqkv[l], B, ldq, H, np)) return -1;
         BAttnArgs a;
         a.qkv = s->qkv; a.q_norm = w->q_norm; a.k_norm = w->k_norm; a.cos = rope->cos; a.sin = rope->sin;
-        a.kc = s->kc + (size_t)l * s->kv_max * kvd; a.vc = s->vc + (size_t)l * s->kv_max * kvd; a.kv_stride = kv_stride;
+        if (s->kv_max > 0) { a.kc = s->kc + (size_t)l * s->kv_max * kvd; a.vc = s->vc + (size_t)l * s->kv_max * kvd; a.kv_stride = kv_stride; a.tables = NULL; a.table_stride = 0; }
+        else { a.kc = c->tk.k + (size_t)l * c->tk.kv_max * kvd; a.vc = c->tk.v + (size_t)l * c->tk.kv_max * kvd; a.kv_stride = 0; a.tables = c->kv.tables; a.table_stride = c->kv.max_seq_pages; }
         a.xb = bb->xb; a.pos = pos; a.pos_add = pos_add; a.heads = lm->heads; a.kv_heads = lm->kv_heads; a.hd = hd; a.pieces = np;
         a.eps = lm->eps; a.scale = 1.0f / sqrtf((float)hd);
         if (!pos && pos_add + 1 <= 32 && hd <= 128 && hd % 4 == 0) qtc_launch_pdl(c->stream, k_b_attn_small, dim3(dim3((lm->heads + 3) / 4, B)), dim3(128), 0, a);
-        else qtc_launch_pdl(c->stream, k_b_attn, dim3(dim3(lm->heads, B)), dim3(128), (size_t)(2 * hd + s->kv_max + 32) * 4, a);
+        else qtc_launch_pdl(c->stream, k_b_attn, dim3(dim3(lm->heads, B)), dim3(128), (size_t)(2 * hd + (s->kv_max > 0 ? s->kv_max : c->kv.used[0] * QTC_KV_PAGE_POS) + 32) * 4, a);
         BLAUNCH(c);
         if (qtc_gemm_tc(c, s->x, H, bb->xb, w->wo, B, H, qd, np)) return -1;                      /* x += Wo . att */
         static int epi = -1;
@@ -563,6 +578,7 @@ static int b_params_key(const qtc_ctx *c, int B) {
     const unsigned char *p = (const unsigned char *)&c->params;
     for (size_t i = 0; i < sizeof(c->params); i++) h = (h ^ p[i]) * 16777619u;
     h = (h ^ (uint32_t)B) * 16777619u;
+    h = (h ^ (uint32_t)c->kv.used[0]) * 16777619u;      /* k_b_attn's score buffer (dynamic smem) is sized by the rows' capacity */
     return (int)(h & 0x7fffffff);
 }
 static int b_capture(qtc_ctx *c, cudaGraphExec_t *out, int which, int B, long long *nlaunch) {

@@ -275,6 +275,7 @@ int qtc_codec_stream_begin(qtc_ctx *c, int max_frames) {
         cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
         stream_free(d);
         const int cap = max_frames + 64;
+        c->dev_mallocs += 2 + 2 * k->layers;
         bool ok = cudaMalloc(&d->s_tf, (size_t)cap * k->latent * 4) == cudaSuccess && cudaMalloc(&d->s_codes, (size_t)cap * k->num_quantizers * 4) == cudaSuccess;
         for (int l = 0; l < k->layers && ok; l++)
             ok = cudaMalloc(&d->s_k[l], (size_t)cap * kvd * 4) == cudaSuccess && cudaMalloc(&d->s_v[l], (size_t)cap * kvd * 4) == cudaSuccess;
@@ -293,6 +294,7 @@ int qtc_codec_stream_begin(qtc_ctx *c, int max_frames) {
                 cs[(size_t)t * hd + i] = cs[(size_t)t * hd + i + hd / 2] = cosf(ang);
                 sn[(size_t)t * hd + i] = sn[(size_t)t * hd + i + hd / 2] = sinf(ang);
             }
+        c->dev_mallocs += 2;
         if (cudaMalloc(&d->rope_cs, cs.size() * 4) != cudaSuccess || cudaMalloc(&d->rope_sn, sn.size() * 4) != cudaSuccess) { qtc_set_error("codec: rope tables"); return -1; }
         cudaMemcpy(d->rope_cs, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice);
         cudaMemcpy(d->rope_sn, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice);
@@ -310,6 +312,7 @@ int qtc_codec_stream_reserve(qtc_ctx *c, int chunk) {
     if (2 * half_bytes > d->ws_bytes) {
         cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->cstream);
         cudaFree(d->ws); d->ws = NULL; d->ws_bytes = 0;
+        QTC_COUNT_MALLOC(c);
         if (cudaMalloc(&d->ws, 2 * half_bytes) != cudaSuccess) { qtc_set_error("codec: workspace of %.1f MB failed", 2 * half_bytes / 1e6); return -1; }
         d->ws_bytes = 2 * half_bytes;
     }
@@ -466,6 +469,7 @@ extern "C" int qwen_tts_cuda_codec_stream_push(qtc_ctx_t *c, const int *codes, i
         cudaStreamSynchronize(c->cstream);
         cudaFree(d->codes_dev);
         d->codes_dev = NULL; d->codes_cap = 0;
+        QTC_COUNT_MALLOC(c);
         if (cudaMalloc(&d->codes_dev, (size_t)(n + 64) * nq * 4) != cudaSuccess) { qtc_set_error("codec: codes buffer"); return -1; }
         d->codes_cap = n + 64;
     }
@@ -490,6 +494,7 @@ extern "C" float *qwen_tts_cuda_codec_decode(qtc_ctx_t *c, const int *codes, int
         cudaStreamSynchronize(c->cstream);
         cudaFree(d->codes_dev);
         d->codes_dev = NULL; d->codes_cap = 0;
+        QTC_COUNT_MALLOC(c);
         if (cudaMalloc(&d->codes_dev, (size_t)(T + 64) * nq * 4) != cudaSuccess) { qtc_set_error("codec: codes buffer"); return NULL; }
         d->codes_cap = T + 64;
     }

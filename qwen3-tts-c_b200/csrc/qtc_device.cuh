@@ -30,6 +30,17 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
     return r;
 }
 
+/* ---- paged KV cache -----------------------------------------------------------
+ * The talker's K and V rows live in one pool per layer, allocated once at upload: pages of 64 positions x (kv_heads*head_dim)
+ * fp32, handed out to utterances by a host-side free list; table[i] = pool page that holds positions [64 i, 64 i + 64) of
+ * the utterance.  Row t of a layer's cache is at layer_base + kv_off(table, t, kvd) floats.  table == NULL: a contiguous
+ * cache (the sub-talker's 18 positions, reset every frame).  The reference grows one contiguous fp32 cache by realloc
+ * (c/qwen_tts_talker.c:265-271, 489-496). */
+#define QTC_KV_PAGE 64
+__device__ __forceinline__ size_t kv_off(const int *table, int t, int kvd) {
+    return table ? ((size_t)table[t >> 6] * QTC_KV_PAGE + (size_t)(t & (QTC_KV_PAGE - 1))) * (size_t)kvd : (size_t)t * (size_t)kvd;
+}
+
 /* programmatic dependent launch (batched path): every kernel of a captured frame starts with pdl_enter() - the next kernel may
  * be scheduled as soon as all CTAs of this one are resident (its launch latency and prologue overlap this kernel's run), and
  * nothing of this kernel's own work happens before the previous kernel has completed and flushed.  Without the launch

@@ -32,7 +32,8 @@ struct FusedArgs {
     const LmDev *lm;               /* device copy of the stack descriptor */
     float *x;                      /* [H] residual stream: input on entry, post-final-norm hidden on exit */
     float *q, *kk, *vv, *att, *g;  /* cross-CTA scratch in HBM/L2 */
-    float *kc, *vc;                /* [layers, kv_max, kvd] */
+    float *kc, *vc;                /* [layers, kv_max, kvd]: per layer a pool slice (paged, kv_max = pool positions) or a contiguous cache */
+    const int *table;              /* page table of the utterance (talker), NULL = contiguous (sub-talker) */
     const float *cos, *sin;        /* [kv_max, hd] */
     int kv_max;
     const int *pos_ptr; int pos_add;

@@ -42,7 +42,7 @@ __device__ __forceinline__ void att_stage_issue(const FusedArgs &a, const LmDev 
     const int te = p.t1 < pos ? p.t1 : pos, rows = te - p.t0;
     for (int i = threadIdx.x; i < rows * q4 * 2; i += FUSED_THREADS) {
         const int which = i >= rows * q4, j = which ? i - rows * q4 : i, r = j / q4, c = j - r * q4;
-        const float *src = (which ? vc : kc) + (size_t)(p.t0 + r) * kvd + c * 4;
+        const float *src = (which ? vc : kc) + kv_off(a.table, p.t0 + r, kvd) + c * 4;
         float *dst = kvs + (size_t)which * p.cap * hd + r * hd + c * 4;
         const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst);
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src));
@@ -104,7 +104,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
     }
     compute_sync();
     if (p.sp == 0 && h % rep == 0)
-        for (int i = tid; i < hd; i += FUSED_THREADS) { kc[(size_t)pos * kvd + g * hd + i] = ks[i]; vc[(size_t)pos * kvd + g * hd + i] = __ldcg(vr + i); }
+        for (int i = tid; i < hd; i += FUSED_THREADS) { kc[kv_off(a.table, pos, kvd) + g * hd + i] = ks[i]; vc[kv_off(a.table, pos, kvd) + g * hd + i] = __ldcg(vr + i); }
 
     /* scores of my KV range: a warp per position */
     const float scale = 1.0f / sqrtf((float)hd);
@@ -117,7 +117,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
                 const int t = tb + j * FUSED_WARPS;
                 if (t < t1 && t < pos)
                     kv[j] = p.staged ? *reinterpret_cast<const float4 *>(Ks + (size_t)(t - t0) * hd + lane * 4)
-                                     : __ldcg(reinterpret_cast<const float4 *>(kc + (size_t)t * kvd + g * hd) + lane);
+                                     : __ldcg(reinterpret_cast<const float4 *>(kc + kv_off(a.table, t, kvd) + g * hd) + lane);
                 else kv[j] = *reinterpret_cast<const float4 *>(ks + lane * 4);
             }
 #pragma unroll
@@ -133,7 +133,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
         for (int t = t0 + warp; t < t1; t += FUSED_WARPS) {
             float d = 0.0f;
             if (t < pos) {
-                const float *kt = p.staged ? Ks + (size_t)(t - t0) * hd : kc + (size_t)t * kvd + g * hd;
+                const float *kt = p.staged ? Ks + (size_t)(t - t0) * hd : kc + kv_off(a.table, t, kvd) + g * hd;
                 for (int i = lane; i < hd; i += 32) d = fmaf(qs[i], p.staged ? kt[i] : __ldcg(kt + i), d);
             } else for (int i = lane; i < hd; i += 32) d = fmaf(qs[i], ks[i], d);
             d = warp_sum(d);
@@ -165,7 +165,7 @@ __device__ __forceinline__ void cta_attention(const FusedArgs &a, const LmDev &l
             for (int j = 0; j < 8; j++) {
                 const int t = tb + j * ngrp;
                 v[j] = 0.0f;
-                if (t < t1) v[j] = t < pos ? (p.staged ? Vs[(size_t)(t - t0) * hd + dim] : __ldcg(vc + (size_t)t * kvd + g * hd + dim)) : __ldcg(vr + dim);
+                if (t < t1) v[j] = t < pos ? (p.staged ? Vs[(size_t)(t - t0) * hd + dim] : __ldcg(vc + kv_off(a.table, t, kvd) + g * hd + dim)) : __ldcg(vr + dim);
             }
 #pragma unroll
             for (int j = 0; j < 8; j++) {
@@ -227,8 +227,8 @@ __device__ __forceinline__ void cta_attention_small(const FusedArgs &a, const Lm
     (void)sgn;
     if (h % rep == 0) {
         float *kc = a.kc + (size_t)l * a.kv_max * kvd, *vc = a.vc + (size_t)l * a.kv_max * kvd;
-        *reinterpret_cast<float4 *>(kc + (size_t)pos * kvd + g * hd + lane * 4) = k_new;
-        *reinterpret_cast<float4 *>(vc + (size_t)pos * kvd + g * hd + lane * 4) = v_new;
+        *reinterpret_cast<float4 *>(kc + kv_off(a.table, pos, kvd) + g * hd + lane * 4) = k_new;
+        *reinterpret_cast<float4 *>(vc + kv_off(a.table, pos, kvd) + g * hd + lane * 4) = v_new;
     }
     const float *Ks = kvs, *Vs = kvs + (size_t)p.cap * hd;
     const float scale = 1.0f / sqrtf((float)hd);
@@ -304,8 +304,8 @@ __device__ __forceinline__ void cta_attention_warps(const FusedArgs &a, const Lm
     }
     if (writer) {
         float *kc = a.kc + (size_t)l * a.kv_max * kvd, *vc = a.vc + (size_t)l * a.kv_max * kvd;
-        *reinterpret_cast<float4 *>(kc + (size_t)pos * kvd + g * hd + lane * 4) = k_new;
-        *reinterpret_cast<float4 *>(vc + (size_t)pos * kvd + g * hd + lane * 4) = v_new;
+        *reinterpret_cast<float4 *>(kc + kv_off(a.table, pos, kvd) + g * hd + lane * 4) = k_new;
+        *reinterpret_cast<float4 *>(vc + kv_off(a.table, pos, kvd) + g * hd + lane * 4) = v_new;
     }
     const float *Ks = kvs, *Vs = kvs + (size_t)p.cap * hd;
     const float scale = 1.0f / sqrtf((float)hd);

@@ -59,12 +59,13 @@ static int prefill_dev(qtc_ctx *c, const float *embeds_dev, int seq_len) {
     return 0;
 }
 
-static int ensure_cap(float **buf, int *cap, int need_rows, int H) {
+static int ensure_cap(qtc_ctx *c, float **buf, int *cap, int need_rows, int H) {
     if (need_rows <= *cap) return 0;
     cudaFree(*buf);
     *buf = NULL;
     const int n = need_rows + 64;
     QTC_CUDA(cudaMalloc(buf, (size_t)n * H * 4));
+    QTC_COUNT_MALLOC(c);
     *cap = n;
     return 0;
 }
@@ -73,7 +74,7 @@ extern "C" int qwen_tts_cuda_talker_prefill(qtc_ctx_t *c, const float *input_emb
     if (need_lm(c)) return -1;
     if (!input_embeds || seq_len <= 0) { qtc_set_error("prefill: empty input"); return -1; }
     if (pull_state(c)) return -1;
-    if (ensure_cap(&c->prefill, &c->prefill_cap, seq_len, c->H)) return -1;
+    if (ensure_cap(c, &c->prefill, &c->prefill_cap, seq_len, c->H)) return -1;
     c->graph_key = -1;
     QTC_CUDA(cudaMemcpyAsync(c->prefill, input_embeds, (size_t)seq_len * c->H * 4, cudaMemcpyHostToDevice, c->stream));
     if (prefill_dev(c, c->prefill, seq_len)) return -1;
@@ -136,7 +137,7 @@ static int embed_text_dev(qtc_ctx *c, int token, float *out_dev) {
 extern "C" int qwen_tts_cuda_embed_text_tokens(qtc_ctx_t *c, const int *token_ids, int n, float *out) {
     if (need_lm(c)) return -1;
     if (!token_ids || !out || n <= 0) { qtc_set_error("embed_text_tokens: empty input"); return -1; }
-    if (ensure_cap(&c->prefill, &c->prefill_cap, n, c->H)) return -1;
+    if (ensure_cap(c, &c->prefill, &c->prefill_cap, n, c->H)) return -1;
     for (int i = 0; i < n; i++) if (embed_text_dev(c, token_ids[i], c->prefill + (size_t)i * c->H)) return -1;
     QTC_CUDA(cudaMemcpyAsync(out, c->prefill, (size_t)n * c->H * 4, cudaMemcpyDeviceToHost, c->stream));
     QTC_CUDA(cudaStreamSynchronize(c->stream));
@@ -150,6 +151,7 @@ static int params_key(const qtc_ctx *c) {
     for (size_t i = 0; i < sizeof(c->params); i++) h = (h ^ p[i]) * 16777619u;
     h = (h ^ (uint32_t)c->mode) * 16777619u;
     h = (h ^ (uint32_t)c->arith) * 16777619u;
+    if (c->mode == 0 || c->arith) h = (h ^ (uint32_t)c->kv.used[0]) * 16777619u;   /* per-op attention: the score buffer (dynamic smem) is sized by the capacity */
     return (int)(h & 0x7fffffff);
 }
 
@@ -243,11 +245,13 @@ int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, in
     const int fixed = c->params.fixed_codec_tokens > 0 ? c->params.fixed_codec_tokens : 0;
     if (limit <= 0) return 0;
     const double t0 = now_ms();
+    if (c->kv.used[0] * QTC_KV_PAGE_POS < prefill_len + limit + 1 && (int)c->kv.free_pages.size() * QTC_KV_PAGE_POS < prefill_len + limit + 1) qtc_kv_release_all(c);   /* pages of an earlier batch */
     if (qtc_ensure_kv(c, &c->tk, &c->talker, prefill_len + limit + 1)) return -1;
     if (limit > c->codes_cap) {
         cudaFree(c->codes); cudaFreeHost(c->codes_host);
         c->codes = NULL; c->codes_host = NULL;
         QTC_CUDA(cudaMalloc(&c->codes, (size_t)(limit + 64) * G * 4));
+        QTC_COUNT_MALLOC(c);
         QTC_CUDA(cudaMallocHost(&c->codes_host, (size_t)(limit + 64) * G * 4));
         c->codes_cap = limit + 64;
         c->graph_key = -1;
@@ -353,7 +357,7 @@ extern "C" int qwen_tts_cuda_generate_frames(qtc_ctx_t *c, const float *prefill_
     int limit = fixed > 0 ? fixed : c->params.max_new_tokens;
     if (limit > max_tokens) limit = max_tokens;
     const float *old_tr = c->trailing;
-    if (ensure_cap(&c->prefill, &c->prefill_cap, prefill_len, H) || ensure_cap(&c->trailing, &c->trailing_cap, n_trailing, H)) return -1;
+    if (ensure_cap(c, &c->prefill, &c->prefill_cap, prefill_len, H) || ensure_cap(c, &c->trailing, &c->trailing_cap, n_trailing, H)) return -1;
     if (old_tr != c->trailing) c->graph_key = -1;          /* the graphs hold the buffer's address */
     QTC_CUDA(cudaMemcpyAsync(c->prefill, prefill_embeds, (size_t)prefill_len * H * 4, cudaMemcpyHostToDevice, c->stream));
     QTC_CUDA(cudaMemcpyAsync(c->trailing, trailing_text, (size_t)n_trailing * H * 4, cudaMemcpyHostToDevice, c->stream));
@@ -432,7 +436,7 @@ extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const c
     if (ntr < 1) ntr = 1;
     /* the prompt is assembled in HBM; nothing crosses the bus except the token ids */
     const float *old_tr = c->trailing;
-    if (ensure_cap(&c->prefill, &c->prefill_cap, plen_max + 3, c->H) || ensure_cap(&c->trailing, &c->trailing_cap, ntr, c->H)) return NULL;
+    if (ensure_cap(c, &c->prefill, &c->prefill_cap, plen_max + 3, c->H) || ensure_cap(c, &c->trailing, &c->trailing_cap, ntr, c->H)) return NULL;
     if (old_tr != c->trailing) c->graph_key = -1;
     int plen = 0;
     if (qtc_build_prompt_dev(c, tok.data(), (int)tok.size(), spk, lang, c->prefill, &plen, c->trailing, &ntr, c->tts_pad)) return NULL;

@@ -83,9 +83,23 @@ struct SampleCfg {
     float rep_penalty;                /* 1.0 = off */
 };
 
+/* the talker's paged KV pool (qtc_device.cuh: kv_off): allocated once at upload, never grown or copied.  Slots are
+ * sequences (slot 0: the batch-1 utterance and the stage API; slots 0..B-1: the rows of a lock-step batch). */
+#define QTC_KV_PAGE_POS 64
+struct KvPool {
+    int pages = 0;                     /* pages per layer */
+    int slots = 0, max_seq_pages = 0;
+    int *tables = NULL;                /* device [slots][max_seq_pages] */
+    int *tables_host = NULL;           /* pinned mirror */
+    std::vector<int> free_pages;       /* stack of free page ids */
+    std::vector<int> used;             /* pages held by each slot */
+    long long page_allocs = 0;         /* pages handed out so far */
+};
+
 /* one decoder stack's mutable buffers */
 struct LmBuffers {
-    float *k, *v;                 /* [layers, kv_max, kv_heads*head_dim] f32 */
+    float *k, *v;                 /* [layers, kv_max, kv_heads*head_dim] f32: talker = the pool (kv_max = pool positions per layer) */
+    const int *table;             /* talker: page table of slot 0 (device); sub-talker: NULL (contiguous) */
     int kv_max;
     float *cos, *sin;             /* [kv_max, head_dim], host-computed with the oracle's expression */
     float *x, *xn, *q, *kk, *vv, *att, *g, *logits;
@@ -105,6 +119,8 @@ struct qtc_ctx {
     const uint16_t *sub_in_w;
     const float *sub_in_b;
     LmBuffers tk, st;
+    KvPool kv;
+    long long dev_mallocs;        /* cudaMalloc calls made for this context after upload returned (steady state: none) */
     /* generation */
     GenState *state;              /* device */
     GenState *state_host;         /* pinned mirror */
@@ -172,6 +188,10 @@ int qtc_embed_row(qtc_ctx *c, float *out, const uint16_t *table, const int *idx_
 int qtc_sample(qtc_ctx *c, const float *logits, const SampleCfg &cfg, uint32_t *rng, int *hist_count,
                int *out_token, GenState *st, int role);
 int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need);
+int qtc_kv_pool_init(qtc_ctx *c, int max_batch);
+int qtc_kv_reserve(qtc_ctx *c, int slot, int positions);      /* the slot holds pages for at least `positions` positions */
+void qtc_kv_release_all(qtc_ctx *c);
+#define QTC_COUNT_MALLOC(c) ((c)->dev_mallocs++)
 int qtc_talker_forward_dev(qtc_ctx *c, const float *embed_dev);   /* one decode step + head -> tk.logits */
 int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code_ptr, int *codes_out_dev);
 int qtc_sample_talker(qtc_ctx *c);

@@ -105,30 +105,86 @@ static void rope_rows_host(float *cs, float *sn, int pos0, int npos, int hd, flo
         }
 }
 
-/* grow-only KV cache + rope table; contents are preserved (the reference reallocs, c/qwen_tts_talker.c:489-496) */
-int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
-    if (need <= b->kv_max) return 0;
-    QTC_CUDA(cudaStreamSynchronize(c->stream));
-    const int nmax = ((need + 255) / 256) * 256;
+/* ---- paged KV pool (north_star: "GQA attention over an HBM-resident paged KV cache") -----------------------------------
+ * One allocation per K and V at upload: [layers][pages][64][kvd] fp32; RoPE rows for every position a sequence can reach are
+ * computed then too.  After that, growing a sequence is a host-side pop from the free list plus a 4-byte table update: no
+ * cudaMalloc, no device-to-device copy of the cache, no stale graph (the reference reallocs and copies the whole cache,
+ * c/qwen_tts_talker.c:489-496; round 1 did the same on the device). */
+int qtc_kv_pool_init(qtc_ctx *c, int max_batch) {
+    const LmDev *lm = &c->talker;
     const size_t kvd = (size_t)lm->kv_heads * lm->head_dim, hd = lm->head_dim;
-    float *nk = NULL, *nv = NULL, *ncs = NULL, *nsn = NULL;
-    QTC_CUDA(cudaMalloc(&nk, (size_t)lm->layers * nmax * kvd * 4 + 16));
-    QTC_CUDA(cudaMalloc(&nv, (size_t)lm->layers * nmax * kvd * 4 + 16));
-    QTC_CUDA(cudaMalloc(&ncs, (size_t)nmax * hd * 4));
-    QTC_CUDA(cudaMalloc(&nsn, (size_t)nmax * hd * 4));
-    if (b->kv_max > 0)
-        for (int l = 0; l < lm->layers; l++) {
-            QTC_CUDA(cudaMemcpy(nk + (size_t)l * nmax * kvd, b->k + (size_t)l * b->kv_max * kvd, (size_t)b->kv_max * kvd * 4, cudaMemcpyDeviceToDevice));
-            QTC_CUDA(cudaMemcpy(nv + (size_t)l * nmax * kvd, b->v + (size_t)l * b->kv_max * kvd, (size_t)b->kv_max * kvd * 4, cudaMemcpyDeviceToDevice));
-        }
+    KvPool &p = c->kv;
+    p.slots = max_batch > 1 ? (max_batch > 64 ? 64 : max_batch) : 1;
+    /* a single utterance may run to max_new_tokens = 4096 frames after a prompt; a batch row gets 576 positions on average */
+    int positions = 4096 + 192;
+    if (p.slots * 576 > positions) positions = p.slots * 576;
+    p.pages = (positions + QTC_KV_PAGE_POS - 1) / QTC_KV_PAGE_POS;
+    p.max_seq_pages = p.pages;
+    const size_t floats = (size_t)lm->layers * p.pages * QTC_KV_PAGE_POS * kvd;
+    QTC_CUDA(cudaMalloc(&c->tk.k, floats * 4 + 16));
+    QTC_CUDA(cudaMalloc(&c->tk.v, floats * 4 + 16));
+    QTC_CUDA(cudaMalloc(&p.tables, (size_t)p.slots * p.max_seq_pages * 4));
+    QTC_CUDA(cudaMallocHost(&p.tables_host, (size_t)p.slots * p.max_seq_pages * 4));
+    memset(p.tables_host, 0, (size_t)p.slots * p.max_seq_pages * 4);
+    QTC_CUDA(cudaMemset(p.tables, 0, (size_t)p.slots * p.max_seq_pages * 4));
+    p.free_pages.clear();
+    for (int i = p.pages - 1; i >= 0; i--) p.free_pages.push_back(i);      /* page 0 is handed out first */
+    p.used.assign(p.slots, 0);
+    c->tk.kv_max = p.pages * QTC_KV_PAGE_POS;
+    c->tk.table = p.tables;
+    const int npos = c->tk.kv_max;
+    std::vector<float> hc((size_t)npos * hd), hs((size_t)npos * hd);
+    rope_rows_host(hc.data(), hs.data(), 0, npos, (int)hd, lm->theta);
+    QTC_CUDA(cudaMalloc(&c->tk.cos, hc.size() * 4));
+    QTC_CUDA(cudaMalloc(&c->tk.sin, hs.size() * 4));
+    QTC_CUDA(cudaMemcpy(c->tk.cos, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice));
+    QTC_CUDA(cudaMemcpy(c->tk.sin, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
+    return 0;
+}
+void qtc_kv_release_all(qtc_ctx *c) {
+    KvPool &p = c->kv;
+    for (int s = 0; s < p.slots; s++) {
+        for (int i = p.used[s] - 1; i >= 0; i--) p.free_pages.push_back(p.tables_host[(size_t)s * p.max_seq_pages + i]);
+        p.used[s] = 0;
+    }
+}
+int qtc_kv_reserve(qtc_ctx *c, int slot, int positions) {
+    KvPool &p = c->kv;
+    if (slot < 0 || slot >= p.slots) { qtc_set_error("kv: slot %d outside the %d slots this context was uploaded with (max_batch)", slot, p.slots); return -1; }
+    const int need = (positions + QTC_KV_PAGE_POS - 1) / QTC_KV_PAGE_POS, have = p.used[slot];
+    if (need <= have) return 0;
+    if (need > p.max_seq_pages || need - have > (int)p.free_pages.size()) {
+        qtc_set_error("kv: pool exhausted (%d pages of 64 positions, %zu free, sequence %d needs %d more): upload with a larger max_batch",
+                      p.pages, p.free_pages.size(), slot, need - have);
+        return -1;
+    }
+    int *row = p.tables_host + (size_t)slot * p.max_seq_pages;
+    for (int i = have; i < need; i++) { row[i] = p.free_pages.back(); p.free_pages.pop_back(); p.page_allocs++; }
+    p.used[slot] = need;
+    /* the new entries only; kernels already enqueued never read them (their positions are lower) */
+    QTC_CUDA(cudaMemcpyAsync(p.tables + (size_t)slot * p.max_seq_pages + have, row + have, (size_t)(need - have) * 4, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+/* talker: pages for `need` positions of slot 0.  Sub-talker: its contiguous cache of G + 2 positions, allocated once at upload. */
+int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
+    if (b == &c->tk) {
+        if (need > b->kv_max) { qtc_set_error("kv: %d positions asked, the pool holds %d per sequence", need, b->kv_max); return -1; }
+        return qtc_kv_reserve(c, 0, need);
+    }
+    if (need <= b->kv_max) return 0;
+    if (b->kv_max > 0) { qtc_set_error("kv: the sub-talker cache holds %d positions, %d asked", b->kv_max, need); return -1; }
+    const int nmax = ((need + 63) / 64) * 64;
+    const size_t kvd = (size_t)lm->kv_heads * lm->head_dim, hd = lm->head_dim;
+    QTC_CUDA(cudaMalloc(&b->k, (size_t)lm->layers * nmax * kvd * 4 + 16));
+    QTC_CUDA(cudaMalloc(&b->v, (size_t)lm->layers * nmax * kvd * 4 + 16));
+    QTC_CUDA(cudaMalloc(&b->cos, (size_t)nmax * hd * 4));
+    QTC_CUDA(cudaMalloc(&b->sin, (size_t)nmax * hd * 4));
     std::vector<float> hc((size_t)nmax * hd), hs((size_t)nmax * hd);
     rope_rows_host(hc.data(), hs.data(), 0, nmax, (int)hd, lm->theta);
-    QTC_CUDA(cudaMemcpy(ncs, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice));
-    QTC_CUDA(cudaMemcpy(nsn, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
-    cudaFree(b->k); cudaFree(b->v); cudaFree(b->cos); cudaFree(b->sin);
-    b->k = nk; b->v = nv; b->cos = ncs; b->sin = nsn; b->kv_max = nmax;
-    c->graph_key = -1;      /* pointers changed: captured graphs are stale - the batched ones too (they hold cos/sin) */
-    if (c->bb) qtc_batch_invalidate_graphs(c);
+    QTC_CUDA(cudaMemcpy(b->cos, hc.data(), hc.size() * 4, cudaMemcpyHostToDevice));
+    QTC_CUDA(cudaMemcpy(b->sin, hs.data(), hs.size() * 4, cudaMemcpyHostToDevice));
+    b->kv_max = nmax; b->table = NULL;
     return 0;
 }
 
@@ -152,7 +208,7 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     memset(&a, 0, sizeof(a));
     a.lm = lm == &c->talker ? c->talker_dev : c->sub_dev;
     a.x = b->x; a.q = b->q; a.kk = b->kk; a.vv = b->vv; a.att = b->att; a.g = b->g;
-    a.kc = b->k; a.vc = b->v; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
+    a.kc = b->k; a.vc = b->v; a.table = b->table; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
     a.pos_ptr = pos_ptr; a.pos_add = pos_add;
     a.head_w = head_w; a.head_rows = head_rows; a.logits = logits;
     a.bar = c->bar; a.head_cnt = c->head_cnt; a.part = c->attn_part; a.st = st;
@@ -197,11 +253,13 @@ int qtc_lm_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, i
         AttnArgs a;
         a.q = b->q; a.k = b->kk; a.v = b->vv; a.q_norm = w->q_norm; a.k_norm = w->k_norm;
         a.cos = b->cos; a.sin = b->sin;
-        a.kc = b->k + (size_t)l * b->kv_max * kvd; a.vc = b->v + (size_t)l * b->kv_max * kvd;
+        a.kc = b->k + (size_t)l * b->kv_max * kvd; a.vc = b->v + (size_t)l * b->kv_max * kvd; a.table = b->table;
         a.att = b->att; a.pos_ptr = pos_ptr; a.pos_add = pos_add;
         a.heads = lm->heads; a.kv_heads = lm->kv_heads; a.hd = hd; a.eps = lm->eps;
         a.scale = 1.0f / sqrtf((float)hd);
-        const size_t smem = (size_t)(2 * hd + b->kv_max + 32) * 4;
+        const int cap = b == &c->tk ? c->kv.used[0] * QTC_KV_PAGE_POS : b->kv_max;      /* positions this sequence can reach */
+        const size_t smem = (size_t)(2 * hd + cap + 32) * 4;
+        if (smem > 160 * 1024) { qtc_set_error("per-op attention: %d positions do not fit its score buffer (use the fused mode)", cap); return -1; }
         if (c->arith == QTC_STRICT) k_attn_decode<QTC_STRICT><<<lm->heads, 128, smem, c->stream>>>(a);
         else k_attn_decode<QTC_FAST><<<lm->heads, 128, smem, c->stream>>>(a);
         LAUNCH_CHECK(c);

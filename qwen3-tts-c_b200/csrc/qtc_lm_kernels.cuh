@@ -41,7 +41,8 @@ struct AttnArgs {
     const float *q, *k, *v;        /* raw projections of this token: [heads*hd], [kvh*hd], [kvh*hd] */
     const float *q_norm, *k_norm;  /* [hd] */
     const float *cos, *sin;        /* [kv_max, hd] */
-    float *kc, *vc;                /* this layer's cache [kv_max, kvh*hd] */
+    float *kc, *vc;                /* this layer's cache: pool slice (paged) or [kv_max, kvh*hd] */
+    const int *table;              /* page table of the utterance, or NULL (contiguous) */
     float *att;                    /* out [heads*hd] */
     const int *pos_ptr; int pos_add;
     int heads, kv_heads, hd;
@@ -107,8 +108,8 @@ __global__ void __launch_bounds__(128) k_attn_decode(const AttnArgs a) {
     const float *vr = a.v + g * hd;
     if (h % rep == 0)                                         /* KV append, c/qwen_tts_talker.c:192-196 */
         for (int i = threadIdx.x; i < hd; i += blockDim.x) {
-            a.kc[(size_t)pos * kvd + g * hd + i] = ks[i];
-            a.vc[(size_t)pos * kvd + g * hd + i] = vr[i];
+            a.kc[kv_off(a.table, pos, kvd) + g * hd + i] = ks[i];
+            a.vc[kv_off(a.table, pos, kvd) + g * hd + i] = vr[i];
         }
 
     /* scores */
@@ -117,7 +118,7 @@ __global__ void __launch_bounds__(128) k_attn_decode(const AttnArgs a) {
         for (int t = threadIdx.x; t < n; t += blockDim.x) {
             float d = 0.0f;
             if (t < pos) {
-                const float4 *kt = reinterpret_cast<const float4 *>(a.kc + (size_t)t * kvd + g * hd);
+                const float4 *kt = reinterpret_cast<const float4 *>(a.kc + kv_off(a.table, t, kvd) + g * hd);
                 for (int i = 0; i < hd / 4; i++) {
                     const float4 kv = kt[i];
                     d = __fadd_rn(d, __fmul_rn(qs[4 * i], kv.x)); d = __fadd_rn(d, __fmul_rn(qs[4 * i + 1], kv.y));
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(128) k_attn_decode(const AttnArgs a) {
     } else {
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
         for (int t = warp; t < n; t += nw) {
-            const float *kt = t < pos ? a.kc + (size_t)t * kvd + g * hd : ks;
+            const float *kt = t < pos ? a.kc + kv_off(a.table, t, kvd) + g * hd : ks;
             float d = 0.0f;
             for (int i = lane; i < hd; i += 32) d = fmaf(qs[i], kt[i], d);
             d = warp_sum(d);
@@ -167,13 +168,13 @@ __global__ void __launch_bounds__(128) k_attn_decode(const AttnArgs a) {
         float o = 0.0f;
         const float *vcol = a.vc + g * hd + i;
         if (ARITH == QTC_STRICT) {
-            for (int t = 0; t < pos; t++) o = __fadd_rn(o, __fmul_rn(sc[t], vcol[(size_t)t * kvd]));
+            for (int t = 0; t < pos; t++) o = __fadd_rn(o, __fmul_rn(sc[t], vcol[kv_off(a.table, t, kvd)]));
             o = __fadd_rn(o, __fmul_rn(sc[pos], vr[i]));
         } else {
             float o1 = 0.0f;
             int t = 0;
-            for (; t + 1 < pos; t += 2) { o = fmaf(sc[t], vcol[(size_t)t * kvd], o); o1 = fmaf(sc[t + 1], vcol[(size_t)(t + 1) * kvd], o1); }
-            for (; t < pos; t++) o = fmaf(sc[t], vcol[(size_t)t * kvd], o);
+            for (; t + 1 < pos; t += 2) { o = fmaf(sc[t], vcol[kv_off(a.table, t, kvd)], o); o1 = fmaf(sc[t + 1], vcol[kv_off(a.table, t + 1, kvd)], o1); }
+            for (; t < pos; t++) o = fmaf(sc[t], vcol[kv_off(a.table, t, kvd)], o);
             o = fmaf(sc[pos], vr[i], o + o1);
         }
         a.att[h * hd + i] = o;

@@ -94,7 +94,9 @@ class Perf(C.Structure):
                 ("prefill_ms", C.c_double), ("codec_tokens", C.c_int), ("stop_reason", C.c_int),
                 ("stop_step", C.c_int), ("kernel_launches", C.c_longlong),
                 ("device_ms", C.c_double), ("ttff_ms", C.c_double), ("ttfa_ms", C.c_double),
-                ("frame_ms_p50", C.c_double), ("frame_ms_p99", C.c_double)]
+                ("frame_ms_p50", C.c_double), ("frame_ms_p99", C.c_double),
+                ("device_mallocs", C.c_longlong), ("kv_page_allocs", C.c_longlong),
+                ("kv_pool_pages", C.c_int), ("kv_pages_in_use", C.c_int)]
 
 
 PcmCallback = C.CFUNCTYPE(None, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p)

@@ -162,6 +162,10 @@ def test_long_kv_on_17b_layers_vs_oracle(cuda, orc):
     assert cuda.qwen_tts_cuda_talker_prefill(ctx, B.fptr(emb), n_pre) == 0
     worst = 0.0
     want, got = np.zeros(V, dtype=np.float32), np.zeros(V, dtype=np.float32)
+    perf = B.Perf()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    mallocs0, pages0 = perf.device_mallocs, perf.kv_pages_in_use
+    assert pages0 == 1                                    # 40 positions: one page of 64
     for i in range(n_steps):
         orc.orc_talker_forward(s, B.fptr(emb[n_pre + i]), B.fptr(want))
         assert cuda.qwen_tts_cuda_talker_forward(ctx, B.fptr(emb[n_pre + i]), B.fptr(got)) == 0
@@ -169,6 +173,8 @@ def test_long_kv_on_17b_layers_vs_oracle(cuda, orc):
         assert int(got.argmax()) == int(want.argmax()), i
     assert worst <= 5e-4, worst
     assert cuda.qwen_tts_cuda_get_kv_len(ctx) == n_pre + n_steps
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    assert perf.kv_pages_in_use == 7 and perf.device_mallocs == mallocs0      # six page boundaries crossed, not one cudaMalloc
     orc.orc_destroy(s)
     cuda.qwen_tts_cuda_release(ctx)
 
@@ -177,7 +183,7 @@ def test_batch64_rows_vs_oracle_17b(cuda, orc):
     """config 4 shapes: 64 ragged prompts in lock-step on the 1.7B model, 3 frames; rows 0, 29 and 63 against the oracle's
     solo run of the same prompt with seed + row (codes equal)"""
     hm = get_model(orc, "1.7b")
-    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 64)
     assert ctx, cuda.qwen_tts_cuda_last_error()
     nb, frames, G = 64, 3, 16
     cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]

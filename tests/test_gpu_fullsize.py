@@ -25,7 +25,7 @@ CSV = ",".join(str(t) for t in FIXTURE_TOKENS).encode()
 @pytest.fixture(scope="module")
 def big(cuda, orc):
     hm = get_model(orc, "1.7b")
-    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 64)          # KV pool sized for 64 lock-step rows (config 4)
     assert ctx, cuda.qwen_tts_cuda_last_error()
     yield hm, ctx
     cuda.qwen_tts_cuda_release(ctx)
