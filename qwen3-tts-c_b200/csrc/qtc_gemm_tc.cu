@@ -16,11 +16,12 @@
  */
 #include "qtc_internal.h"
 #include "qtc_device.cuh"
+#include "qtc_tc.cuh"
 
 #include <cuda.h>
 #include <unordered_map>
 
-#define TC_BM 128           /* weight rows per CTA (UMMA M) */
+
 #define TC_BN 64            /* batch columns per piece; UMMA N = 64 x pieces */
 #define TC_BK 64            /* K per stage: 64 bf16 = one 128-byte swizzle row */
 #define TC_A_BYTES (TC_BM * TC_BK * 2)
@@ -35,53 +36,6 @@ template <int NP> struct TcCfg {
     static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
     static constexpr int TMEM_COLS = NP == 1 ? 64 : 256;       /* power of two >= N */
 };
-
-__device__ __forceinline__ uint32_t tc_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void tc_mbar_init(uint64_t *bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tc_smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void tc_mbar_expect_tx(uint64_t *bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tc_smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void tc_mbar_wait(uint64_t *bar, unsigned parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "TCW_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra TCD_%=;\n"
-        "bra TCW_%=;\n"
-        "TCD_%=:\n"
-        "}\n" ::"r"(tc_smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tc_tma_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 ::"r"(tc_smem_u32(dst)), "l"(map), "r"(tc_smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
-/* K-major operand tile in SWIZZLE_128B layout: rows of 128 bytes, 8-row groups 1024 bytes apart */
-__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t addr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((addr & 0x3ffffu) >> 4);          /* start address, 16-byte units           [0,14)  */
-    d |= (uint64_t)(1024 >> 4) << 32;                 /* stride byte offset (8 rows x 128 B)    [32,46) */
-    d |= 1ull << 46;                                  /* descriptor version (sm_100)            [46,48) */
-    d |= 2ull << 61;                                  /* layout: SWIZZLE_128B                   [61,64) */
-    return d;
-}
-/* kind::f16 instruction descriptor: D f32, A/B bf16, both K-major, M = 128, N = n */
-__device__ __forceinline__ uint32_t tc_idesc(int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-}
-__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void tc_commit(uint64_t *bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tc_smem_u32(bar)) : "memory");
-}
 
 /* grid (row tiles, K splits).  Y [batch, ldy] fp32, pre-initialised; rows >= N and batch columns >= nbatch are dropped */
 /* EPI 0: Y += acc (fp32 reductions in L2, any K split).
@@ -241,7 +195,7 @@ static int make_map(CUtensorMap *m, const void *ptr, int rows, int cols, int box
 struct MapKey { const void *p; int rows, cols, box; bool operator==(const MapKey &o) const { return p == o.p && rows == o.rows && cols == o.cols && box == o.box; } };
 struct MapHash { size_t operator()(const MapKey &k) const { return std::hash<const void *>()(k.p) ^ ((size_t)k.rows * 1315423911u) ^ ((size_t)k.cols << 20) ^ (size_t)k.box; } };
 static std::unordered_map<MapKey, CUtensorMap, MapHash> g_maps;
-static const CUtensorMap *cached_map(const void *ptr, int rows, int cols, int box) {
+const CUtensorMap *qtc_tmap_bf16(const void *ptr, int rows, int cols, int box) {
     const MapKey k = {ptr, rows, cols, box};
     auto it = g_maps.find(k);
     if (it != g_maps.end()) return &it->second;
@@ -285,7 +239,7 @@ int qtc_gemm_tc_ex(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint1
         QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM));
         g_tc_attr = 1;
     }
-    const CUtensorMap *mw = cached_map(W, N, K, TC_BM), *mx = cached_map(X, TC_BN * pieces, K, TC_BN * pieces);
+    const CUtensorMap *mw = qtc_tmap_bf16(W, N, K, TC_BM), *mx = qtc_tmap_bf16(X, TC_BN * pieces, K, TC_BN * pieces);
     if (!mw || !mx) return -1;
     const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = swiglu_out ? 1 : pick_splits(tiles, kblocks, c->num_sms);
     if (swiglu_out && (N & 1)) { qtc_set_error("gemm_tc: interleaved gate/up needs an even row count"); return -1; }

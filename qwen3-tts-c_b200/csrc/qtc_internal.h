@@ -209,6 +209,16 @@ void qtc_gemm_tc_forget(const void *ptr);
 void *qtc_dmalloc(qtc_ctx *c, size_t bytes);
 template <class T> T *qtc_upload(qtc_ctx *c, const T *host, size_t n);
 
+/* ---- vocoder convolutions on tcgen05 (qtc_conv_tc.cu) ------------------------ */
+struct ConvTcW { const uint16_t *hi, *lo; int cin, cout, taps, phases; };   /* weight planes [phases*taps*cout, cin] bf16 */
+bool qtc_conv_tc_ok(int cin, int cout);
+int qtc_conv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cout, int cin, int K);
+int qtc_tconv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cin, int cout, int k, int s);
+int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint16_t *in_lo, int L, int dil, const float *bias, const float *res,
+                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta);
+int qtc_cf_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, int C, int L, const float *alpha, const float *inv_beta);
+int qtc_mono_from_planes(qtc_ctx *c, float *out, const uint16_t *hi, const uint16_t *lo, const float *w, const float *bias, int C, int K, int L);
+
 /* ---- codec (qtc_codec.cu) --------------------------------------------------- */
 CodecDev *qtc_codec_upload(qtc_ctx *c, const qtc_codec_t *k);
 void qtc_codec_release(CodecDev *cd);

@@ -270,3 +270,35 @@ extern "C" double qwen_tts_cuda_bench_subtalker(qtc_ctx_t *c, int iters, int do_
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return total / iters;
 }
+
+/* test surface of the tensor-core convolution (qtc_conv_tc.cu): kernel_causal_conv1d (stride <= 1) or kernel_transposed_conv1d
+ * (stride > 1; w is then [cin, cout, k]) on channels-first host input [cin, length] with SnakeBeta(alpha, inv_beta) applied to
+ * the input first (NULL: none) and an optional residual; the result is TIME-MAJOR [out_length, cout] fp32, as the vocoder keeps it */
+extern "C" int qwen_tts_cuda_conv1d_tc(float *out_tm, const float *in, const float *w, const float *b, int cin, int cout, int k, int length,
+                                       int dilation, int stride, const float *alpha, const float *inv_beta, const float *res_tm) {
+    qtc_ctx *c = kctx();
+    if (!c || !out_tm || !in || !w || cin <= 0 || cout <= 0 || k <= 0 || length <= 0) return -1;
+    if (!qtc_conv_tc_ok(cin, cout)) { qtc_set_error("conv1d_tc: cin %% 8 / cout %% 16"); return -1; }
+    const int s = stride > 1 ? stride : 1;
+    const size_t Lout = (size_t)length * s;
+    ConvTcW W;
+    const size_t allocs0 = c->allocs.size();
+    if (s > 1 ? qtc_tconv_tc_prep(c, &W, w, cin, cout, k, s) : qtc_conv_tc_prep(c, &W, w, cout, cin, k)) return -1;
+    DevBuf di((size_t)cin * length * 4), dh((size_t)cin * length * 2), dl((size_t)cin * length * 2), db((size_t)cout * 4), dy(Lout * cout * 4);
+    DevBuf da((size_t)cin * 4), dib((size_t)cin * 4);
+    int rc = -1;
+    if (di.p && dh.p && dl.p && db.p && dy.p && da.p && dib.p) {
+        H2D(di.p, in, (size_t)cin * length * 4);
+        if (b) H2D(db.p, b, (size_t)cout * 4);
+        if (alpha) { H2D(da.p, alpha, (size_t)cin * 4); H2D(dib.p, inv_beta, (size_t)cin * 4); }
+        if (res_tm) H2D(dy.p, res_tm, Lout * cout * 4);
+        rc = qtc_cf_to_planes(c, dh.as<uint16_t>(), dl.as<uint16_t>(), di.as<float>(), cin, length, alpha ? da.as<float>() : NULL, alpha ? dib.as<float>() : NULL);
+        if (rc == 0) rc = qtc_conv_tc(c, &W, dh.as<uint16_t>(), dl.as<uint16_t>(), length, dilation, b ? db.as<float>() : NULL, res_tm ? dy.as<float>() : NULL,
+                                      dy.as<float>(), NULL, NULL, NULL, NULL);
+        if (rc == 0 && cudaStreamSynchronize(c->stream) != cudaSuccess) { qtc_set_error("conv1d_tc: %s", cudaGetErrorString(cudaGetLastError())); rc = -1; }
+        if (rc == 0) D2H(out_tm, dy.p, Lout * cout * 4);
+    }
+    qtc_gemm_tc_forget(dh.p); qtc_gemm_tc_forget(dl.p);
+    while (c->allocs.size() > allocs0) { qtc_gemm_tc_forget(c->allocs.back()); cudaFree(c->allocs.back()); c->allocs.pop_back(); }
+    return rc;
+}
