@@ -256,6 +256,8 @@ float *qwen_tts_cuda_generate(qtc_ctx_t *ctx, const char *text, const char *spea
  * pays the decoder's fixed cost once more, so throughput is a few per cent lower than with the default, chunk_frames <= 0:
  * the reference's decode-at-the-end order. */
 int  qwen_tts_cuda_set_streaming(qtc_ctx_t *ctx, int first_frames, int chunk_frames);
+/* vocoder convolutions (c/qwen_tts_kernels.c:659-972): 1 (default) tcgen05 implicit GEMMs, 0 fp32 FFMA kernels */
+int  qwen_tts_cuda_set_codec_tc(qtc_ctx_t *ctx, int on);
 void qwen_tts_cuda_set_stream_callback(qtc_ctx_t *ctx, qtc_pcm_callback_t cb, void *user);
 /* stage-level: a decode session of up to max_frames frames fed chunk by chunk.  push: codes [n, num_quantizers] (host) are
  * the NEXT n frames, pcm_out (host) receives exactly their n * 1920 samples; returns the sample count or -1. */

@@ -150,6 +150,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
          cudaMallocHost(&c->host_stage, c->host_stage_bytes) == cudaSuccess;
     c->codes_host = NULL;
     c->cstream = c->stream;
+    { const char *e = getenv("QTC_CODEC_TC"); c->codec_tc = e ? atoi(e) : 1; }
     c->pcm_dev = NULL; c->pcm_cap = 0; c->first_pcm_host = NULL; c->stream_first = 8; c->stream_chunk = 0;      /* decode at the end unless qwen_tts_cuda_set_streaming asks for chunks */ c->stream_cb = NULL; c->stream_user = NULL;
     if (!ok) { qtc_set_error("stream/event/pinned allocation failed"); qwen_tts_cuda_release(c); return NULL; }
     if (c->G < 1 || c->G > QTC_MAX_GROUPS) { qtc_set_error("num_code_groups %d out of range", c->G); qwen_tts_cuda_release(c); return NULL; }
@@ -235,6 +236,13 @@ extern "C" void qwen_tts_cuda_get_perf(const qtc_ctx_t *c, qtc_perf_t *out) {
 extern "C" int qwen_tts_cuda_set_mode(qtc_ctx_t *c, int mode) {
     if (!c || mode < 0 || mode > 1) return -1;
     c->mode = mode; c->graph_key = -1;
+    return 0;
+}
+/* 1 (default): the vocoder's convolutions run on the tensor cores (two bf16 pieces per value, three MMAs per product);
+ * 0: the fp32 FFMA kernels (round 1's path, kept as the A/B baseline and for decoders whose channel counts do not tile) */
+extern "C" int qwen_tts_cuda_set_codec_tc(qtc_ctx_t *c, int on) {
+    if (!c) return -1;
+    c->codec_tc = on ? 1 : 0;
     return 0;
 }
 extern "C" int qwen_tts_cuda_set_arith(qtc_ctx_t *c, int strict) {

@@ -33,6 +33,9 @@ struct CodecDev {
     const float *voc_pre_w, *voc_pre_b;
     struct { const float *alpha, *beta; TconvDev tc; ResUnitDev ru[3]; } block[4];
     const float *fin_alpha, *fin_beta, *fin_w, *fin_b;
+    /* the same vocoder weights as bf16 hi/lo planes for the tensor-core path (qtc_conv_tc.cu); tc_ok: every layer is tileable */
+    ConvTcW tc_pre, tc_t[4], tc_c1[4][3], tc_c2[4][3];
+    bool tc_ok;
     /* workspace, grown on demand */
     float *ws; size_t ws_bytes;
     int *codes_dev; int codes_cap;
@@ -126,6 +129,21 @@ CodecDev *qtc_codec_upload(qtc_ctx *c, const qtc_codec_t *k) {
     }
     UP(d->fin_alpha, k->final_alpha, dim); UP(d->fin_beta, k->final_beta, dim);
     UP(d->fin_w, k->final_conv_w, (size_t)dim * 7); UP(d->fin_b, k->final_conv_b, 1);
+    /* tensor-core path: all vocoder channel counts must tile (multiples of 16 out, 8 in); the decoder of the 12 Hz tokenizer
+     * (1536 / 768 / 384 / 192 / 96) does, toy decoders fall back to the FFMA kernels */
+    d->tc_ok = ok && qtc_conv_tc_ok((int)lat, k->decoder_dim) && dim % 2 == 0;
+    for (int b = 0, dd = k->decoder_dim; b < 4 && d->tc_ok; b++, dd /= 2) d->tc_ok = qtc_conv_tc_ok(dd, dd / 2) && qtc_conv_tc_ok(dd / 2, dd / 2);
+    if (d->tc_ok) {
+        bool g = qtc_conv_tc_prep(c, &d->tc_pre, k->voc_pre_w, k->decoder_dim, (int)lat, 7) == 0;
+        for (int b = 0, dd = k->decoder_dim; b < 4 && g; b++, dd /= 2) {
+            const int r = k->upsample_rates[b], od = dd / 2;
+            g = qtc_tconv_tc_prep(c, &d->tc_t[b], k->block[b].tconv_w, dd, od, 2 * r, r) == 0;
+            for (int u = 0; u < 3 && g; u++)
+                g = qtc_conv_tc_prep(c, &d->tc_c1[b][u], k->block[b].res[u].conv1_w, od, od, 7) == 0 &&
+                    qtc_conv_tc_prep(c, &d->tc_c2[b][u], k->block[b].res[u].conv2_w, od, od, 1) == 0;
+        }
+        if (!g) ok = false;
+    }
 #undef UP
 #undef NEED
     if (!ok) { delete d; return NULL; }
@@ -232,7 +250,7 @@ static size_t codec_half_bytes(const qtc_codec_t *k, int T) {
     if (L * dim > need) need = L * dim;
     for (int b = 0; b < 4; b++) {
         const size_t Lo = L * k->upsample_rates[b], od = dim / 2;
-        if (2 * Lo * od > need) need = 2 * Lo * od;
+        if (3 * Lo * od > need) need = 3 * Lo * od;          /* raw rows + two pairs of bf16 planes (tensor-core path); 2 x fp32 otherwise */
         L = Lo; dim = od;
     }
     return need * 4 + 64 * 256;       /* + alignment slack for the bump allocator */
@@ -400,12 +418,47 @@ int qtc_codec_stream_push(qtc_ctx *c, const int *codes_dev, int n, float **pcm_d
         cur = up; L = Lo; side ^= 1;
     }
     int dim = k->decoder_dim;
+    static const int dil[3] = {1, 3, 9};
+    if (d->tc_ok && c->codec_tc) {
+        /* ---- vocoder on the tensor cores: time-major, two bf16 planes per activation (qtc_conv_tc.cu) ---- */
+        Arena a3 = half_arena(side);
+        uint16_t *p0h = (uint16_t *)a3.take((size_t)L * lat / 2 + 8), *p0l = (uint16_t *)a3.take((size_t)L * lat / 2 + 8);
+        uint16_t *sh = (uint16_t *)a3.take((size_t)L * dim / 2 + 8), *sl = (uint16_t *)a3.take((size_t)L * dim / 2 + 8);
+        if (a3.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder pre-conv, tc)"); return -1; }
+        CK(qtc_cf_to_planes(c, p0h, p0l, cur, lat, L, NULL, NULL));
+        CK(qtc_conv_tc(c, &d->tc_pre, p0h, p0l, L, 1, d->voc_pre_b, NULL, NULL, sh, sl, d->block[0].alpha, d->block[0].beta));
+        side ^= 1;
+        for (int b = 0; b < 4; b++) {
+            const int r = k->upsample_rates[b], od = dim / 2, Lo = L * r;
+            Arena a4 = half_arena(side);
+            float *X = a4.take((size_t)Lo * od);
+            uint16_t *s2h = (uint16_t *)a4.take((size_t)Lo * od / 2 + 8), *s2l = (uint16_t *)a4.take((size_t)Lo * od / 2 + 8);
+            uint16_t *th = (uint16_t *)a4.take((size_t)Lo * od / 2 + 8), *tl = (uint16_t *)a4.take((size_t)Lo * od / 2 + 8);
+            if (a4.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder, tc)"); return -1; }
+            const ResUnitDev *r0 = &d->block[b].ru[0];
+            CK(qtc_conv_tc(c, &d->tc_t[b], sh, sl, L, 1, d->block[b].tc.b, NULL, X, s2h, s2l, r0->a1, r0->b1));
+            for (int uu = 0; uu < 3; uu++) {
+                const ResUnitDev *ru = &d->block[b].ru[uu];
+                CK(qtc_conv_tc(c, &d->tc_c1[b][uu], s2h, s2l, Lo, dil[uu], ru->c1, NULL, NULL, th, tl, ru->a2, ru->b2));
+                /* conv1 + residual; the planes it leaves carry the NEXT consumer's SnakeBeta: next ResUnit, next block, or the final conv */
+                const float *na = uu < 2 ? d->block[b].ru[uu + 1].a1 : (b < 3 ? d->block[b + 1].alpha : d->fin_alpha);
+                const float *nb = uu < 2 ? d->block[b].ru[uu + 1].b1 : (b < 3 ? d->block[b + 1].beta : d->fin_beta);
+                CK(qtc_conv_tc(c, &d->tc_c2[b][uu], th, tl, Lo, 1, ru->c2, X, uu < 2 ? X : NULL, s2h, s2l, na, nb));
+            }
+            sh = s2h; sl = s2l; L = Lo; dim = od; side ^= 1;
+        }
+        Arena a5 = half_arena(side);
+        float *wav = a5.take((size_t)L);
+        CK(qtc_mono_from_planes(c, wav, sh, sl, d->fin_w, d->fin_b, dim, 7, L));
+        d->s_T = T1;
+        if (pcm_dev) *pcm_dev = wav + (size_t)(T0 - w0) * (L / W);
+        return n * (L / W);
+    }
     Arena a3 = half_arena(side);
     float *voc = a3.take((size_t)dim * L);
     if (a3.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder pre-conv)"); return -1; }
     CK(qtc_conv(c, voc, cur, d->voc_pre_w, d->voc_pre_b, NULL, NULL, NULL, lat, dim, 7, 1, L, 1));
     side ^= 1;
-    static const int dil[3] = {1, 3, 9};
     for (int b = 0; b < 4; b++) {
         const int r = k->upsample_rates[b], od = dim / 2, Lo = L * r;
         Arena a4 = half_arena(side);

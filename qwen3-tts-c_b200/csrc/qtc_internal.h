@@ -167,6 +167,7 @@ struct qtc_ctx {
     float *first_pcm_host;                   /* pinned landing buffer of the first chunk (time to first audio is measured on its arrival) */
     int stream_first, stream_chunk;          /* frames in the first chunk / in later chunks; stream_chunk <= 0: decode once at the end */
     qtc_pcm_callback_t stream_cb; void *stream_user;
+    int codec_tc;                            /* 1 (default): vocoder convolutions on tcgen05 where the decoder's shapes tile; 0: FFMA kernels */
     std::vector<cudaEvent_t> frame_ev, chunk_ev;
     /* CUDA graphs of the frame loop (built lazily, keyed by params) */
     cudaGraphExec_t g_front, g_talker;

@@ -151,6 +151,7 @@ def load_cuda():
     lib.qwen_tts_cuda_generate.restype = vp
     lib.qwen_tts_cuda_generate.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p, i32p, i32p, C.c_int, i32p]
     lib.qwen_tts_cuda_set_streaming.argtypes = [vp, C.c_int, C.c_int]
+    lib.qwen_tts_cuda_set_codec_tc.argtypes = [vp, C.c_int]
     lib.qwen_tts_cuda_set_stream_callback.argtypes = [vp, PcmCallback, vp]
     lib.qwen_tts_cuda_set_stream_callback.restype = None
     lib.qwen_tts_cuda_codec_stream_begin.argtypes = [vp, C.c_int]

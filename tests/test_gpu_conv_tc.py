@@ -14,6 +14,14 @@ from test_gpu_parity import snr_db
 pytestmark = pytest.mark.gpu
 
 
+def _log(tag, snr):
+    import os
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "snr_conv_tc.log"), "a") as f:
+        f.write(f"{tag} {snr:.2f} dB\n")
+
+
 def _setup(cuda):
     cuda.qwen_tts_cuda_conv1d_tc.argtypes = [B.f32p, B.f32p, B.f32p, B.f32p] + [C.c_int] * 6 + [B.f32p, B.f32p, B.f32p]
 
@@ -41,6 +49,7 @@ def test_conv_tc_vs_oracle(cuda, orc, ci, co, k, L, dil, act, res):
     assert cuda.qwen_tts_cuda_conv1d_tc(B.fptr(got), B.fptr(x), B.fptr(w), B.fptr(b), ci, co, k, L, dil, 1, B.fptr(a) if act else None,
                                         B.fptr(ib) if act else None, B.fptr(r) if res else None) == 0, cuda.qwen_tts_cuda_last_error()
     snr = snr_db(want, np.ascontiguousarray(got.T))
+    _log(f"conv {ci}->{co} k={k} dil={dil} L={L}", snr)
     assert snr >= 90.0, snr
 
 
@@ -63,4 +72,5 @@ def test_tconv_tc_vs_oracle(cuda, orc, ci, co, s, L):
     assert cuda.qwen_tts_cuda_conv1d_tc(B.fptr(got), B.fptr(x), B.fptr(w), B.fptr(b), ci, co, 2 * s, L, 1, s, B.fptr(a), B.fptr(ib), None) == 0, \
         cuda.qwen_tts_cuda_last_error()
     snr = snr_db(want, np.ascontiguousarray(got.T))
+    _log(f"tconv {ci}->{co} s={s} L={L}", snr)
     assert snr >= 90.0, snr

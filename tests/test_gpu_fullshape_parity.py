@@ -8,8 +8,24 @@ so the things that exist only at full size are held to a second opinion, not to 
   * the lock-step batch at B = 64 on 1.7B shapes, rows against the oracle's solo run of the same prompt and seed.
 
 Bars: codes equal (sampled and greedy; fast and strict arithmetic), strict logits bit-identical, fast logits within 2e-4
-relative (north_star: 1e-2), PCM SNR >= 80 dB.
+relative (north_star: 1e-2).  Waveform against the oracle's PCM for the same codes: >= 80 dB with the vocoder on the fp32 FFMA
+kernels, >= 70 dB with it on the tensor cores (the default: two bf16 pieces per value, three MMAs per product, fp32
+accumulation in TMEM; measured 74-76 dB through the ~30 convolutions of the decoder, i.e. a few 1e-4 of the signal - one or
+two steps of the 16-bit WAV the reference writes).  Measured values are appended to gpurun_out/snr_fullshape.log.
 """
+import os
+
+SNR_BAR = {1: 70.0, 0: 80.0}          # qwen_tts_cuda_set_codec_tc(1 / 0)
+
+
+def _log_snr(tag, snr):
+    try:
+        d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "snr_fullshape.log"), "a") as f:
+            f.write(f"{tag} {snr:.2f} dB\n")
+    except OSError:
+        pass
 import ctypes as C
 
 import numpy as np
@@ -59,12 +75,16 @@ def test_full_model_utterance_vs_oracle(cuda, orc, full, greedy):
     p = (B.greedy_params if greedy else B.default_params)(fixed_codec_tokens=n)
     want, want_pcm = _oracle_generate(orc, hm, p, n)
     assert len(want) == n and want_pcm.size == n * 1920
-    for strict in (0, 1):
+    for strict, tc in ((0, 1), (1, 1), (0, 0)):
         cuda.qwen_tts_cuda_set_arith(ctx, strict)
+        cuda.qwen_tts_cuda_set_codec_tc(ctx, tc)
         codes, pcm = _generate(cuda, ctx, p, n)
         assert np.array_equal(codes, want), f"{name} strict={strict}: first mismatch at {np.argwhere(codes != want)[0]}"
-        assert snr_db(want_pcm, pcm) >= 80.0
+        snr = snr_db(want_pcm, pcm)
+        _log_snr(f"utterance {name} greedy={greedy} strict={strict} codec_tc={tc}", snr)
+        assert snr >= SNR_BAR[tc], (tc, snr)
     cuda.qwen_tts_cuda_set_arith(ctx, 0)
+    cuda.qwen_tts_cuda_set_codec_tc(ctx, 1)
 
 
 def test_full_model_stage_logits_vs_oracle(cuda, orc, full):
@@ -134,12 +154,15 @@ def test_full_codec_80_frames_vs_oracle(cuda, orc):
     want = B.take_floats(orc.orc_free, orc.orc_codec_decode(s, B.iptr(codes), T, C.byref(ns)), T * 1920)
     orc.orc_destroy(s)
     assert ns.value == T * 1920
-    ptr = cuda.qwen_tts_cuda_codec_decode(ctx, B.iptr(codes), T, C.byref(ns))
-    assert ptr and ns.value == T * 1920, cuda.qwen_tts_cuda_last_error()
-    got = B.take_floats(cuda.qwen_tts_cuda_free_host, ptr, ns.value)
-    snr = snr_db(want, got)
-    assert snr >= 80.0, snr
-    assert float(np.abs(got - want).max()) <= 1e-3
+    for tc in (1, 0):
+        cuda.qwen_tts_cuda_set_codec_tc(ctx, tc)
+        ptr = cuda.qwen_tts_cuda_codec_decode(ctx, B.iptr(codes), T, C.byref(ns))
+        assert ptr and ns.value == T * 1920, cuda.qwen_tts_cuda_last_error()
+        got = B.take_floats(cuda.qwen_tts_cuda_free_host, ptr, ns.value)
+        snr = snr_db(want, got)
+        _log_snr(f"codec 80 frames codec_tc={tc} max_abs_err={float(np.abs(got - want).max()):.2e}", snr)
+        assert snr >= SNR_BAR[tc], (tc, snr)
+        assert float(np.abs(got - want).max()) <= (1e-3 if tc == 0 else 5e-3)
     cuda.qwen_tts_cuda_release(ctx)
 
 
