@@ -21,10 +21,12 @@
  * the two bf16 planes the next convolution's TMA reads.  So a ResUnit (Snake, conv7, Snake, conv1, +res) is two launches and no
  * element-wise pass; nothing is transposed between layers.
  *
- * Kernel.  One CTA = 128 samples x N output channels (N <= 256, a divisor of Cout).  Warp 0: TMA producer (A hi/lo boxes of
- * [128 x 64], B hi/lo boxes of [N x 64] per 64-channel block and tap, 2-4 stage mbarrier pipeline); warp 1: MMA issuer (12
- * tcgen05.mma.kind::f16 per stage) + TMEM owner; warps 2-5: epilogue (tcgen05.ld 32x32b.x16, one output row per thread).  Two
- * CTAs fit an SM for the small-channel layers, so one CTA's epilogue (sinf per element) overlaps the other's MMAs.
+ * Kernel.  Persistent, one CTA per SM; a tile = 128 samples x N output channels (N <= 256, a divisor of Cout).  Warp 0: TMA
+ * producer (A hi/lo boxes of [128 x 64], B hi/lo boxes of [N x 64] per 64-channel block and tap, 2-4 stage mbarrier pipeline
+ * that runs on across tiles); warp 1: MMA issuer (12 tcgen05.mma.kind::f16 per stage) + TMEM owner; warps 2-5: epilogue
+ * (tcgen05.ld 32x32b.x16, one output row per thread).  The accumulator is double-buffered in TMEM, so the epilogue of a tile
+ * (sinf per element) overlaps the MMAs of the next (one tile per CTA and one CTA per SM measured 20 % tensor-pipe activity on
+ * the 96-channel layers: profiles/r02_ncu_full_k_conv_tc_v1.csv).
  */
 #include "qtc_internal.h"
 #include "qtc_device.cuh"
@@ -32,7 +34,8 @@
 
 #define CT_BK 64                        /* K per stage: 64 bf16 = one 128-byte swizzle row */
 #define CT_A_BYTES (TC_BM * CT_BK * 2)  /* one plane of the A tile: 16 KB */
-#define CT_THREADS 192
+#define CT_EPI_WARPS 8                   /* two warps per TMEM lane quarter, each takes half of the tile's columns */
+#define CT_THREADS (64 + 32 * CT_EPI_WARPS)
 
 struct ConvTcArgs {
     int L;                  /* input rows (samples) */
@@ -56,23 +59,25 @@ __device__ __forceinline__ uint32_t ct_bf16_rn(float v) {
     return (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;
 }
 
-/* grid (time tiles, Cout / N, phases).  mapA*: activation planes [L, Cin]; mapW*: weight planes [phases*taps*Cout, Cin] */
-__global__ void __launch_bounds__(CT_THREADS) k_conv_tc(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__ CUtensorMap mapAl,
-                                                         const __grid_constant__ CUtensorMap mapWh, const __grid_constant__ CUtensorMap mapWl,
-                                                         const ConvTcArgs a) {
+/* Persistent: grid = min(tiles, SMs); CTA walks tiles (n tile fastest, then time, then phase) with the TMA / MMA warps running
+ * ahead into the next tile while the epilogue warps drain the previous accumulator (two TMEM buffers).
+ * mapA*: activation planes [L, Cin]; mapW*: weight planes [phases*taps*Cout, Cin] */
+__global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__ CUtensorMap mapAl,
+                                                            const __grid_constant__ CUtensorMap mapWh, const __grid_constant__ CUtensorMap mapWl,
+                                                            const ConvTcArgs a) {
     extern __shared__ __align__(1024) unsigned char ct_smem_raw[];
-    __shared__ __align__(8) uint64_t full[4], empty[4], acc_full;
+    __shared__ __align__(8) uint64_t full[4], empty[4], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_s;
     unsigned char *tiles = reinterpret_cast<unsigned char *>(((uintptr_t)ct_smem_raw + 1023) & ~(uintptr_t)1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int t0 = blockIdx.x * TC_BM, n0 = blockIdx.y * a.N, phase = blockIdx.z;
     const int b_bytes = a.N * CT_BK * 2, stage_bytes = 2 * CT_A_BYTES + 2 * b_bytes;
     const int iters = a.taps * a.kb_per_tap;
-    const uint32_t tmem_cols = a.N <= 32 ? 32u : a.N <= 64 ? 64u : a.N <= 128 ? 128u : 256u;
+    const uint32_t acc_cols = a.N <= 32 ? 32u : a.N <= 64 ? 64u : a.N <= 128 ? 128u : 256u, tmem_cols = 2 * acc_cols;
+    const int tiles_n = a.Cout / a.N, tiles_t = (a.L + TC_BM - 1) / TC_BM, ntiles = tiles_n * tiles_t * a.os;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < a.stages; i++) { tc_mbar_init(&full[i], 1); tc_mbar_init(&empty[i], 1); }
-        tc_mbar_init(&acc_full, 1);
+        for (int i = 0; i < 2; i++) { tc_mbar_init(&acc_full[i], 1); tc_mbar_init(&acc_empty[i], CT_EPI_WARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAh) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAl) : "memory");
@@ -90,82 +95,119 @@ __global__ void __launch_bounds__(CT_THREADS) k_conv_tc(const __grid_constant__ 
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int it = 0; it < iters; it++) {
-                const int st = it % a.stages, ph = (it / a.stages) & 1;
-                const int tap = it / a.kb_per_tap, kb = it - tap * a.kb_per_tap;
-                if (it >= a.stages) tc_mbar_wait(&empty[st], ph ^ 1);
-                unsigned char *sa = tiles + (size_t)st * stage_bytes, *sb = sa + 2 * CT_A_BYTES;
-                tc_mbar_expect_tx(&full[st], stage_bytes);
-                const int arow = t0 - (a.taps - 1 - tap) * a.dil;                  /* may be negative: rows before t = 0 are zeros */
-                const int wrow = (phase * a.taps + tap) * a.Cout + n0;
-                tc_tma_2d(sa, &mapAh, kb * CT_BK, arow, &full[st]);
-                tc_tma_2d(sa + CT_A_BYTES, &mapAl, kb * CT_BK, arow, &full[st]);
-                tc_tma_2d(sb, &mapWh, kb * CT_BK, wrow, &full[st]);
-                tc_tma_2d(sb + b_bytes, &mapWl, kb * CT_BK, wrow, &full[st]);
+            int g = 0;                                                              /* pipeline slot counter across tiles */
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const int ny = tile % tiles_n, rest = tile / tiles_n, tx = rest % tiles_t, phase = rest / tiles_t;
+                const int t0 = tx * TC_BM, n0 = ny * a.N;
+                for (int it = 0; it < iters; it++, g++) {
+                    const int st = g % a.stages, ph = (g / a.stages) & 1;
+                    const int tap = it / a.kb_per_tap, kb = it - tap * a.kb_per_tap;
+                    if (g >= a.stages) tc_mbar_wait(&empty[st], ph ^ 1);
+                    unsigned char *sa = tiles + (size_t)st * stage_bytes, *sb = sa + 2 * CT_A_BYTES;
+                    tc_mbar_expect_tx(&full[st], stage_bytes);
+                    const int arow = t0 - (a.taps - 1 - tap) * a.dil;              /* may be negative: rows before t = 0 are zeros */
+                    const int wrow = (phase * a.taps + tap) * a.Cout + n0;
+                    tc_tma_2d(sa, &mapAh, kb * CT_BK, arow, &full[st]);
+                    tc_tma_2d(sa + CT_A_BYTES, &mapAl, kb * CT_BK, arow, &full[st]);
+                    tc_tma_2d(sb, &mapWh, kb * CT_BK, wrow, &full[st]);
+                    tc_tma_2d(sb + b_bytes, &mapWl, kb * CT_BK, wrow, &full[st]);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = tc_idesc(a.N);
-            for (int it = 0; it < iters; it++) {
-                const int st = it % a.stages, ph = (it / a.stages) & 1;
-                tc_mbar_wait(&full[st], ph);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t sa = tc_smem_u32(tiles + (size_t)st * stage_bytes), sb = sa + 2 * CT_A_BYTES;
-                const uint64_t ah = tc_smem_desc(sa), al = tc_smem_desc(sa + CT_A_BYTES), bh = tc_smem_desc(sb), bl = tc_smem_desc(sb + b_bytes);
+            int g = 0, j = 0;
+            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
+                const int buf = j & 1;
+                if (j >= 2) { tc_mbar_wait(&acc_empty[buf], ((j >> 1) & 1) ^ 1); asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+                const uint32_t acc = tmem_d + (uint32_t)buf * acc_cols;
+                for (int it = 0; it < iters; it++, g++) {
+                    const int st = g % a.stages, ph = (g / a.stages) & 1;
+                    tc_mbar_wait(&full[st], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = tc_smem_u32(tiles + (size_t)st * stage_bytes), sb = sa + 2 * CT_A_BYTES;
+                    const uint64_t ah = tc_smem_desc(sa), al = tc_smem_desc(sa + CT_A_BYTES), bh = tc_smem_desc(sb), bl = tc_smem_desc(sb + b_bytes);
 #pragma unroll
-                for (int k = 0; k < CT_BK / 16; k++) {           /* UMMA K = 16 bf16 = 32 bytes inside the swizzle row */
-                    const uint64_t o = (uint64_t)(k * 2);
-                    tc_mma(tmem_d, ah + o, bh + o, idesc, (it | k) != 0);
-                    tc_mma(tmem_d, ah + o, bl + o, idesc, 1);
-                    tc_mma(tmem_d, al + o, bh + o, idesc, 1);
+                    for (int k = 0; k < CT_BK / 16; k++) {       /* UMMA K = 16 bf16 = 32 bytes inside the swizzle row */
+                        const uint64_t o = (uint64_t)(k * 2);
+                        tc_mma(acc, ah + o, bh + o, idesc, (it | k) != 0);
+                        tc_mma(acc, ah + o, bl + o, idesc, 1);
+                        tc_mma(acc, al + o, bh + o, idesc, 1);
+                    }
+                    tc_commit(&empty[st]);
                 }
-                tc_commit(&empty[st]);
+                tc_commit(&acc_full[buf]);
             }
-            tc_commit(&acc_full);
         }
     } else {
-        /* epilogue: warp w may touch TMEM lanes [32 (w % 4), +32); thread = one output row */
-        const int q = warp & 3, t = t0 + q * 32 + lane;
-        const bool live = t < a.L;
-        const size_t orow = ((size_t)t * a.os + phase) * a.Cout + n0;
-        tc_mbar_wait(&acc_full, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        for (int c0 = 0; c0 < a.N; c0 += 16) {
-            uint32_t v[16];
-            const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                         : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (!live) continue;
-            float y[16];
+        /* epilogue: warp w may touch TMEM lanes [32 (w % 4), +32); thread = one output row, half of its columns (the residual
+         * rows of the next 16 columns are requested before the current 16 are processed: the chain per chunk was one L2/HBM round
+         * trip long and the k = 1 convolutions were bound by it) */
+        const int q = warp & 3, half = (warp - 2) >> 2, ncol = a.N / 2, cbeg = half * ncol, cend = cbeg + ncol;
+        int j = 0;
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
+            const int ny = tile % tiles_n, rest = tile / tiles_n, tx = rest % tiles_t, phase = rest / tiles_t;
+            const int n0 = ny * a.N, t = tx * TC_BM + q * 32 + lane, buf = j & 1;
+            const bool live = t < a.L;
+            const size_t orow = ((size_t)t * a.os + phase) * a.Cout + n0;
+            tc_mbar_wait(&acc_full[buf], (j >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            float4 rn[4];
+            if (a.res && live) {
+                const float4 *r4 = reinterpret_cast<const float4 *>(a.res + orow + cbeg);
 #pragma unroll
-            for (int j = 0; j < 16; j++) y[j] = __uint_as_float(v[j]) + (a.bias ? a.bias[n0 + c0 + j] : 0.0f);
-            if (a.res) {
-                const float4 *r4 = reinterpret_cast<const float4 *>(a.res + orow + c0);
-#pragma unroll
-                for (int j = 0; j < 4; j++) { const float4 r = r4[j]; y[4 * j] += r.x; y[4 * j + 1] += r.y; y[4 * j + 2] += r.z; y[4 * j + 3] += r.w; }
+                for (int jj = 0; jj < 4; jj++) rn[jj] = r4[jj];
             }
-            if (a.out_raw) {
-                float4 *o4 = reinterpret_cast<float4 *>(a.out_raw + orow + c0);
+            for (int c0 = cbeg; c0 < cend; c0 += 16) {
+                uint32_t v[16];
+                float4 rc[4];
 #pragma unroll
-                for (int j = 0; j < 4; j++) o4[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
-            }
-            if (a.out_hi) {
-                uint32_t hi[8], lo[8];
+                for (int jj = 0; jj < 4; jj++) rc[jj] = rn[jj];
+                if (a.res && live && c0 + 16 < cend) {
+                    const float4 *r4 = reinterpret_cast<const float4 *>(a.res + orow + c0 + 16);
 #pragma unroll
-                for (int j = 0; j < 16; j += 2) {
-                    float z0 = y[j], z1 = y[j + 1];
-                    if (a.alpha) { z0 = ct_snake(z0, a.alpha[n0 + c0 + j], a.inv_beta[n0 + c0 + j]); z1 = ct_snake(z1, a.alpha[n0 + c0 + j + 1], a.inv_beta[n0 + c0 + j + 1]); }
-                    const uint32_t h0 = ct_bf16_rn(z0), h1 = ct_bf16_rn(z1);
-                    const uint32_t l0 = ct_bf16_rn(z0 - __uint_as_float(h0 << 16)), l1 = ct_bf16_rn(z1 - __uint_as_float(h1 << 16));
-                    hi[j >> 1] = h0 | (h1 << 16); lo[j >> 1] = l0 | (l1 << 16);
+                    for (int jj = 0; jj < 4; jj++) rn[jj] = r4[jj];
                 }
-                uint4 *ph = reinterpret_cast<uint4 *>(a.out_hi + orow + c0), *pl = reinterpret_cast<uint4 *>(a.out_lo + orow + c0);
-                ph[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]); ph[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-                pl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]); pl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * acc_cols + (uint32_t)c0;
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                             : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                               "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                             : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (c0 + 16 >= cend) {
+                    /* the accumulator is in registers: hand the buffer back before the (long) SnakeBeta part of the last chunk */
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc_smem_u32(&acc_empty[buf])) : "memory");
+                }
+                if (!live) continue;
+                float y[16];
+#pragma unroll
+                for (int jj = 0; jj < 16; jj++) y[jj] = __uint_as_float(v[jj]) + (a.bias ? a.bias[n0 + c0 + jj] : 0.0f);
+                if (a.res) {
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj++) { const float4 r = rc[jj]; y[4 * jj] += r.x; y[4 * jj + 1] += r.y; y[4 * jj + 2] += r.z; y[4 * jj + 3] += r.w; }
+                }
+                if (a.out_raw) {
+                    float4 *o4 = reinterpret_cast<float4 *>(a.out_raw + orow + c0);
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj++) o4[jj] = make_float4(y[4 * jj], y[4 * jj + 1], y[4 * jj + 2], y[4 * jj + 3]);
+                }
+                if (a.out_hi) {
+                    uint32_t hi[8], lo[8];
+#pragma unroll
+                    for (int jj = 0; jj < 16; jj += 2) {
+                        float z0 = y[jj], z1 = y[jj + 1];
+                        if (a.alpha) { z0 = ct_snake(z0, a.alpha[n0 + c0 + jj], a.inv_beta[n0 + c0 + jj]); z1 = ct_snake(z1, a.alpha[n0 + c0 + jj + 1], a.inv_beta[n0 + c0 + jj + 1]); }
+                        const uint32_t h0 = ct_bf16_rn(z0), h1 = ct_bf16_rn(z1);
+                        const uint32_t l0 = ct_bf16_rn(z0 - __uint_as_float(h0 << 16)), l1 = ct_bf16_rn(z1 - __uint_as_float(h1 << 16));
+                        hi[jj >> 1] = h0 | (h1 << 16); lo[jj >> 1] = l0 | (l1 << 16);
+                    }
+                    uint4 *ph = reinterpret_cast<uint4 *>(a.out_hi + orow + c0), *pl = reinterpret_cast<uint4 *>(a.out_lo + orow + c0);
+                    ph[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]); ph[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                    pl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]); pl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                }
             }
         }
     }
@@ -199,27 +241,33 @@ __global__ void k_cf_to_planes(uint16_t *hi, uint16_t *lo, const float *src, int
         }
     }
 }
-/* final conv (Cout = 1, k = 7, c/qwen_tts_codec.c:727-735) on time-major planes that already hold SnakeBeta(x): one warp per
- * sample would waste lanes at C = 96, so a thread takes one sample and walks its 7 x C window (rows are contiguous: coalesced
- * across the warp after the first row); clamp fused */
-__global__ void k_mono_from_planes(float *out, const uint16_t *hi, const uint16_t *lo, const float *w /*[C, K]*/, const float *bias, int C, int K, int L) {
-    extern __shared__ float wsm[];                       /* [K][C] */
-    for (int i = threadIdx.x; i < C * K; i += blockDim.x) { const int c = i / K, k = i - c * K; wsm[k * C + c] = w[i]; }
-    __syncthreads();
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= L) return;
-    /* the reference's order: channel outer, tap inner (c/qwen_tts_kernels.c:795-827); kept per channel here */
-    float acc = bias ? bias[0] : 0.0f;
-    for (int c = 0; c < C; c += 2) {
-        for (int k = 0; k < K; k++) {
-            const int tt = t - (K - 1 - k);
-            if (tt < 0) continue;
-            const uint32_t h = *reinterpret_cast<const uint32_t *>(hi + (size_t)tt * C + c), l = *reinterpret_cast<const uint32_t *>(lo + (size_t)tt * C + c);
-            const float v0 = __uint_as_float(h << 16) + __uint_as_float(l << 16), v1 = __uint_as_float(h & 0xffff0000u) + __uint_as_float(l & 0xffff0000u);
-            acc = fmaf(wsm[k * C + c], v0, acc);
-            acc = fmaf(wsm[k * C + c + 1], v1, acc);
+/* final conv (Cout = 1, k = 7, c/qwen_tts_codec.c:727-735) on time-major planes that already hold SnakeBeta(x): a CTA stages the
+ * 256 + K - 1 rows its samples need in shared memory as fp32 (coalesced 16-byte loads of both planes), then a thread walks the
+ * K x C window of one sample (row stride C + 1 floats: conflict-free); clamp fused */
+#define MONO_T 256
+__global__ void __launch_bounds__(MONO_T) k_mono_from_planes(float *out, const uint16_t *hi, const uint16_t *lo, const float *w /*[C, K]*/, const float *bias, int C, int K, int L) {
+    extern __shared__ float msm[];                       /* [K][C] weights, then [MONO_T + K - 1][C + 1] rows */
+    float *wsm = msm, *rows = msm + K * C;
+    const int t0 = blockIdx.x * MONO_T, nrows = MONO_T + K - 1, C8 = C >> 3;
+    for (int i = threadIdx.x; i < C * K; i += MONO_T) { const int c = i / K, k = i - c * K; wsm[k * C + c] = w[i]; }
+    for (int i = threadIdx.x; i < nrows * C8; i += MONO_T) {
+        const int r = i / C8, c8 = i - r * C8, t = t0 - (K - 1) + r;
+        float *d = rows + r * (C + 1) + c8 * 8;
+        if (t >= 0 && t < L) {
+            const uint4 h = *reinterpret_cast<const uint4 *>(hi + (size_t)t * C + c8 * 8), l = *reinterpret_cast<const uint4 *>(lo + (size_t)t * C + c8 * 8);
+            d[0] = bf16_lo(h.x) + bf16_lo(l.x); d[1] = bf16_hi(h.x) + bf16_hi(l.x); d[2] = bf16_lo(h.y) + bf16_lo(l.y); d[3] = bf16_hi(h.y) + bf16_hi(l.y);
+            d[4] = bf16_lo(h.z) + bf16_lo(l.z); d[5] = bf16_hi(h.z) + bf16_hi(l.z); d[6] = bf16_lo(h.w) + bf16_lo(l.w); d[7] = bf16_hi(h.w) + bf16_hi(l.w);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; e++) d[e] = 0.0f;
         }
     }
+    __syncthreads();
+    const int t = t0 + threadIdx.x;
+    if (t >= L) return;
+    float acc = bias ? bias[0] : 0.0f;
+    for (int c = 0; c < C; c++)
+        for (int k = 0; k < K; k++) acc = fmaf(wsm[k * C + c], rows[(threadIdx.x + k) * (C + 1) + c], acc);
     out[t] = fminf(1.0f, fmaxf(-1.0f, acc));
 }
 
@@ -265,11 +313,12 @@ int qtc_tconv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cin, int cout,
     return (o->hi && o->lo) ? 0 : -1;
 }
 
+/* N: the largest multiple of 32 (two epilogue halves of whole 16-column chunks) <= 256 that divides Cout */
 static int pick_n(int cout) {
-    for (int n = 256; n >= 16; n -= 16) if (cout % n == 0) return n;
+    for (int n = 256; n >= 32; n -= 32) if (cout % n == 0) return n;
     return 0;
 }
-bool qtc_conv_tc_ok(int cin, int cout) { return cin % 8 == 0 && cout % 16 == 0 && pick_n(cout) > 0; }
+bool qtc_conv_tc_ok(int cin, int cout) { return cin % 8 == 0 && cout % 32 == 0 && pick_n(cout) > 0; }
 
 static int g_ct_attr = 0;
 /* out rows = L * phases.  in_hi/in_lo: [L, Cin] planes.  Any of out_raw / out_hi may be NULL; alpha NULL: planes hold the raw output */
@@ -283,9 +332,8 @@ int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint1
     a.bias = bias; a.res = res; a.out_raw = out_raw; a.out_hi = out_hi; a.out_lo = out_lo; a.alpha = alpha; a.inv_beta = inv_beta;
     if (a.N <= 0 || w->cin % 8) { qtc_set_error("conv_tc: Cout %d / Cin %d not tileable", w->cout, w->cin); return -1; }
     const int stage_bytes = 2 * CT_A_BYTES + 2 * a.N * CT_BK * 2;
-    /* two CTAs per SM where two 2-stage pipelines fit (<= 113 KB each), else one CTA with up to 4 stages */
-    int stages = (110 * 1024) / stage_bytes;
-    if (stages < 2) { stages = (220 * 1024) / stage_bytes; }
+    /* one persistent CTA per SM: as many stages as fit (2-4) */
+    int stages = (220 * 1024) / stage_bytes;
     if (stages > 4) stages = 4;
     if (stages < 2) stages = 2;
     a.stages = stages;
@@ -295,7 +343,9 @@ int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint1
     const int wrows = w->phases * w->taps * w->cout;
     const CUtensorMap *mwh = qtc_tmap_bf16(w->hi, wrows, w->cin, a.N), *mwl = qtc_tmap_bf16(w->lo, wrows, w->cin, a.N);
     if (!mah || !mal || !mwh || !mwl) return -1;
-    const dim3 grid((L + TC_BM - 1) / TC_BM, w->cout / a.N, w->phases);
+    const long long ntiles = (long long)((L + TC_BM - 1) / TC_BM) * (w->cout / a.N) * w->phases;
+    const int sms = c->num_sms > 0 ? c->num_sms : 148;
+    const dim3 grid((unsigned)(ntiles < sms ? ntiles : sms));
     k_conv_tc<<<grid, CT_THREADS, smem, c->cstream>>>(*mah, *mal, *mwh, *mwl, a);
     c->launches++;
     const cudaError_t e = cudaGetLastError();
@@ -308,7 +358,12 @@ int qtc_cf_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, i
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 int qtc_mono_from_planes(qtc_ctx *c, float *out, const uint16_t *hi, const uint16_t *lo, const float *w, const float *bias, int C, int K, int L) {
-    k_mono_from_planes<<<(L + 255) / 256, 256, (size_t)C * K * 4, c->cstream>>>(out, hi, lo, w, bias, C, K, L);
+    if (C % 8) { qtc_set_error("mono_from_planes: C %% 8"); return -1; }
+    const size_t smem = ((size_t)C * K + (size_t)(MONO_T + K - 1) * (C + 1)) * 4;
+    static int attr = 0;
+    if (!attr) { if (cudaFuncSetAttribute(k_mono_from_planes, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return -1; attr = 1; }
+    if (smem > 200 * 1024) { qtc_set_error("mono_from_planes: %d channels do not fit the row stage", C); return -1; }
+    k_mono_from_planes<<<(L + MONO_T - 1) / MONO_T, MONO_T, smem, c->cstream>>>(out, hi, lo, w, bias, C, K, L);
     c->launches++;
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

@@ -278,7 +278,7 @@ extern "C" int qwen_tts_cuda_conv1d_tc(float *out_tm, const float *in, const flo
                                        int dilation, int stride, const float *alpha, const float *inv_beta, const float *res_tm) {
     qtc_ctx *c = kctx();
     if (!c || !out_tm || !in || !w || cin <= 0 || cout <= 0 || k <= 0 || length <= 0) return -1;
-    if (!qtc_conv_tc_ok(cin, cout)) { qtc_set_error("conv1d_tc: cin %% 8 / cout %% 16"); return -1; }
+    if (!qtc_conv_tc_ok(cin, cout)) { qtc_set_error("conv1d_tc: cin %% 8 / cout %% 32"); return -1; }
     const int s = stride > 1 ? stride : 1;
     const size_t Lout = (size_t)length * s;
     ConvTcW W;

@@ -28,7 +28,7 @@ def _setup(cuda):
 
 @pytest.mark.parametrize("ci,co,k,L,dil,act,res", [
     (96, 96, 7, 1000, 9, True, False), (96, 96, 1, 777, 1, True, True), (192, 192, 7, 515, 3, True, False), (384, 384, 7, 300, 1, False, False),
-    (768, 768, 7, 260, 9, True, False), (1024, 1536, 7, 130, 1, False, False), (64, 16, 3, 5, 1, False, False), (200, 48, 7, 129, 2, True, True)])
+    (768, 768, 7, 260, 9, True, False), (1024, 1536, 7, 130, 1, False, False), (64, 32, 3, 5, 1, False, False), (200, 64, 7, 129, 2, True, True)])
 def test_conv_tc_vs_oracle(cuda, orc, ci, co, k, L, dil, act, res):
     _setup(cuda)
     rng = np.random.default_rng(ci + co + k)
@@ -53,7 +53,7 @@ def test_conv_tc_vs_oracle(cuda, orc, ci, co, k, L, dil, act, res):
     assert snr >= 90.0, snr
 
 
-@pytest.mark.parametrize("ci,co,s,L", [(1536, 768, 8, 70), (768, 384, 5, 200), (384, 192, 4, 333), (192, 96, 3, 1000), (96, 48, 8, 77)])
+@pytest.mark.parametrize("ci,co,s,L", [(1536, 768, 8, 70), (768, 384, 5, 200), (384, 192, 4, 333), (192, 96, 3, 1000), (96, 64, 8, 77)])
 def test_tconv_tc_vs_oracle(cuda, orc, ci, co, s, L):
     _setup(cuda)
     rng = np.random.default_rng(ci + s)
