@@ -11,17 +11,19 @@
  * output rows interleave (row m*s + p): same kernel, blockIdx.z = phase.
  *
  * Precision.  The reference computes in fp32.  Every activation and weight is carried as TWO bf16 pieces (hi = rn(x),
- * lo = rn(x - hi): 16 mantissa bits) and each product as three MMAs (hi.hi + hi.lo + lo.hi) accumulated in fp32 in TMEM: the
- * dropped terms are ~2^-17 relative, ~100 dB below the signal per layer (the waveform stays >= 80 dB from the reference's
- * through the whole decoder: tests/test_gpu_conv_tc.py, test_gpu_fullshape_parity.py).  That is 3 of 2250 TFLOP/s-class MMAs per
- * product instead of 1 of 74 TFLOP/s-class FFMAs.
+ * lo = rn(x - hi): 16 mantissa bits) and each product as three MMAs (hi.hi + hi.lo + lo.hi) accumulated in fp32 in TMEM - the
+ * hi.hi products in one accumulator, the two cross terms in a second one that the epilogue adds (the accumulate step of the
+ * tensor core drops low bits of the running sum, an error that grows with the number of MMAs into the same accumulator:
+ * 93.7 dB at K = 7168 with one accumulator, 102.3 dB with two).  Measured 102-110 dB per layer and 82-85 dB through the whole
+ * decoder against the reference's fp32 path (tests/test_gpu_conv_tc.py, test_gpu_fullshape_parity.py; profiles/r02_snr_*).
+ * That is 3 of 2250 TFLOP/s-class MMAs per product instead of 1 of 74 TFLOP/s-class FFMAs.
  *
  * Fusion.  SnakeBeta is applied where a tensor is PRODUCED, not where it is consumed: the epilogue adds bias and residual,
  * stores the raw fp32 row (only where a later residual needs it), applies the NEXT layer's SnakeBeta and stores the result as
  * the two bf16 planes the next convolution's TMA reads.  So a ResUnit (Snake, conv7, Snake, conv1, +res) is two launches and no
  * element-wise pass; nothing is transposed between layers.
  *
- * Kernel.  Persistent, one CTA per SM; a tile = 128 samples x N output channels (N <= 256, a divisor of Cout).  Warp 0: TMA
+ * Kernel.  Persistent, one CTA per SM; a tile = 128 samples x N output channels (N <= 128, a divisor of Cout).  Warp 0: TMA
  * producer (A hi/lo boxes of [128 x 64], B hi/lo boxes of [N x 64] per 64-channel block and tap, 2-4 stage mbarrier pipeline
  * that runs on across tiles); warp 1: MMA issuer (12 tcgen05.mma.kind::f16 per stage) + TMEM owner; warps 2-5: epilogue
  * (tcgen05.ld 32x32b.x16, one output row per thread).  The accumulator is double-buffered in TMEM, so the epilogue of a tile
@@ -72,7 +74,11 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b_bytes = a.N * CT_BK * 2, stage_bytes = 2 * CT_A_BYTES + 2 * b_bytes;
     const int iters = a.taps * a.kb_per_tap;
-    const uint32_t acc_cols = a.N <= 32 ? 32u : a.N <= 64 ? 64u : a.N <= 128 ? 128u : 256u, tmem_cols = 2 * acc_cols;
+    /* TMEM: two buffers (tile j, tile j + 1), each with TWO accumulators: hi.hi products go to the first, the two cross terms
+     * (2^-8 of the magnitude) to the second; the epilogue adds them in fp32.  The tensor core's accumulate step loses low bits
+     * of the running sum (toward zero: the error grows ~linearly with the number of MMAs, 93.7 dB at K = 7168 with one
+     * accumulator), so keeping two of every three MMAs out of the large sum is worth ~9 dB on the long contractions. */
+    const uint32_t acc_cols = a.N <= 32 ? 32u : a.N <= 64 ? 64u : 128u, tmem_cols = 4 * acc_cols;
     const int tiles_n = a.Cout / a.N, tiles_t = (a.L + TC_BM - 1) / TC_BM, ntiles = tiles_n * tiles_t * a.os;
 
     if (threadIdx.x == 0) {
@@ -121,7 +127,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
             for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
                 const int buf = j & 1;
                 if (j >= 2) { tc_mbar_wait(&acc_empty[buf], ((j >> 1) & 1) ^ 1); asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-                const uint32_t acc = tmem_d + (uint32_t)buf * acc_cols;
+                const uint32_t acc = tmem_d + (uint32_t)buf * 2 * acc_cols, acc2 = acc + acc_cols;
                 for (int it = 0; it < iters; it++, g++) {
                     const int st = g % a.stages, ph = (g / a.stages) & 1;
                     tc_mbar_wait(&full[st], ph);
@@ -132,8 +138,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
                     for (int k = 0; k < CT_BK / 16; k++) {       /* UMMA K = 16 bf16 = 32 bytes inside the swizzle row */
                         const uint64_t o = (uint64_t)(k * 2);
                         tc_mma(acc, ah + o, bh + o, idesc, (it | k) != 0);
-                        tc_mma(acc, ah + o, bl + o, idesc, 1);
-                        tc_mma(acc, al + o, bh + o, idesc, 1);
+                        tc_mma(acc2, ah + o, bl + o, idesc, (it | k) != 0);
+                        tc_mma(acc2, al + o, bh + o, idesc, 1);
                     }
                     tc_commit(&empty[st]);
                 }
@@ -160,7 +166,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
                 for (int jj = 0; jj < 4; jj++) rn[jj] = r4[jj];
             }
             for (int c0 = cbeg; c0 < cend; c0 += 16) {
-                uint32_t v[16];
+                uint32_t v[16], v2[16];
                 float4 rc[4];
 #pragma unroll
                 for (int jj = 0; jj < 4; jj++) rc[jj] = rn[jj];
@@ -169,11 +175,15 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
 #pragma unroll
                     for (int jj = 0; jj < 4; jj++) rn[jj] = r4[jj];
                 }
-                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * acc_cols + (uint32_t)c0;
+                const uint32_t taddr = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * 2 * acc_cols + (uint32_t)c0;
                 asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                              : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
                                "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                              : "r"(taddr));
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                             : "=r"(v2[0]), "=r"(v2[1]), "=r"(v2[2]), "=r"(v2[3]), "=r"(v2[4]), "=r"(v2[5]), "=r"(v2[6]), "=r"(v2[7]),
+                               "=r"(v2[8]), "=r"(v2[9]), "=r"(v2[10]), "=r"(v2[11]), "=r"(v2[12]), "=r"(v2[13]), "=r"(v2[14]), "=r"(v2[15])
+                             : "r"(taddr + acc_cols));
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (c0 + 16 >= cend) {
                     /* the accumulator is in registers: hand the buffer back before the (long) SnakeBeta part of the last chunk */
@@ -184,7 +194,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
                 if (!live) continue;
                 float y[16];
 #pragma unroll
-                for (int jj = 0; jj < 16; jj++) y[jj] = __uint_as_float(v[jj]) + (a.bias ? a.bias[n0 + c0 + jj] : 0.0f);
+                for (int jj = 0; jj < 16; jj++) y[jj] = (__uint_as_float(v[jj]) + __uint_as_float(v2[jj])) + (a.bias ? a.bias[n0 + c0 + jj] : 0.0f);
                 if (a.res) {
 #pragma unroll
                     for (int jj = 0; jj < 4; jj++) { const float4 r = rc[jj]; y[4 * jj] += r.x; y[4 * jj + 1] += r.y; y[4 * jj + 2] += r.z; y[4 * jj + 3] += r.w; }
@@ -313,9 +323,10 @@ int qtc_tconv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cin, int cout,
     return (o->hi && o->lo) ? 0 : -1;
 }
 
-/* N: the largest multiple of 32 (two epilogue halves of whole 16-column chunks) <= 256 that divides Cout */
+/* N: the largest multiple of 32 (two epilogue halves of whole 16-column chunks) <= 128 (four accumulators of <= 128 TMEM
+ * columns: two tiles in flight x {hi.hi, cross terms}) that divides Cout */
 static int pick_n(int cout) {
-    for (int n = 256; n >= 32; n -= 32) if (cout % n == 0) return n;
+    for (int n = 128; n >= 32; n -= 32) if (cout % n == 0) return n;
     return 0;
 }
 bool qtc_conv_tc_ok(int cin, int cout) { return cin % 8 == 0 && cout % 32 == 0 && pick_n(cout) > 0; }

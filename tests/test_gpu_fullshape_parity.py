@@ -8,14 +8,14 @@ so the things that exist only at full size are held to a second opinion, not to 
   * the lock-step batch at B = 64 on 1.7B shapes, rows against the oracle's solo run of the same prompt and seed.
 
 Bars: codes equal (sampled and greedy; fast and strict arithmetic), strict logits bit-identical, fast logits within 2e-4
-relative (north_star: 1e-2).  Waveform against the oracle's PCM for the same codes: >= 80 dB with the vocoder on the fp32 FFMA
-kernels, >= 70 dB with it on the tensor cores (the default: two bf16 pieces per value, three MMAs per product, fp32
-accumulation in TMEM; measured 74-76 dB through the ~30 convolutions of the decoder, i.e. a few 1e-4 of the signal - one or
-two steps of the 16-bit WAV the reference writes).  Measured values are appended to gpurun_out/snr_fullshape.log.
+relative (north_star: 1e-2).  Waveform against the oracle's PCM for the same codes: >= 80 dB, both with the vocoder on the
+tensor cores (the default: two bf16 pieces per value, three MMAs per product, the cross terms in their own TMEM accumulator;
+measured 82-85 dB through the ~30 convolutions of the decoder) and on the fp32 FFMA kernels (98-101 dB).  Measured values are
+appended to gpurun_out/snr_fullshape.log (copies under profiles/).
 """
 import os
 
-SNR_BAR = {1: 70.0, 0: 80.0}          # qwen_tts_cuda_set_codec_tc(1 / 0)
+SNR_BAR = {1: 80.0, 0: 80.0}          # qwen_tts_cuda_set_codec_tc(1 / 0)
 
 
 def _log_snr(tag, snr):
@@ -162,7 +162,7 @@ def test_full_codec_80_frames_vs_oracle(cuda, orc):
         snr = snr_db(want, got)
         _log_snr(f"codec 80 frames codec_tc={tc} max_abs_err={float(np.abs(got - want).max()):.2e}", snr)
         assert snr >= SNR_BAR[tc], (tc, snr)
-        assert float(np.abs(got - want).max()) <= (1e-3 if tc == 0 else 5e-3)
+        assert float(np.abs(got - want).max()) <= 1e-3
     cuda.qwen_tts_cuda_release(ctx)
 
 
