@@ -36,6 +36,10 @@ struct CodecDev {
     /* the same vocoder weights as bf16 hi/lo planes for the tensor-core path (qtc_conv_tc.cu); tc_ok: every layer is tileable */
     ConvTcW tc_pre, tc_t[4], tc_c1[4][3], tc_c2[4][3];
     bool tc_ok;
+    /* ... and the transformer / upsample projections (k = 1 "convolutions" over time-major rows); tcx_ok: they tile too */
+    struct { ConvTcW q, k, v, o, gate, up, down; } tcl[QTC_MAX_CODEC_LAYERS];
+    ConvTcW tc_in, tc_out, tc_up[2], tc_pw1[2], tc_pw2[2];
+    bool tcx_ok;
     /* workspace, grown on demand */
     float *ws; size_t ws_bytes;
     int *codes_dev; int codes_cap;
@@ -144,6 +148,26 @@ CodecDev *qtc_codec_upload(qtc_ctx *c, const qtc_codec_t *k) {
         }
         if (!g) ok = false;
     }
+    d->tcx_ok = d->tc_ok && ok && qtc_conv_tc_ok((int)lat, (int)Hc) && qtc_conv_tc_ok((int)Hc, (int)qd) && qtc_conv_tc_ok((int)Hc, (int)kvd) &&
+                qtc_conv_tc_ok((int)qd, (int)Hc) && qtc_conv_tc_ok((int)Hc, (int)I) && qtc_conv_tc_ok((int)I, (int)Hc) && qtc_conv_tc_ok((int)Hc, (int)lat) &&
+                lat % 32 == 0;
+    if (d->tcx_ok) {
+        bool g = qtc_conv_tc_prep(c, &d->tc_in, k->in_proj_w, (int)Hc, (int)lat, 1) == 0 && qtc_conv_tc_prep(c, &d->tc_out, k->out_proj_w, (int)lat, (int)Hc, 1) == 0;
+        for (int l = 0; l < k->layers && g; l++) {
+            const qtc_codec_layer_t *s = &k->layer[l];
+            g = qtc_conv_tc_prep(c, &d->tcl[l].q, s->wq, (int)qd, (int)Hc, 1) == 0 && qtc_conv_tc_prep(c, &d->tcl[l].k, s->wk, (int)kvd, (int)Hc, 1) == 0 &&
+                qtc_conv_tc_prep(c, &d->tcl[l].v, s->wv, (int)kvd, (int)Hc, 1) == 0 && qtc_conv_tc_prep(c, &d->tcl[l].o, s->wo, (int)Hc, (int)qd, 1) == 0 &&
+                qtc_conv_tc_prep(c, &d->tcl[l].gate, s->gate, (int)I, (int)Hc, 1) == 0 && qtc_conv_tc_prep(c, &d->tcl[l].up, s->up, (int)I, (int)Hc, 1) == 0 &&
+                qtc_conv_tc_prep(c, &d->tcl[l].down, s->down, (int)Hc, (int)I, 1) == 0;
+        }
+        for (int s = 0; s < 2 && g; s++) {
+            const int f = k->upsampling_ratios[s];
+            g = qtc_tconv_tc_prep(c, &d->tc_up[s], k->up_tconv_w[s], (int)lat, (int)lat, f, f) == 0 &&
+                qtc_conv_tc_prep(c, &d->tc_pw1[s], k->convnext[s].pw1_w, 4 * (int)lat, (int)lat, 1) == 0 &&
+                qtc_conv_tc_prep(c, &d->tc_pw2[s], k->convnext[s].pw2_w, (int)lat, 4 * (int)lat, 1) == 0;
+        }
+        if (!g) ok = false;
+    }
 #undef UP
 #undef NEED
     if (!ok) { delete d; return NULL; }
@@ -244,8 +268,8 @@ static size_t codec_half_bytes(const qtc_codec_t *k, int T) {
     const size_t lat = k->latent, Hc = k->hidden, I = k->intermediate, vq = k->codebook_dim / 2;
     const size_t hd = Hc / k->heads, qd = k->heads * hd, kvd = k->kv_heads * hd;
     size_t L = T;
-    size_t need = (size_t)T * (2 * vq + lat / 2 + 2 * lat + 2 * Hc + 2 * qd + 2 * kvd + 2 * I);      /* transformer stage */
-    for (int s = 0; s < 2; s++) { L *= k->upsampling_ratios[s]; const size_t b = L * lat * 7; if (b > need) need = b; }
+    size_t need = (size_t)T * (2 * vq + lat / 2 + 3 * lat + 4 * Hc + 2 * qd + 2 * kvd + 3 * I);      /* transformer stage */
+    for (int s = 0; s < 2; s++) { L *= k->upsampling_ratios[s]; const size_t b = L * lat * 9; if (b > need) need = b; }
     size_t dim = k->decoder_dim;
     if (L * dim > need) need = L * dim;
     for (int b = 0; b < 4; b++) {
@@ -372,8 +396,69 @@ int qtc_codec_stream_push(qtc_ctx *c, const int *codes_dev, int n, float **pcm_d
     CK(qtc_sgemm(c, h0, aco, d->aco_proj, m, half, vq, NULL, NULL, h0, 0, 1, m));
     CK(qtc_conv(c, pre, h0, d->pre_w, d->pre_b, NULL, NULL, NULL, k->codebook_dim, lat, 3, 1, m, 1));
     CK(transpose(c, seq, pre, lat, m));                                                         /* [m, lat] */
-    CK(qtc_sgemm(c, x, seq + (size_t)skip * lat, d->in_w, n, Hc, lat, d->in_b, NULL, NULL, 0, 0, Hc));
     const float scale = 1.0f / sqrtf((float)hd);
+    const bool tcx = d->tcx_ok && c->codec_tc;
+    const int w0 = T0 > d->s_ctx ? T0 - d->s_ctx : 0, W = T1 - w0;
+    int L = W, side = 1;                 /* the transformer stage uses half 0; `side` = half the next stage writes */
+    auto half_arena = [&](int sd) { Arena a = {(char *)d->ws + (size_t)sd * half_bytes, 0, half_bytes}; return a; };
+    uint16_t *uph = NULL, *upl = NULL;   /* tensor-core path: planes [4W, lat] the upsample stages leave for the vocoder pre-conv */
+    float *cur = NULL;
+    if (tcx) {
+        /* ---- transformer + upsample on the tensor cores: every projection is a k = 1 convolution over time-major rows; RMSNorm,
+         * attention and SwiGLU emit the bf16 planes the next GEMM reads; LayerScale and residual ride in the GEMM's epilogue ---- */
+        const size_t pmax = (size_t)n * (I > Hc ? I : Hc) / 2 + 8;
+        uint16_t *Ph = (uint16_t *)ar.take(pmax), *Pl = (uint16_t *)ar.take(pmax);
+        if (ar.off > half_bytes) { qtc_set_error("codec: workspace underestimated (transformer, tc)"); return -1; }
+        CK(qtc_rows_to_planes(c, Ph, Pl, seq + (size_t)skip * lat, (size_t)n * lat));
+        CK(qtc_conv_tc(c, &d->tc_in, Ph, Pl, n, 1, d->in_b, NULL, x, NULL, NULL, NULL, NULL));
+        for (int l = 0; l < k->layers; l++) {
+            const CodecLayerDev *w = &d->layer[l];
+            float *kk = d->s_k[l] + (size_t)T0 * kvd, *v = d->s_v[l] + (size_t)T0 * kvd;
+            k_row_norm<<<n, 256, 0, st>>>(NULL, x, w->in_norm, NULL, Hc, k->rms_eps, 0, Ph, Pl);
+            c->launches++;
+            CK(qtc_conv_tc(c, &d->tcl[l].q, Ph, Pl, n, 1, NULL, NULL, q, NULL, NULL, NULL, NULL));
+            CK(qtc_conv_tc(c, &d->tcl[l].k, Ph, Pl, n, 1, NULL, NULL, kk, NULL, NULL, NULL, NULL));
+            CK(qtc_conv_tc(c, &d->tcl[l].v, Ph, Pl, n, 1, NULL, NULL, v, NULL, NULL, NULL, NULL));
+            k_rope_rows<<<n, 256, 0, st>>>(q, kk, d->rope_cs + (size_t)T0 * hd, d->rope_sn + (size_t)T0 * hd, n, nh, nkv, hd);
+            c->launches++;
+            k_window_attn<<<(n * nh + 3) / 4, 128, 0, st>>>(NULL, q, d->s_k[l], d->s_v[l], n, nh, nkv, hd, k->sliding_window, scale, T0, Ph, Pl);
+            c->launches++;
+            CK(qtc_conv_tc(c, &d->tcl[l].o, Ph, Pl, n, 1, NULL, x, x, NULL, NULL, NULL, NULL, w->attn_scale, 0));
+            k_row_norm<<<n, 256, 0, st>>>(NULL, x, w->post_norm, NULL, Hc, k->rms_eps, 0, Ph, Pl);
+            c->launches++;
+            CK(qtc_conv_tc(c, &d->tcl[l].gate, Ph, Pl, n, 1, NULL, NULL, g, NULL, NULL, NULL, NULL));
+            CK(qtc_conv_tc(c, &d->tcl[l].up, Ph, Pl, n, 1, NULL, NULL, u, NULL, NULL, NULL, NULL));
+            k_swiglu_mul<<<(unsigned)(((size_t)n * I + 255) / 256), 256, 0, st>>>(g, u, (size_t)n * I, Ph, Pl);
+            c->launches++;
+            CK(qtc_conv_tc(c, &d->tcl[l].down, Ph, Pl, n, 1, NULL, x, x, NULL, NULL, NULL, NULL, w->mlp_scale, 0));
+        }
+        if (d->final_norm) { k_row_norm<<<n, 256, 0, st>>>(NULL, x, d->final_norm, NULL, Hc, k->rms_eps, 0, Ph, Pl); c->launches++; }
+        else CK(qtc_rows_to_planes(c, Ph, Pl, x, (size_t)n * Hc));
+        CK(qtc_conv_tc(c, &d->tc_out, Ph, Pl, n, 1, d->out_b, NULL, d->s_tf + (size_t)T0 * lat, NULL, NULL, NULL, NULL));   /* time-major rows [T0, T1) */
+        /* upsample: transposed conv (k = s: one tap per phase) + ConvNeXt, all time-major */
+        Arena a1 = half_arena(side);
+        uint16_t *ih = (uint16_t *)a1.take((size_t)W * lat / 2 + 8), *il = (uint16_t *)a1.take((size_t)W * lat / 2 + 8);
+        CK(qtc_rows_to_planes(c, ih, il, d->s_tf + (size_t)w0 * lat, (size_t)W * lat));
+        for (int s = 0; s < 2; s++) {
+            const int f = k->upsampling_ratios[s], Lo = L * f;
+            const ConvNextDev *b = &d->cnx[s];
+            Arena a2 = s == 0 ? a1 : half_arena(side);
+            float *U = a2.take((size_t)Lo * lat), *cv = a2.take((size_t)Lo * lat);
+            uint16_t *p1h = (uint16_t *)a2.take((size_t)Lo * lat / 2 + 8), *p1l = (uint16_t *)a2.take((size_t)Lo * lat / 2 + 8);
+            uint16_t *p2h = (uint16_t *)a2.take((size_t)Lo * 2 * lat + 8), *p2l = (uint16_t *)a2.take((size_t)Lo * 2 * lat + 8);
+            uint16_t *oh = (uint16_t *)a2.take((size_t)Lo * lat / 2 + 8), *ol = (uint16_t *)a2.take((size_t)Lo * lat / 2 + 8);
+            if (a2.off > half_bytes) { qtc_set_error("codec: workspace underestimated (upsample, tc)"); return -1; }
+            CK(qtc_conv_tc(c, &d->tc_up[s], ih, il, L, 1, d->up_tconv[s].b, NULL, U, NULL, NULL, NULL, NULL));
+            CK(qtc_dwconv_tm(c, cv, U, b->dw_w, b->dw_b, lat, 7, Lo));
+            k_row_norm<<<Lo, 256, 0, st>>>(NULL, cv, b->norm_w, b->norm_b, lat, 1e-6f, 1, p1h, p1l);
+            c->launches++;
+            CK(qtc_conv_tc(c, &d->tc_pw1[s], p1h, p1l, Lo, 1, b->pw1_b, NULL, NULL, p2h, p2l, NULL, NULL, NULL, 1));
+            CK(qtc_conv_tc(c, &d->tc_pw2[s], p2h, p2l, Lo, 1, b->pw2_b, U, NULL, oh, ol, NULL, NULL, b->gamma, 0));
+            ih = oh; il = ol; L = Lo; side ^= 1;
+        }
+        uph = ih; upl = il;
+    } else {
+    CK(qtc_sgemm(c, x, seq + (size_t)skip * lat, d->in_w, n, Hc, lat, d->in_b, NULL, NULL, 0, 0, Hc));
     for (int l = 0; l < k->layers; l++) {
         const CodecLayerDev *w = &d->layer[l];
         float *kk = d->s_k[l] + (size_t)T0 * kvd, *v = d->s_v[l] + (size_t)T0 * kvd;          /* rows of this chunk in the persistent caches */
@@ -397,11 +482,8 @@ int qtc_codec_stream_push(qtc_ctx *c, const int *codes_dev, int n, float **pcm_d
     CK(qtc_sgemm(c, d->s_tf + (size_t)T0 * lat, x, d->out_w, n, lat, Hc, d->out_b, NULL, NULL, 0, 0, lat));   /* time-major rows [T0, T1) */
 
     /* ---- conv stack on the window [w0, T1): 2 x (transposed conv + ConvNeXt), vocoder ---- */
-    const int w0 = T0 > d->s_ctx ? T0 - d->s_ctx : 0, W = T1 - w0;
-    float *cur = pre;                                                                           /* half 0, free again: [lat, W] */
+    cur = pre;                                                                                  /* half 0, free again: [lat, W] */
     CK(transpose(c, cur, d->s_tf + (size_t)w0 * lat, W, lat));
-    int L = W, side = 1;                 /* the transformer stage used half 0; `side` = half the next stage writes */
-    auto half_arena = [&](int sd) { Arena a = {(char *)d->ws + (size_t)sd * half_bytes, 0, half_bytes}; return a; };
     for (int s = 0; s < 2; s++) {
         const int f = k->upsampling_ratios[s], Lo = L * f;
         Arena a2 = half_arena(side);
@@ -417,15 +499,17 @@ int qtc_codec_stream_push(qtc_ctx *c, const int *codes_dev, int n, float **pcm_d
         CK(qtc_sgemm(c, up, pw, b->pw2_w, Lo, lat, 4 * lat, b->pw2_b, b->gamma, up, 0, 1, Lo)); /* h[c,t] += gamma*(..) */
         cur = up; L = Lo; side ^= 1;
     }
+    }
     int dim = k->decoder_dim;
     static const int dil[3] = {1, 3, 9};
     if (d->tc_ok && c->codec_tc) {
         /* ---- vocoder on the tensor cores: time-major, two bf16 planes per activation (qtc_conv_tc.cu) ---- */
         Arena a3 = half_arena(side);
-        uint16_t *p0h = (uint16_t *)a3.take((size_t)L * lat / 2 + 8), *p0l = (uint16_t *)a3.take((size_t)L * lat / 2 + 8);
+        uint16_t *p0h = uph, *p0l = upl;
+        if (!uph) { p0h = (uint16_t *)a3.take((size_t)L * lat / 2 + 8); p0l = (uint16_t *)a3.take((size_t)L * lat / 2 + 8); }
         uint16_t *sh = (uint16_t *)a3.take((size_t)L * dim / 2 + 8), *sl = (uint16_t *)a3.take((size_t)L * dim / 2 + 8);
         if (a3.off > half_bytes) { qtc_set_error("codec: workspace underestimated (vocoder pre-conv, tc)"); return -1; }
-        CK(qtc_cf_to_planes(c, p0h, p0l, cur, lat, L, NULL, NULL));
+        if (!uph) CK(qtc_cf_to_planes(c, p0h, p0l, cur, lat, L, NULL, NULL));
         CK(qtc_conv_tc(c, &d->tc_pre, p0h, p0l, L, 1, d->voc_pre_b, NULL, NULL, sh, sl, d->block[0].alpha, d->block[0].beta));
         side ^= 1;
         for (int b = 0; b < 4; b++) {

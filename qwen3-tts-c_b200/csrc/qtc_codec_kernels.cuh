@@ -267,17 +267,25 @@ __global__ void k_transpose(float *dst, const float *src, int rows, int cols) {
     }
 }
 
-/* row-wise norms over [rows, n]; one CTA per row.  mode 0: RMSNorm(w), 1: LayerNorm(w,b) (c/qwen_tts_kernels.c:45-58) */
-__global__ void __launch_bounds__(256) k_row_norm(float *out, const float *x, const float *w, const float *b, int n, float eps, int mode) {
+__device__ __forceinline__ void put_planes(uint16_t *ph, uint16_t *pl, size_t i, float v) {
+    const uint32_t u = __float_as_uint(v), h = (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;
+    const uint32_t r = __float_as_uint(v - __uint_as_float(h << 16));
+    ph[i] = (uint16_t)h; pl[i] = (uint16_t)((r + 0x7fffu + ((r >> 16) & 1u)) >> 16);
+}
+/* row-wise norms over [rows, n]; one CTA per row.  mode 0: RMSNorm(w), 1: LayerNorm(w,b) (c/qwen_tts_kernels.c:45-58).
+ * ph / pl != NULL: the result goes out as bf16 planes (input of a tensor-core GEMM) instead of fp32 */
+__global__ void __launch_bounds__(256) k_row_norm(float *out, const float *x, const float *w, const float *b, int n, float eps, int mode,
+                                                  uint16_t *ph = NULL, uint16_t *pl = NULL) {
     __shared__ float red[32];
     const float *xi = x + (size_t)blockIdx.x * n;
     float *yo = out + (size_t)blockIdx.x * n;
+    const size_t pb = (size_t)blockIdx.x * n;
     if (mode == 0) {
         float ss = 0.0f;
         for (int i = threadIdx.x; i < n; i += blockDim.x) ss = fmaf(xi[i], xi[i], ss);
         ss = block_sum(ss, red);
         const float inv = 1.0f / sqrtf(ss / (float)n + eps);
-        for (int i = threadIdx.x; i < n; i += blockDim.x) yo[i] = xi[i] * inv * w[i];
+        for (int i = threadIdx.x; i < n; i += blockDim.x) { const float y = xi[i] * inv * w[i]; if (ph) put_planes(ph, pl, pb + i, y); else yo[i] = y; }
     } else {
         float s = 0.0f;
         for (int i = threadIdx.x; i < n; i += blockDim.x) s += xi[i];
@@ -290,7 +298,7 @@ __global__ void __launch_bounds__(256) k_row_norm(float *out, const float *x, co
             float y = (xi[i] - mean) * inv;
             if (w) y *= w[i];
             if (b) y += b[i];
-            yo[i] = y;
+            if (ph) put_planes(ph, pl, pb + i, y); else yo[i] = y;
         }
     }
 }
@@ -328,7 +336,7 @@ __global__ void k_rope_rows(float *q, float *k, const float *cs, const float *sn
  * q / out hold T queries whose absolute positions are q0 .. q0+T-1; k / v are indexed by absolute position (the streaming
  * decoder keeps them across chunks), so a chunk attends to keys of earlier chunks exactly as a one-shot decode does. */
 __global__ void __launch_bounds__(128) k_window_attn(float *out, const float *q, const float *k, const float *v, int T, int nh, int nkv,
-                                                      int hd, int W, float scale, int q0) {
+                                                      int hd, int W, float scale, int q0, uint16_t *ph = NULL, uint16_t *pl = NULL) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * 4 + warp;
     if (item >= T * nh) return;
@@ -371,7 +379,10 @@ __global__ void __launch_bounds__(128) k_window_attn(float *out, const float *q,
     }
     float *oh = out + ((size_t)ql * nh + h) * hd;
 #pragma unroll
-    for (int u = 0; u < 8; u++) { const int e = lane + 32 * u; if (e < hd) oh[e] = o[u]; }
+    for (int u = 0; u < 8; u++) {
+        const int e = lane + 32 * u;
+        if (e < hd) { if (ph) put_planes(ph, pl, ((size_t)ql * nh + h) * hd + e, o[u]); else oh[e] = o[u]; }
+    }
 }
 
 /* dst[i] = src[i]: PCM of a streamed chunk into the utterance's device buffer */
@@ -381,7 +392,7 @@ __global__ void k_copy_pcm(float *dst, const float *src, size_t n) {
 }
 
 /* g[i] = silu(g[i]) * u[i] (c/qwen_tts_codec.c:411-414) */
-__global__ void k_swiglu_mul(float *g, const float *u, size_t n) {
+__global__ void k_swiglu_mul(float *g, const float *u, size_t n, uint16_t *ph = NULL, uint16_t *pl = NULL) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { const float x = g[i]; g[i] = (x / (1.0f + expf(-x))) * u[i]; }
+    if (i < n) { const float x = g[i], y = (x / (1.0f + expf(-x))) * u[i]; if (ph) put_planes(ph, pl, i, y); else g[i] = y; }
 }

@@ -50,6 +50,8 @@ struct ConvTcArgs {
     float *out_raw;         /* [Lout, Cout] fp32 or NULL */
     uint16_t *out_hi, *out_lo;          /* [Lout, Cout] bf16 planes of act(out), or NULL */
     const float *alpha, *inv_beta;      /* SnakeBeta of the NEXT layer, per output channel; NULL: planes hold out itself */
+    const float *scale;                 /* [Cout] or NULL: LayerScale / gamma, applied to (acc + bias) before the residual */
+    int gelu;                           /* tanh-GELU after the bias (c/qwen_tts_kernels.c:244-249) */
 };
 
 __device__ __forceinline__ float ct_snake(float x, float a, float ib) {
@@ -195,6 +197,14 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
                 float y[16];
 #pragma unroll
                 for (int jj = 0; jj < 16; jj++) y[jj] = (__uint_as_float(v[jj]) + __uint_as_float(v2[jj])) + (a.bias ? a.bias[n0 + c0 + jj] : 0.0f);
+                if (a.gelu) {
+#pragma unroll
+                    for (int jj = 0; jj < 16; jj++) y[jj] = 0.5f * y[jj] * (1.0f + tanhf(0.7978845608028654f * (y[jj] + 0.044715f * y[jj] * y[jj] * y[jj])));
+                }
+                if (a.scale) {
+#pragma unroll
+                    for (int jj = 0; jj < 16; jj++) y[jj] *= a.scale[n0 + c0 + jj];
+                }
                 if (a.res) {
 #pragma unroll
                     for (int jj = 0; jj < 4; jj++) { const float4 r = rc[jj]; y[4 * jj] += r.x; y[4 * jj + 1] += r.y; y[4 * jj + 2] += r.z; y[4 * jj + 3] += r.w; }
@@ -251,6 +261,30 @@ __global__ void k_cf_to_planes(uint16_t *hi, uint16_t *lo, const float *src, int
         }
     }
 }
+/* fp32 rows -> bf16 planes (hi, lo), element-wise; n % 4 == 0 */
+__global__ void k_rows_to_planes(uint16_t *hi, uint16_t *lo, const float *src, size_t n4) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const float4 v = reinterpret_cast<const float4 *>(src)[i];
+    const uint32_t h0 = ct_bf16_rn(v.x), h1 = ct_bf16_rn(v.y), h2 = ct_bf16_rn(v.z), h3 = ct_bf16_rn(v.w);
+    const uint32_t l0 = ct_bf16_rn(v.x - __uint_as_float(h0 << 16)), l1 = ct_bf16_rn(v.y - __uint_as_float(h1 << 16));
+    const uint32_t l2 = ct_bf16_rn(v.z - __uint_as_float(h2 << 16)), l3 = ct_bf16_rn(v.w - __uint_as_float(h3 << 16));
+    reinterpret_cast<uint2 *>(hi)[i] = make_uint2(h0 | (h1 << 16), h2 | (h3 << 16));
+    reinterpret_cast<uint2 *>(lo)[i] = make_uint2(l0 | (l1 << 16), l2 | (l3 << 16));
+}
+/* depthwise causal conv, time-major [L, C] (ConvNeXt dwconv k = 7, c/qwen_tts_codec.c:477): out[t, c] = b[c] + sum_k w[c, k] in[t - (K-1-k), c] */
+__global__ void k_dwconv_tm(float *out, const float *in, const float *w, const float *bias, int C, int K, int L) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)L * C) return;
+    const int t = (int)(i / C), c = (int)(i - (size_t)t * C);
+    float acc = bias ? bias[c] : 0.0f;
+    for (int k = 0; k < K; k++) {
+        const int tt = t - (K - 1 - k);
+        if (tt >= 0) acc = fmaf(w[c * K + k], in[(size_t)tt * C + c], acc);
+    }
+    out[i] = acc;
+}
+
 /* final conv (Cout = 1, k = 7, c/qwen_tts_codec.c:727-735) on time-major planes that already hold SnakeBeta(x): a CTA stages the
  * 256 + K - 1 rows its samples need in shared memory as fp32 (coalesced 16-byte loads of both planes), then a thread walks the
  * K x C window of one sample (row stride C + 1 floats: conflict-free); clamp fused */
@@ -334,10 +368,11 @@ bool qtc_conv_tc_ok(int cin, int cout) { return cin % 8 == 0 && cout % 32 == 0 &
 static int g_ct_attr = 0;
 /* out rows = L * phases.  in_hi/in_lo: [L, Cin] planes.  Any of out_raw / out_hi may be NULL; alpha NULL: planes hold the raw output */
 int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint16_t *in_lo, int L, int dil, const float *bias, const float *res,
-                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta) {
+                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta, const float *scale, int gelu) {
     if (L <= 0) return 0;
     ConvTcArgs a;
     memset(&a, 0, sizeof(a));
+    a.scale = scale; a.gelu = gelu;
     a.L = L; a.Cin = w->cin; a.Cout = w->cout; a.N = pick_n(w->cout); a.taps = w->taps; a.dil = dil; a.os = w->phases;
     a.kb_per_tap = (w->cin + CT_BK - 1) / CT_BK;
     a.bias = bias; a.res = res; a.out_raw = out_raw; a.out_hi = out_hi; a.out_lo = out_lo; a.alpha = alpha; a.inv_beta = inv_beta;
@@ -365,6 +400,18 @@ int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint1
 }
 int qtc_cf_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, int C, int L, const float *alpha, const float *inv_beta) {
     k_cf_to_planes<<<dim3((L + 31) / 32, (C + 31) / 32), dim3(32, 8), 0, c->cstream>>>(hi, lo, src, C, L, alpha, inv_beta);
+    c->launches++;
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+int qtc_rows_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, size_t n) {
+    if (n % 4) { qtc_set_error("rows_to_planes: n %% 4"); return -1; }
+    k_rows_to_planes<<<(unsigned)((n / 4 + 255) / 256), 256, 0, c->cstream>>>(hi, lo, src, n / 4);
+    c->launches++;
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+int qtc_dwconv_tm(qtc_ctx *c, float *out, const float *in, const float *w, const float *bias, int C, int K, int L) {
+    const size_t n = (size_t)L * C;
+    k_dwconv_tm<<<(unsigned)((n + 255) / 256), 256, 0, c->cstream>>>(out, in, w, bias, C, K, L);
     c->launches++;
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

@@ -216,7 +216,9 @@ bool qtc_conv_tc_ok(int cin, int cout);
 int qtc_conv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cout, int cin, int K);
 int qtc_tconv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cin, int cout, int k, int s);
 int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint16_t *in_lo, int L, int dil, const float *bias, const float *res,
-                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta);
+                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta, const float *scale = NULL, int gelu = 0);
+int qtc_rows_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, size_t n);
+int qtc_dwconv_tm(qtc_ctx *c, float *out, const float *in, const float *w, const float *bias, int C, int K, int L);
 int qtc_cf_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, int C, int L, const float *alpha, const float *inv_beta);
 int qtc_mono_from_planes(qtc_ctx *c, float *out, const uint16_t *hi, const uint16_t *lo, const float *w, const float *bias, int C, int K, int L);
 
