@@ -217,7 +217,7 @@ static int push_chunk(qtc_ctx *c, StreamOut *so, int upto) {
     if ((size_t)so->nchunks >= c->chunk_ev.size()) { cudaEvent_t e; QTC_CUDA(cudaEventCreate(&e)); c->chunk_ev.push_back(e); }
     QTC_CUDA(cudaEventRecord(c->ev3, c->stream));                                   /* last codec kernel so far */
     QTC_CUDA(cudaStreamWaitEvent(c->stream2, c->ev3, 0));
-    float *dst = so->host + (size_t)so->decoded * so->spf;
+    float *dst = c->first_pcm_host + (size_t)so->decoded * so->spf;          /* pinned landing buffer of the utterance */
     QTC_CUDA(cudaMemcpyAsync(dst, wav, (size_t)ns * 4, cudaMemcpyDeviceToHost, c->stream2));
     QTC_CUDA(cudaEventRecord(c->chunk_ev[so->nchunks], c->stream2));
     so->chunk_end[so->nchunks] = upto;
@@ -232,6 +232,7 @@ static void deliver_chunks(qtc_ctx *c, StreamOut *so, bool wait) {
         if (wait) cudaEventSynchronize(e);
         else if (cudaEventQuery(e) != cudaSuccess) break;
         const int t0 = so->delivered ? so->chunk_end[so->delivered - 1] : 0, t1 = so->chunk_end[so->delivered];
+        memcpy(so->host + (size_t)t0 * so->spf, c->first_pcm_host + (size_t)t0 * so->spf, (size_t)(t1 - t0) * so->spf * 4);
         if (c->stream_cb) c->stream_cb(so->host + (size_t)t0 * so->spf, (t1 - t0) * so->spf, t0, c->stream_user);
         so->delivered++;
     }
@@ -456,11 +457,13 @@ extern "C" float *qwen_tts_cuda_generate(qtc_ctx_t *c, const char *text, const c
         const size_t bytes = (size_t)limit * so.spf * 4;
         so.host = (float *)malloc(bytes);
         if (!so.host) { qtc_set_error("generate: PCM buffer of %zu bytes", bytes); return NULL; }
-        if (cudaHostRegister(so.host, bytes, cudaHostRegisterDefault) != cudaSuccess) {
-            cudaGetLastError(); free(so.host); qtc_set_error("generate: cudaHostRegister of the PCM buffer failed"); return NULL;
+        if (bytes > c->pcm_cap) {                /* pinned landing buffer, grown on demand (page-locking the caller's buffer per call
+                                                    cost up to 60 ms in cudaHostUnregister) */
+            cudaFreeHost(c->first_pcm_host); c->first_pcm_host = NULL; c->pcm_cap = 0;
+            if (cudaMallocHost(&c->first_pcm_host, bytes + (1 << 20)) != cudaSuccess) { cudaGetLastError(); free(so.host); qtc_set_error("generate: pinned PCM buffer"); return NULL; }
+            c->pcm_cap = bytes + (1 << 20);
         }
         n = qtc_generate_frames_resident(c, plen, ntr, codes.data(), limit, &so);
-        cudaHostUnregister(so.host);
         t_codec = now_ms();
         if (n <= 0) { free(so.host); if (n < 0) return NULL; }
         else { pcm = so.host; *out_samples = so.samples; }

@@ -164,7 +164,7 @@ struct qtc_ctx {
     long long launches;
     /* streamed decode inside generate: PCM of the whole utterance on the device, chunk schedule, per-frame / per-chunk events */
     float *pcm_dev; size_t pcm_cap;          /* [frames * samples_per_frame] */
-    float *first_pcm_host;                   /* pinned landing buffer of the first chunk (time to first audio is measured on its arrival) */
+    float *first_pcm_host;                   /* pinned landing buffer of the streamed PCM (pcm_cap bytes); chunks are handed on from it */
     int stream_first, stream_chunk;          /* frames in the first chunk / in later chunks; stream_chunk <= 0: decode once at the end */
     qtc_pcm_callback_t stream_cb; void *stream_user;
     int codec_tc;                            /* 1 (default): vocoder convolutions on tcgen05 where the decoder's shapes tile; 0: FFMA kernels */
@@ -198,7 +198,7 @@ int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code
 int qtc_sample_talker(qtc_ctx *c);
 int qtc_frame_front(qtc_ctx *c);    /* sample + sub-talker + next embedding, device resident */
 struct StreamOut {                 /* streamed decode of one utterance */
-    float *host; int spf, samples;     /* page-locked PCM buffer, samples per frame, samples written */
+    float *host; int spf, samples;     /* the caller's PCM buffer (malloc), samples per frame, samples written */
     int decoded = 0, nchunks = 0, delivered = 0;
     std::vector<int> chunk_end;        /* frame index each chunk ends at */
 };
