@@ -176,13 +176,18 @@ def run_reference(args, rank, world):
         dt = time.time() - t0
         rtf = args.steps * REF_FRAMES * FRAME_S / dt
         cores = os.cpu_count()
+        # the same path through the oracle port, whose GEMVs are OpenMP loops over rows (the reference's are single-threaded by
+        # construction): both CPU figures travel in this line, so the GPU / CPU ratio is never quoted against the handicapped one alone
+        port_rtf, port_dt = cpu_baseline_sample(hm, spec, main, frames=1)
         line = {"impl": "reference", "metric": METRIC, "value": rtf, "unit": "audio_s/s", "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32 (bf16 weights)", "data": "synthetic",
                 "config": {"workload": "1.7B-CustomVoice shapes, batch 1, default sampling, random-init weights",
                            "sample": f"{REF_FRAMES} frames of the frame loop + codec decode of them per step, after an untimed prefill"},
                 "cpu_baseline": {"value": rtf, "unit": "audio_s/s", "cores": cores, "kind": "reference",
-                                 "sample": f"{args.steps} x {REF_FRAMES} frames; GEMVs single-threaded (no BLAS on the image), codec convs OpenMP x{cores}"},
+                                 "sample": f"{args.steps} x {REF_FRAMES} frames; GEMVs single-threaded (no BLAS on the image), codec convs OpenMP x{cores}",
+                                 "port_all_cores": {"value": port_rtf, "unit": "audio_s/s", "cores": cores, "kind": "port",
+                                                    "sample": f"1 frame + its codec decode after an untimed prefill, {port_dt:.1f} s; oracle port, OpenMP over output rows"}},
                 "ms_per_frame": dt / (args.steps * REF_FRAMES) * 1e3,
                 "e2e": {"value": rtf, "unit": "audio_s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
@@ -223,38 +228,45 @@ def cpu_baseline_sample(hm, spec, main, frames=1):
     return frames * FRAME_S / dt, dt
 
 
-def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
-    """configs 4-5: `--batch` utterances per GPU decoded in lock-step (tcgen05 GEMM path), fixed frame budget, codes only
-    (the codec decode of each utterance is the batch-1 decoder and is timed by the default line)"""
-    nb, frames, G = args.batch, args.frames, spec["groups"]
+def measure_batch(args, cuda, ctx, spec, rank, world, local, dist, torch, n_utt, frames, steps, warmup, with_pcm=True):
+    """configs 4-5: this rank's n_utt utterances decoded as lock-step batches of <= 64 (tcgen05 GEMM path), fixed frame budget,
+    codes AND PCM (every utterance's codes go through the codec decoder; PCM lands in a host buffer).  Returns the numbers
+    of the slowest rank (device time: prompt build .. last codec kernel of every batch)."""
+    G = spec["groups"]
     cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
     cuda.qwen_tts_cuda_set_batch_pieces.argtypes = [C.c_void_p, C.c_int]
     assert cuda.qwen_tts_cuda_set_batch_pieces(ctx, args.pieces) == 0
     p = B.default_params(fixed_codec_tokens=frames, sample_seed=1000 * rank + 42)
     cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
     rng = np.random.default_rng(rank)
-    prompts = []
-    for b in range(nb):                       # fixture prompt with a random-length run of text ids in the middle
-        extra = [int(x) for x in rng.integers(1000, 5000, size=int(rng.integers(0, 24)))]
-        prompts.append(TOKENS[:4] + extra + TOKENS[4:])
-    toks = np.array(sum(prompts, []), dtype=np.int32)
-    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
-    spk = np.full(nb, mg.SPEAKERS["aiden"], dtype=np.int32)
-    lang = np.full(nb, mg.LANGUAGES["english"], dtype=np.int32)
-    codes = np.zeros((nb, frames, G), dtype=np.int32)
-    nfr = np.zeros(nb, dtype=np.int32)
+    batches = []
+    for lo, hi in shard.micro_batches(0, n_utt, 64):
+        nb = hi - lo
+        prompts = []
+        for b in range(nb):                   # fixture prompt with a random-length run of text ids in the middle
+            extra = [int(x) for x in rng.integers(1000, 5000, size=int(rng.integers(0, 24)))]
+            prompts.append(TOKENS[:4] + extra + TOKENS[4:])
+        batches.append(dict(nb=nb, toks=np.array(sum(prompts, []), dtype=np.int32),
+                            offs=np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32),
+                            spk=np.full(nb, mg.SPEAKERS["aiden"], dtype=np.int32), lang=np.full(nb, mg.LANGUAGES["english"], dtype=np.int32),
+                            codes=np.zeros((nb, frames, G), dtype=np.int32), nfr=np.zeros(nb, dtype=np.int32),
+                            pcm=np.zeros((nb, frames * 1920), dtype=np.float32) if with_pcm else None))
     perf = B.Perf()
 
     def one():
         t0 = time.perf_counter()
-        rc = cuda.qwen_tts_cuda_generate_batch(ctx, nb, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), None, frames)
-        wall = time.perf_counter() - t0
-        if rc != 0 or int(nfr.min()) != frames:
-            raise RuntimeError("generate_batch failed: " + cuda.qwen_tts_cuda_last_error().decode())
-        cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
-        return wall, perf.device_ms / 1e3, perf.talker_ms / 1e3
+        dev = loop = 0.0
+        for bt in batches:
+            rc = cuda.qwen_tts_cuda_generate_batch(ctx, bt["nb"], B.iptr(bt["toks"]), B.iptr(bt["offs"]), B.iptr(bt["spk"]), B.iptr(bt["lang"]), B.iptr(bt["codes"]),
+                                                   B.iptr(bt["nfr"]), B.fptr(bt["pcm"]) if with_pcm else None, frames)
+            if rc != 0 or int(bt["nfr"].min()) != frames:
+                raise RuntimeError("generate_batch failed: " + cuda.qwen_tts_cuda_last_error().decode())
+            cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+            dev += perf.device_ms / 1e3
+            loop += perf.talker_ms / 1e3
+        return time.perf_counter() - t0, dev, loop
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         one()
     cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
     l0 = perf.kernel_launches
@@ -265,7 +277,7 @@ def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     devs, loops = [], []
-    for _ in range(args.steps):
+    for _ in range(steps):
         w, dv, lp = one()
         devs.append(dv); loops.append(lp)
     if dist is not None:
@@ -274,28 +286,41 @@ def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
     wall_total, dev_total = time.perf_counter() - t0, sum(devs)
     sampler.stop_flag = True
     cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
-    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=f"cuda:{local}")
+    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=None)
+    total_utt = sum(shard.gather_counts(dist, n_utt, device=None))
+    audio_s = steps * total_utt * frames * FRAME_S
+    hbm, which = peaks()
+    nb0 = batches[0]["nb"]
+    ms_frame = sum(loops) / (steps * frames * len(batches)) * 1e3
+    pos_mid = 10 + frames // 2
+    kv_one = cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos_mid) - cuda.qwen_tts_cuda_talker_step_bytes(ctx, 0)   # fp32 KV read of ONE utterance
+    step_bytes = cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos_mid) + (nb0 - 1) * kv_one + cuda.qwen_tts_cuda_subtalker_frame_bytes(ctx)
+    ach = step_bytes / (ms_frame * 1e-3) / 1e9
+    pcm_bytes = sum(int(bt["pcm"].nbytes) for bt in batches) if with_pcm else 0
+    return {"value": audio_s / dev_total, "e2e": audio_s / wall_total, "unit": "audio_s/s", "utterances": total_utt, "utterances_per_gpu": n_utt,
+            "batches_per_gpu": len(batches), "frames": frames, "includes_pcm": bool(with_pcm), "ms_per_batch_frame": ms_frame,
+            "ms_per_step": wall_total / steps * 1e3, "gpu_launches": int(perf.kernel_launches - l0),
+            "h2d_bytes_per_step": sum(int(bt["toks"].nbytes + bt["offs"].nbytes) for bt in batches),
+            "d2h_bytes_per_step": sum(int(bt["codes"].nbytes) for bt in batches) + pcm_bytes,
+            "roofline": {"bound": "hbm", "kernel": "one batched frame = talker step + 16 sub-talker steps: weights streamed once per step for the whole batch + every utterance's fp32 KV at the mid position",
+                         "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": which, "bytes_per_frame": step_bytes},
+            "clocks": sampler.summary()}
+
+
+def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
+    """`--batch N`: BASELINE config 4 as its own line (N utterances per GPU in lock-step, PCM included)"""
+    r = measure_batch(args, cuda, ctx, spec, rank, world, local, dist, torch, args.batch, args.frames, args.steps, args.warmup, with_pcm=not args.codes_only)
     if rank == 0:
-        audio_s = world * args.steps * nb * frames * FRAME_S
-        hbm, which = peaks()
-        ms_frame = sum(loops) / (args.steps * frames) * 1e3
-        pos_mid = 10 + frames // 2
-        kv_one = cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos_mid) - cuda.qwen_tts_cuda_talker_step_bytes(ctx, 0)   # fp32 KV read of ONE utterance
-        step_bytes = cuda.qwen_tts_cuda_talker_step_bytes(ctx, pos_mid) + (nb - 1) * kv_one + cuda.qwen_tts_cuda_subtalker_frame_bytes(ctx)
-        ach = step_bytes / (ms_frame * 1e-3) / 1e9
         print(json.dumps({
-            "metric": "audio-sec generated/sec, 1.7B-CustomVoice lock-step batch", "value": audio_s / dev_total, "unit": "audio_s/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall_total / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "metric": "audio-sec generated/sec, 1.7B-CustomVoice lock-step batch", "value": r["value"], "unit": "audio_s/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16 x bf16 -> f32 (tcgen05), activations as %d bf16 piece(s)" % args.pieces, "data": "synthetic",
-            "config": {"workload": f"{args.model} CustomVoice shapes, {nb} utterances per GPU in lock-step, {frames} frames each, default sampling, "
-                                   "ragged prompts, codes only (no codec decode)", "batch": nb, "pieces": args.pieces},
-            "ms_per_frame": ms_frame, "e2e": {"value": audio_s / wall_total, "unit": "audio_s/s", "h2d_bytes_per_step": int(toks.nbytes + offs.nbytes),
-                                              "d2h_bytes_per_step": int(codes.nbytes)},
-            "gpu_launches": int(perf.kernel_launches - l0),
-            "roofline": {"bound": "hbm", "kernel": "one frame = talker step + 16 sub-talker steps: weights streamed once per step for the whole batch + every utterance's fp32 KV at the mid position",
-                         "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None, "peak_source": which,
-                         "bytes_per_frame": step_bytes},
-            "clocks": sampler.summary()}))
+            "config": {"workload": f"{args.model} CustomVoice shapes, {args.batch} utterances per GPU in lock-step batches of <= 64, {args.frames} frames each, "
+                                   "default sampling, ragged prompts, " + ("codes only" if args.codes_only else "codes + codec decode to PCM"),
+                       "batch": args.batch, "pieces": args.pieces},
+            "ms_per_frame": r["ms_per_batch_frame"], "e2e": {"value": r["e2e"], "unit": "audio_s/s", "h2d_bytes_per_step": r["h2d_bytes_per_step"],
+                                                              "d2h_bytes_per_step": r["d2h_bytes_per_step"]},
+            "gpu_launches": r["gpu_launches"], "roofline": r["roofline"], "clocks": r["clocks"]}))
 
 
 def run_codec(args, cuda, ctx, spec, hm, rank, world, local, dist, torch):
@@ -334,7 +359,7 @@ def run_codec(args, cuda, ctx, spec, hm, rank, world, local, dist, torch):
     wall_total, dev_total = time.perf_counter() - t0, sum(devs)
     sampler.stop_flag = True
     cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
-    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=f"cuda:{local}")
+    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=None)
     if rank == 0:
         audio_s = world * args.steps * T * FRAME_S
         flops = 5.12e9 * T                        # 18.44 TFLOP at T = 3600, 93 % of it in the vocoder convolutions
@@ -386,6 +411,8 @@ def main():
     ap.add_argument("--strict", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
     ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")
+    ap.add_argument("--codes-only", action="store_true", help="with --batch: skip the codec decode (round-1 behaviour)")
+    ap.add_argument("--no-batched", action="store_true", help="default line: skip the config 4 / 5 sub-measurement")
     ap.add_argument("--greedy", action="store_true", help="greedy decoding (BASELINE config 1: --model 0.6b --frames 74 --greedy)")
     ap.add_argument("--codec-frames", type=int, default=0, help="> 0: codec decoder only on this many frames (BASELINE config 3: 3600)")
     ap.add_argument("--stream-first", type=int, default=8, help="frames in the first PCM chunk of the streamed-latency utterances")
@@ -407,13 +434,17 @@ def main():
         import torch.distributed as dist_
         dist = dist_
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+        # utterances are independent and the models fit one GPU: nothing of the data path crosses GPUs (north_star: "no NCCL").
+        # The process group carries the barrier and the max-over-ranks of the device time only: gloo on the host.
+        dist.init_process_group("gloo")
     torch.cuda.set_device(local)
     cuda = B.load_cuda()                       # raises if the extension was not built: there is no fallback
     if cuda.qwen_tts_cuda_init(local) != 0:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
     spec, main_t, cod, hm = build_model(args.model)
-    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), max(1, args.batch))     # max_batch sizes the paged KV pool
+    default_line = args.batch == 0 and args.codec_frames == 0
+    want_batched = default_line and not args.no_batched and args.model == "1.7b" and not args.greedy and args.frames == FRAMES
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 64 if (want_batched or args.batch > 0) else 1)     # max_batch sizes the paged KV pool
     if not ctx:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
     cuda.qwen_tts_cuda_set_mode(ctx, args.mode)
@@ -485,10 +516,23 @@ def main():
     launches = perf.kernel_launches - launches0
 
     dev_total, wall_total = sum(devs), t_all
-    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=f"cuda:{local}")   # slowest rank
+    dev_total, wall_total = shard.reduce_times(dist, [dev_total, wall_total], device=None)   # slowest rank
     audio_s = world * args.steps * frames * FRAME_S
     value, e2e = audio_s / dev_total, audio_s / wall_total
 
+    # BASELINE configs 4 / 5 inside the driver-run line: 1 GPU -> config 4 (64 utterances x 250 frames in lock-step on this GPU);
+    # N > 1 -> config 5 (256 utterances split contiguously over the N GPUs, harness/shard.py).  Codes + PCM, device-timed like `value`.
+    batched = None
+    if want_batched:
+        per_gpu = 64 if world == 1 else (shard.partition(256, world)[rank][1] - shard.partition(256, world)[rank][0])
+        r = measure_batch(args, cuda, ctx, spec, rank, world, local, dist, torch, per_gpu, 250, 1, 1, with_pcm=True)
+        if rank == 0:
+            batched = {"config": ("BASELINE config 4: 64 utterances per GPU, 20 s each (250 frames), lock-step, codes + PCM" if world == 1 else
+                                  f"BASELINE config 5: 256 utterances over {world} GPUs ({per_gpu} per GPU in lock-step batches of <= 64), 250 frames each, codes + PCM"),
+                       **{k: r[k] for k in ("value", "e2e", "unit", "utterances", "utterances_per_gpu", "batches_per_gpu", "frames", "includes_pcm",
+                                            "ms_per_batch_frame", "gpu_launches", "roofline")}}
+        p = (B.greedy_params if args.greedy else B.default_params)(fixed_codec_tokens=frames, sample_seed=42 + rank)
+        cuda.qwen_tts_cuda_set_params(ctx, C.byref(p))
     line = None
     if rank == 0:
         hbm, which = peaks()
@@ -519,10 +563,12 @@ def main():
                 "e2e": {"value": e2e, "unit": "audio_s/s", "h2d_bytes_per_step": len(CSV), "d2h_bytes_per_step": pcm_bytes + frames * G * 4},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "talker decode step (all kernels of one step)", "achieved": ach, "peak": hbm, "unit": "GB/s",
-                             "frac": ach / hbm, "traffic": ncu_traffic(args.mode), "peak_source": which, "bytes_per_step": step_bytes, "ms_per_talker_step": step_ms,
+                             "frac": ach / hbm, "traffic": ncu_traffic(args.mode) if args.model == "1.7b" else None, "peak_source": which, "bytes_per_step": step_bytes, "ms_per_talker_step": step_ms,
                              "subtalker": {"ms_per_frame": sub_ms, "streamed_bytes": sub_bytes, "achieved": sub_bytes / (sub_ms * 1e-3) / 1e9,
                                            "frac": sub_bytes / (sub_ms * 1e-3) / 1e9 / hbm}},
                 "clocks": sampler.summary()}
+        if batched is not None:
+            line["batched"] = batched
         if not args.no_cpu and world == 1:
             rtf_cpu, dt = cpu_baseline_sample(hm, spec, main_t, frames=1)
             line["cpu_baseline"] = {"value": rtf_cpu, "unit": "audio_s/s", "cores": os.cpu_count(), "kind": "port",
