@@ -480,7 +480,7 @@ def main():
         cuda.qwen_tts_cuda_free_host(ptr)
         cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
         if record:
-            lat.append((perf.ttff_ms, perf.ttfa_ms, perf.frame_ms_p50, perf.frame_ms_p99, wall))
+            lat.append((perf.ttff_ms, perf.ttfa_ms, perf.frame_ms_p50, perf.frame_ms_p99, wall, perf.prefill_ms))
         return wall, perf.device_ms / 1e3, perf.talker_ms / 1e3, ns.value
 
     def barrier():
@@ -556,7 +556,7 @@ def main():
                 # see "note"
                 "latency": {"ttff_ms": float(np.median([x[0] for x in lat[1:]])), "ttfa_ms": float(np.median([x[1] for x in lat[1:]])),
                             "frame_ms_p50": float(np.median([x[2] for x in lat[1:]])), "frame_ms_p99": float(np.median([x[3] for x in lat[1:]])),
-                            "first_chunk_frames": args.stream_first, "chunk_frames": args.stream_chunk,
+                            "prefill_ms": float(np.median([x[5] for x in lat[1:]])), "first_chunk_frames": args.stream_first, "chunk_frames": args.stream_chunk,
                             "e2e_streamed": frames * FRAME_S / float(np.median([x[4] for x in lat[1:]])),
                             "note": "qwen_tts_cuda_set_streaming on: PCM chunks decoded between frames and copied to the host while the loop goes on; "
                                     "value / e2e of this line are measured with it off (decode at the end, the reference's order)"},

@@ -112,6 +112,7 @@ extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     if (c->g_front) cudaGraphExecDestroy(c->g_front);
     if (c->g_talker) cudaGraphExecDestroy(c->g_talker);
     qtc_batch_release(c);
+    qtc_prefill_release(c);
     qtc_codec_release(c->codec);
     for (void *p : c->allocs) { qtc_gemm_tc_forget(p); cudaFree(p); }
     LmBuffers *bs[2] = {&c->tk, &c->st};
@@ -133,7 +134,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     qtc_ctx *c = new qtc_ctx();
     c->host = *desc;
     c->H = desc->talker.hidden; c->G = desc->num_code_groups; c->max_batch = max_batch > 0 ? max_batch : 1;
-    c->bb = NULL; c->batch_pieces = 3; c->dev_mallocs = 0;
+    c->bb = NULL; c->pf = NULL; c->batch_pieces = 3; c->dev_mallocs = 0;
     c->mode = 1; c->arith = 0; c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
     c->codec = NULL; c->codes = NULL; c->trailing = NULL; c->prefill = NULL; c->codes_cap = c->trailing_cap = c->prefill_cap = 0;
     memset(&c->tk, 0, sizeof(c->tk)); memset(&c->st, 0, sizeof(c->st)); memset(&c->perf, 0, sizeof(c->perf));

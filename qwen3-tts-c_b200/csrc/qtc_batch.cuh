@@ -649,6 +649,35 @@ extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *
     QTC_CUDA(cudaMemcpyAsync(bb->seeds, seeds.data(), (size_t)B * 4, cudaMemcpyHostToDevice, c->stream));
     QTC_CUDA(cudaMemsetAsync(bb->hist, 0, (size_t)B * c->talker.vocab * 4, c->stream));
     QTC_CUDA(cudaStreamSynchronize(c->stream));      /* pos0 / seeds are stack vectors */
+    if (pf_ok(c) && prefill_gemm_on()) {
+        /* prefill of the whole batch as ONE ragged pass (qtc_prefill.cuh): R = sum of the prompt lengths rows through every
+         * projection as one tensor-core GEMM; a row knows its sequence (KV pool slot b) and position.  Every utterance then
+         * stands at its own position plen[b] - the lock-step frames that follow never needed the prompts aligned. */
+        int R = 0;
+        for (int b = 0; b < B; b++) R += plen[b];
+        if (pf_reserve(c, R)) return -1;
+        std::vector<int> hs(R), hp(R), last(B);
+        for (int b = 0, r = 0; b < B; b++) { for (int t = 0; t < plen[b]; t++, r++) { hs[r] = b; hp[r] = t; } last[b] = r - 1; }
+        QTC_CUDA(cudaMemcpyAsync(c->pf->slot, hs.data(), (size_t)R * 4, cudaMemcpyHostToDevice, c->stream));
+        QTC_CUDA(cudaMemcpyAsync(c->pf->pos, hp.data(), (size_t)R * 4, cudaMemcpyHostToDevice, c->stream));
+        QTC_CUDA(cudaMemcpyAsync(bb->frame_codes, last.data(), (size_t)B * 4, cudaMemcpyHostToDevice, c->stream));     /* scratch: last row of every utterance */
+        QTC_CUDA(cudaStreamSynchronize(c->stream));
+        k_pf_gather_rows<<<dim3((H + 255) / 256, R), 256, 0, c->stream>>>(c->pf->x, bb->prefill, bb->prefill_cap, c->pf->slot, c->pf->pos, H);
+        BLAUNCH(c);
+        if (pf_run(c, R, maxlen - 1)) return -1;
+        k_pf_take_last<<<dim3((H + 255) / 256, B), 256, 0, c->stream>>>(bb->tk.x, c->pf->x, bb->frame_codes, H);
+        BLAUNCH(c);
+        for (int b = 0; b < B; b++) pos0[b] = plen[b] - 1;
+        QTC_CUDA(cudaMemcpyAsync(bb->pos, pos0.data(), (size_t)B * 4, cudaMemcpyHostToDevice, c->stream));
+        QTC_CUDA(cudaStreamSynchronize(c->stream));
+        /* final norm -> hidden of every utterance (ctx->tk_x), codec head -> logits of frame 0 */
+        qtc_launch_pdl(c->stream, k_b_norm, dim3(B), dim3(256), 0, bb->xb, bb->hidden, bb->tk.x, c->talker.final_norm, H, c->talker.eps, bb->pieces, bb->tk.logits, c->talker.vocab, bb->pos);
+        BLAUNCH(c);
+        if (qtc_gemm_tc(c, bb->tk.logits, c->talker.vocab, bb->xb, c->codec_head, B, c->talker.vocab, H, bb->pieces)) return -1;
+        qtc_launch_pdl(c->stream, k_b_pos_add, dim3((B + 63) / 64), dim3(64), 0, bb->pos, B, 1);
+        BLAUNCH(c);
+        QTC_CUDA(cudaMemsetAsync(bb->frame_codes, 0, (size_t)B * G * 4, c->stream));
+    } else
     /* lock-step prefill: per token the reference's batched prefill does a decode step's arithmetic */
     for (int s = 0; s < maxlen; s++) {
         qtc_launch_pdl(c->stream, k_b_fill_prefill, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, bb->tk.x, bb->prefill, bb->prefill_cap, bb->pos, H);

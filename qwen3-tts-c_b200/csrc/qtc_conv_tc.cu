@@ -50,6 +50,8 @@ struct ConvTcArgs {
     float *out_raw;         /* [Lout, Cout] fp32 or NULL */
     uint16_t *out_hi, *out_lo;          /* [Lout, Cout] bf16 planes of act(out), or NULL */
     const float *alpha, *inv_beta;      /* SnakeBeta of the NEXT layer, per output channel; NULL: planes hold out itself */
+    int aplanes;                        /* 2: activations as hi + lo planes; 3: hi + mid + lo, the EXACT split of an fp32 value (prefill: products exact) */
+    int wplanes;                        /* 2: weights as hi + lo planes (fp32 originals); 1: the weights ARE bf16 (talker / sub-talker): no lo plane, 2 MMAs */
     const float *scale;                 /* [Cout] or NULL: LayerScale / gamma, applied to (acc + bias) before the residual */
     int gelu;                           /* tanh-GELU after the bias (c/qwen_tts_kernels.c:244-249) */
 };
@@ -68,13 +70,13 @@ __device__ __forceinline__ uint32_t ct_bf16_rn(float v) {
  * mapA*: activation planes [L, Cin]; mapW*: weight planes [phases*taps*Cout, Cin] */
 __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant__ CUtensorMap mapAh, const __grid_constant__ CUtensorMap mapAl,
                                                             const __grid_constant__ CUtensorMap mapWh, const __grid_constant__ CUtensorMap mapWl,
-                                                            const ConvTcArgs a) {
+                                                            const __grid_constant__ CUtensorMap mapAx, const ConvTcArgs a) {
     extern __shared__ __align__(1024) unsigned char ct_smem_raw[];
     __shared__ __align__(8) uint64_t full[4], empty[4], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_s;
     unsigned char *tiles = reinterpret_cast<unsigned char *>(((uintptr_t)ct_smem_raw + 1023) & ~(uintptr_t)1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b_bytes = a.N * CT_BK * 2, stage_bytes = 2 * CT_A_BYTES + 2 * b_bytes;
+    const int b_bytes = a.N * CT_BK * 2, a_bytes = a.aplanes * CT_A_BYTES, stage_bytes = a_bytes + a.wplanes * b_bytes;
     const int iters = a.taps * a.kb_per_tap;
     /* TMEM: two buffers (tile j, tile j + 1), each with TWO accumulators: hi.hi products go to the first, the two cross terms
      * (2^-8 of the magnitude) to the second; the epilogue adds them in fp32.  The tensor core's accumulate step loses low bits
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAl) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapWh) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&mapWl) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&mapAx) : "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(&tmem_base_s)), "r"(tmem_cols) : "memory");
@@ -111,14 +114,15 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
                     const int st = g % a.stages, ph = (g / a.stages) & 1;
                     const int tap = it / a.kb_per_tap, kb = it - tap * a.kb_per_tap;
                     if (g >= a.stages) tc_mbar_wait(&empty[st], ph ^ 1);
-                    unsigned char *sa = tiles + (size_t)st * stage_bytes, *sb = sa + 2 * CT_A_BYTES;
+                    unsigned char *sa = tiles + (size_t)st * stage_bytes, *sb = sa + a_bytes;
                     tc_mbar_expect_tx(&full[st], stage_bytes);
                     const int arow = t0 - (a.taps - 1 - tap) * a.dil;              /* may be negative: rows before t = 0 are zeros */
                     const int wrow = (phase * a.taps + tap) * a.Cout + n0;
                     tc_tma_2d(sa, &mapAh, kb * CT_BK, arow, &full[st]);
                     tc_tma_2d(sa + CT_A_BYTES, &mapAl, kb * CT_BK, arow, &full[st]);
+                    if (a.aplanes == 3) tc_tma_2d(sa + 2 * CT_A_BYTES, &mapAx, kb * CT_BK, arow, &full[st]);
                     tc_tma_2d(sb, &mapWh, kb * CT_BK, wrow, &full[st]);
-                    tc_tma_2d(sb + b_bytes, &mapWl, kb * CT_BK, wrow, &full[st]);
+                    if (a.wplanes == 2) tc_tma_2d(sb + b_bytes, &mapWl, kb * CT_BK, wrow, &full[st]);
                 }
             }
         }
@@ -134,14 +138,18 @@ __global__ void __launch_bounds__(CT_THREADS, 1) k_conv_tc(const __grid_constant
                     const int st = g % a.stages, ph = (g / a.stages) & 1;
                     tc_mbar_wait(&full[st], ph);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t sa = tc_smem_u32(tiles + (size_t)st * stage_bytes), sb = sa + 2 * CT_A_BYTES;
-                    const uint64_t ah = tc_smem_desc(sa), al = tc_smem_desc(sa + CT_A_BYTES), bh = tc_smem_desc(sb), bl = tc_smem_desc(sb + b_bytes);
+                    const uint32_t sa = tc_smem_u32(tiles + (size_t)st * stage_bytes), sb = sa + a_bytes;
+                    const uint64_t ah = tc_smem_desc(sa), al = tc_smem_desc(sa + CT_A_BYTES), ax = tc_smem_desc(sa + 2 * CT_A_BYTES);
+                    const uint64_t bh = tc_smem_desc(sb), bl = tc_smem_desc(sb + b_bytes);
 #pragma unroll
                     for (int k = 0; k < CT_BK / 16; k++) {       /* UMMA K = 16 bf16 = 32 bytes inside the swizzle row */
                         const uint64_t o = (uint64_t)(k * 2);
                         tc_mma(acc, ah + o, bh + o, idesc, (it | k) != 0);
-                        tc_mma(acc2, ah + o, bl + o, idesc, (it | k) != 0);
-                        tc_mma(acc2, al + o, bh + o, idesc, 1);
+                        if (a.wplanes == 2) { tc_mma(acc2, ah + o, bl + o, idesc, (it | k) != 0); tc_mma(acc2, al + o, bh + o, idesc, 1); }
+                        else {
+                            tc_mma(acc2, al + o, bh + o, idesc, (it | k) != 0);
+                            if (a.aplanes == 3) tc_mma(acc2, ax + o, bh + o, idesc, 1);
+                        }
                     }
                     tc_commit(&empty[st]);
                 }
@@ -368,16 +376,18 @@ bool qtc_conv_tc_ok(int cin, int cout) { return cin % 8 == 0 && cout % 32 == 0 &
 static int g_ct_attr = 0;
 /* out rows = L * phases.  in_hi/in_lo: [L, Cin] planes.  Any of out_raw / out_hi may be NULL; alpha NULL: planes hold the raw output */
 int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint16_t *in_lo, int L, int dil, const float *bias, const float *res,
-                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta, const float *scale, int gelu) {
+                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta, const float *scale, int gelu,
+                const uint16_t *in_x) {
     if (L <= 0) return 0;
     ConvTcArgs a;
     memset(&a, 0, sizeof(a));
-    a.scale = scale; a.gelu = gelu;
+    a.scale = scale; a.gelu = gelu; a.wplanes = w->lo ? 2 : 1; a.aplanes = in_x ? 3 : 2;
+    if (in_x && w->lo) { qtc_set_error("conv_tc: a third activation plane goes with single-plane (bf16) weights only"); return -1; }
     a.L = L; a.Cin = w->cin; a.Cout = w->cout; a.N = pick_n(w->cout); a.taps = w->taps; a.dil = dil; a.os = w->phases;
     a.kb_per_tap = (w->cin + CT_BK - 1) / CT_BK;
     a.bias = bias; a.res = res; a.out_raw = out_raw; a.out_hi = out_hi; a.out_lo = out_lo; a.alpha = alpha; a.inv_beta = inv_beta;
     if (a.N <= 0 || w->cin % 8) { qtc_set_error("conv_tc: Cout %d / Cin %d not tileable", w->cout, w->cin); return -1; }
-    const int stage_bytes = 2 * CT_A_BYTES + 2 * a.N * CT_BK * 2;
+    const int stage_bytes = a.aplanes * CT_A_BYTES + a.wplanes * a.N * CT_BK * 2;
     /* one persistent CTA per SM: as many stages as fit (2-4) */
     int stages = (220 * 1024) / stage_bytes;
     if (stages > 4) stages = 4;
@@ -387,12 +397,13 @@ int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint1
     if (!g_ct_attr) { QTC_CUDA(cudaFuncSetAttribute(k_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024)); g_ct_attr = 1; }
     const CUtensorMap *mah = qtc_tmap_bf16(in_hi, L, w->cin, TC_BM), *mal = qtc_tmap_bf16(in_lo, L, w->cin, TC_BM);
     const int wrows = w->phases * w->taps * w->cout;
-    const CUtensorMap *mwh = qtc_tmap_bf16(w->hi, wrows, w->cin, a.N), *mwl = qtc_tmap_bf16(w->lo, wrows, w->cin, a.N);
-    if (!mah || !mal || !mwh || !mwl) return -1;
+    const CUtensorMap *mwh = qtc_tmap_bf16(w->hi, wrows, w->cin, a.N), *mwl = w->lo ? qtc_tmap_bf16(w->lo, wrows, w->cin, a.N) : mwh;
+    const CUtensorMap *max_ = in_x ? qtc_tmap_bf16(in_x, L, w->cin, TC_BM) : mah;
+    if (!mah || !mal || !mwh || !mwl || !max_) return -1;
     const long long ntiles = (long long)((L + TC_BM - 1) / TC_BM) * (w->cout / a.N) * w->phases;
     const int sms = c->num_sms > 0 ? c->num_sms : 148;
     const dim3 grid((unsigned)(ntiles < sms ? ntiles : sms));
-    k_conv_tc<<<grid, CT_THREADS, smem, c->cstream>>>(*mah, *mal, *mwh, *mwl, a);
+    k_conv_tc<<<grid, CT_THREADS, smem, c->cstream>>>(*mah, *mal, *mwh, *mwl, *max_, a);
     c->launches++;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { qtc_set_error("conv_tc launch -> %s", cudaGetErrorString(e)); return -1; }

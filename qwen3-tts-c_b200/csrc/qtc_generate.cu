@@ -51,6 +51,9 @@ extern "C" int qwen_tts_cuda_get_kv_len(const qtc_ctx_t *c) {
  * operations of a decode step, in the same order (oracle/qtts_oracle.c:orc_lm_step, pinned to the reference) */
 static int prefill_dev(qtc_ctx *c, const float *embeds_dev, int seq_len) {
     if (qtc_ensure_kv(c, &c->tk, &c->talker, c->state_host->pos + seq_len + 1)) return -1;
+    /* fast arithmetic: ONE batched pass, every projection a tensor-core GEMM over the seq_len rows (qtc_prefill.cuh);
+     * strict arithmetic (and QTC_PREFILL_GEMM=0): token by token, bit-identical to the reference */
+    if (seq_len >= 2 && qtc_prefill_gemm_ok(c)) return qtc_prefill_gemm(c, embeds_dev, seq_len, c->state_host->pos);
     for (int t = 0; t < seq_len; t++) {
         if (qtc_copy(c, c->tk.x, embeds_dev + (size_t)t * c->H, c->H)) return -1;
         if (qtc_lm_step(c, &c->talker, &c->tk, &c->state->pos, 0)) return -1;

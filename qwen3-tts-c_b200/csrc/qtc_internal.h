@@ -106,6 +106,7 @@ struct LmBuffers {
 };
 
 struct CodecDev;   /* qtc_codec.cu */
+struct PfBuf;      /* qtc_prefill.cuh: scratch of the batched prefill */
 struct BatchBuf;   /* qtc_batch.cu */
 
 struct qtc_ctx {
@@ -152,6 +153,7 @@ struct qtc_ctx {
     float *host_stage;            /* pinned staging for stage-API vectors */
     size_t host_stage_bytes;
     CodecDev *codec;
+    PfBuf *pf;
     qtc_gen_params_t params;
     qtc_perf_t perf;
     int mode;                     /* 0 per-op kernels, 1 fused persistent kernels (default) */
@@ -189,6 +191,9 @@ int qtc_embed_row(qtc_ctx *c, float *out, const uint16_t *table, const int *idx_
 int qtc_sample(qtc_ctx *c, const float *logits, const SampleCfg &cfg, uint32_t *rng, int *hist_count,
                int *out_token, GenState *st, int role);
 int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need);
+int qtc_prefill_gemm(qtc_ctx *c, const float *embeds_dev, int seq_len, int base);   /* qtc_prefill.cuh */
+bool qtc_prefill_gemm_ok(const qtc_ctx *c);
+void qtc_prefill_release(qtc_ctx *c);
 int qtc_kv_pool_init(qtc_ctx *c, int max_batch);
 int qtc_kv_reserve(qtc_ctx *c, int slot, int positions);      /* the slot holds pages for at least `positions` positions */
 void qtc_kv_release_all(qtc_ctx *c);
@@ -216,7 +221,8 @@ bool qtc_conv_tc_ok(int cin, int cout);
 int qtc_conv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cout, int cin, int K);
 int qtc_tconv_tc_prep(qtc_ctx *c, ConvTcW *o, const float *w, int cin, int cout, int k, int s);
 int qtc_conv_tc(qtc_ctx *c, const ConvTcW *w, const uint16_t *in_hi, const uint16_t *in_lo, int L, int dil, const float *bias, const float *res,
-                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta, const float *scale = NULL, int gelu = 0);
+                float *out_raw, uint16_t *out_hi, uint16_t *out_lo, const float *alpha, const float *inv_beta, const float *scale = NULL, int gelu = 0,
+                const uint16_t *in_x = NULL);   /* in_x: third activation plane (exact 3-piece split; bf16 weights only) */
 int qtc_rows_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, size_t n);
 int qtc_dwconv_tm(qtc_ctx *c, float *out, const float *in, const float *w, const float *bias, int C, int K, int L);
 int qtc_cf_to_planes(qtc_ctx *c, uint16_t *hi, uint16_t *lo, const float *src, int C, int L, const float *alpha, const float *inv_beta);

@@ -25,7 +25,7 @@ static qtc_ctx *kctx() {
         g_k = new qtc_ctx();
         g_k->launches = 0; g_k->arith = g_k_strict; g_k->mode = 0;
         if (cudaStreamCreateWithFlags(&g_k->stream, cudaStreamNonBlocking) != cudaSuccess) { delete g_k; g_k = NULL; return NULL; }
-        g_k->cstream = g_k->stream; g_k->stream2 = NULL; g_k->codec_tc = 0;
+        g_k->cstream = g_k->stream; g_k->stream2 = NULL; g_k->codec_tc = 0; g_k->pf = NULL;
         g_k->sample_scratch = NULL; g_k->sample_scratch_f = NULL;
     }
     g_k->arith = g_k_strict;

@@ -448,4 +448,5 @@ int qtc_sample_bare(qtc_ctx *c, const float *logits_dev, int vocab, int top_k, f
     return 0;
 }
 
+#include "qtc_prefill.cuh"
 #include "qtc_batch.cuh"
