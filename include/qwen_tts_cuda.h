@@ -293,6 +293,17 @@ int qwen_tts_cuda_swiglu_matvec_bf16(float *out, const uint16_t *gate_up_fused, 
 int qwen_tts_cuda_rms_norm(float *out, const float *x, const float *w, int dim, float eps);
 int qwen_tts_cuda_sample_top_k(const float *logits, int vocab, int top_k, float top_p,
                                float temperature, float *rng_state);   /* returns token */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  The same sampling kernel as
+ * qwen_tts_cuda_sample_top_k, allocating nothing: logits_dev [vocab] f32, rng_state_dev (1 x f32 holding the xorshift
+ * bits, advanced in place) and token_dev (1 x int32, receives the token) are DEVICE pointers of the caller; the launch is
+ * queued on cuda_stream (a cudaStream_t; NULL = the default stream) and NOT synchronised.  The top-p / large-k branches'
+ * scratch is a static device array of QTC_NOALLOC_MAX_VOCAB (16384) entries = 128 KB per GPU, held until exit: vocab
+ * beyond that is rejected with -1 and a message in qwen_tts_cuda_last_error().  Every call shares the array, so calls
+ * that overlap on the GPU race - serialise them.  Returns 0 when the launch was queued. */
+#define QTC_NOALLOC_MAX_VOCAB 16384
+int qwen_tts_cuda_sample_top_k_noalloc(const float *logits_dev, int vocab, int top_k, float top_p, float temperature,
+                                       float *rng_state_dev, int *token_dev, void *cuda_stream);
 int qwen_tts_cuda_causal_conv1d(float *out, const float *in, const float *w, const float *b,
                                 int cin, int cout, int k, int length, int dilation, int groups);
 int qwen_tts_cuda_transposed_conv1d(float *out, const float *in, const float *w, const float *b,

@@ -450,3 +450,52 @@ int qtc_sample_bare(qtc_ctx *c, const float *logits_dev, int vocab, int top_k, f
 
 #include "qtc_prefill.cuh"
 #include "qtc_batch.cuh"
+
+/* ---- allocation-free sampler entry point (no counterpart in the reference) ----
+ * For callers that may not allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.
+ * Same k_sample launch as qtc_sample_bare, but the slow paths' scratch (V floats + V ints: the top_p / literal-insertion
+ * branches of block_sample_t) lives in a file-scope device array instead of two cudaMalloc'd buffers.  Every GPU that loads
+ * the library holds QTC_NOALLOC_MAX_VOCAB * 8 = 128 KB of it until exit.  Inputs and outputs are DEVICE pointers of the
+ * caller; the launch goes to the caller's stream and is not synchronised here.
+ * The array is shared by every call and keeps the last call's contents.  Nothing in it has to start at zero: each branch
+ * writes the entries it later reads (p[0..V) and ord[0..V), or val/idx[0..k)) before reading them, so no clear is issued.
+ * Calls that overlap on the GPU (two streams, two host threads) race on the array: serialise them.
+ * In host code g_noalloc_scratch is a stand-in symbol, not a device address: the address comes from cudaGetSymbolAddress,
+ * taken once per device with that device current. */
+#ifndef QTC_NOALLOC_MAX_VOCAB
+#define QTC_NOALLOC_MAX_VOCAB 16384        /* also in include/qwen_tts_cuda.h */
+#endif
+#define QTC_NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(size_t)QTC_NOALLOC_MAX_VOCAB * 8];
+static void *g_noalloc_dev_ptr[QTC_NOALLOC_MAX_DEVICES];
+
+extern "C" int qwen_tts_cuda_sample_top_k_noalloc(const float *logits_dev, int vocab, int top_k, float top_p, float temperature,
+                                                  float *rng_state_dev, int *token_dev, void *cuda_stream) {
+    if (!logits_dev || !rng_state_dev || !token_dev) { qtc_set_error("sample_top_k_noalloc: NULL device pointer"); return -1; }
+    if (vocab <= 0 || vocab > QTC_NOALLOC_MAX_VOCAB) {
+        qtc_set_error("sample_top_k_noalloc: vocab %d outside (0, %d] - the static scratch holds %d entries", vocab, QTC_NOALLOC_MAX_VOCAB,
+                      QTC_NOALLOC_MAX_VOCAB);
+        return -1;
+    }
+    int dev = -1;
+    QTC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= QTC_NOALLOC_MAX_DEVICES) { qtc_set_error("sample_top_k_noalloc: device %d out of range", dev); return -1; }
+    if (!g_noalloc_dev_ptr[dev]) {                      /* set-up, once per device, with that device current */
+        void *p = NULL;
+        QTC_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) { qtc_set_error("sample_top_k_noalloc: cudaGetSymbolAddress returned NULL"); return -1; }
+        QTC_CUDA(cudaFuncSetAttribute(k_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+        g_noalloc_dev_ptr[dev] = p;
+    }
+    SampleArgs a;
+    memset(&a, 0, sizeof(a));
+    a.logits = logits_dev;
+    a.cfg.vocab = vocab; a.cfg.top_k = top_k; a.cfg.top_p = top_p; a.cfg.temperature = temperature;
+    a.cfg.suppress_from = -1; a.cfg.eos_id = -1; a.cfg.rep_penalty = 1.0f;
+    a.rng = (uint32_t *)rng_state_dev; a.out_token = token_dev; a.role = 1;
+    a.scratch_f = (float *)g_noalloc_dev_ptr[dev];
+    a.scratch_i = (int *)((unsigned char *)g_noalloc_dev_ptr[dev] + (size_t)QTC_NOALLOC_MAX_VOCAB * 4);
+    k_sample<<<1, SAMPLE_THREADS, (size_t)vocab * 8, (cudaStream_t)cuda_stream>>>(a);
+    QTC_CUDA(cudaGetLastError());
+    return 0;
+}

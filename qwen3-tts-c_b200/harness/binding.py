@@ -161,6 +161,7 @@ def load_cuda():
     lib.qwen_tts_cuda_swiglu_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_rms_norm.argtypes = [f32p, f32p, f32p, C.c_int, C.c_float]
     lib.qwen_tts_cuda_sample_top_k.argtypes = [f32p, C.c_int, C.c_int, C.c_float, C.c_float, f32p]
+    lib.qwen_tts_cuda_sample_top_k_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.qwen_tts_cuda_causal_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 6
     lib.qwen_tts_cuda_transposed_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 5 + [i32p]
     lib.qwen_tts_cuda_snake_beta.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int]
