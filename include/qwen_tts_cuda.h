@@ -327,6 +327,9 @@ double qwen_tts_cuda_subtalker_frame_bytes(const qtc_ctx_t *ctx);
 /* per-phase SM-clock stamps of the fused talker step (layer `layer`, KV position `pos`): 16 slots per CTA,
  * out[num_sms*16]; returns the CTA count.  Evidence for profiles/, not part of the reference's interface. */
 int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *ctx, int pos, int layer, long long *out);
+/* mode 2 (cluster kernel) diagnostics: *capacity = 16-CTA clusters the device holds at once (-1 before the first mode-2 step;
+ * mode 2 needs kv_heads of them), *gave_up = 1 if a grid-barrier wait of that kernel ever hit its spin bound.  No reference counterpart. */
+int qwen_tts_cuda_cluster_status(qtc_ctx_t *ctx, int *capacity, int *gave_up);
 const char *qwen_tts_cuda_last_error(void);
 
 #ifdef __cplusplus

@@ -92,7 +92,7 @@ static int upload_lm(qtc_ctx *c, LmDev *d, const qtc_lm_t *h) {
         if (!h->final_norm) { qtc_set_error("decoder stack without final norm"); return -1; }
         d->final_norm = qtc_upload(c, h->final_norm, H);
     }
-    return 0;
+    return qtc_cluster_prepare(c, d);
 }
 
 static int alloc_lm_buffers(qtc_ctx *c, LmBuffers *b, const LmDev *lm) {
@@ -102,6 +102,9 @@ static int alloc_lm_buffers(qtc_ctx *c, LmBuffers *b, const LmDev *lm) {
     b->q = (float *)qtc_dmalloc(c, qd * 4); b->kk = (float *)qtc_dmalloc(c, kvd * 4); b->vv = (float *)qtc_dmalloc(c, kvd * 4);
     b->att = (float *)qtc_dmalloc(c, qd * 4); b->g = (float *)qtc_dmalloc(c, (size_t)lm->inter * 4);
     b->logits = (float *)qtc_dmalloc(c, (size_t)lm->vocab * 4);
+    b->xacc = (long long *)qtc_dmalloc(c, 3 * H * 8); b->cl_phase = (int *)qtc_dmalloc(c, 16);
+    if (!b->xacc || !b->cl_phase) return -1;
+    cudaMemset(b->xacc, 0, 3 * H * 8); cudaMemset(b->cl_phase, 0, 16);
     return (b->x && b->xn && b->q && b->kk && b->vv && b->att && b->g && b->logits) ? 0 : -1;
 }
 
@@ -135,7 +138,8 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     c->host = *desc;
     c->H = desc->talker.hidden; c->G = desc->num_code_groups; c->max_batch = max_batch > 0 ? max_batch : 1;
     c->bb = NULL; c->pf = NULL; c->batch_pieces = 3; c->dev_mallocs = 0;
-    c->mode = 1; c->arith = 0; c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
+    c->mode = 2; c->arith = 0;
+    { const char *e = getenv("QTC_MODE"); if (e) c->mode = atoi(e) < 0 ? 0 : atoi(e) > 2 ? 2 : atoi(e); } c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
     c->codec = NULL; c->codes = NULL; c->trailing = NULL; c->prefill = NULL; c->codes_cap = c->trailing_cap = c->prefill_cap = 0;
     memset(&c->tk, 0, sizeof(c->tk)); memset(&c->st, 0, sizeof(c->st)); memset(&c->perf, 0, sizeof(c->perf));
     memset(&c->talker, 0, sizeof(c->talker)); memset(&c->sub, 0, sizeof(c->sub));
@@ -200,6 +204,8 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
         c->talker_dev = (LmDev *)qtc_dmalloc(c, sizeof(LmDev));
         c->sub_dev = (LmDev *)qtc_dmalloc(c, sizeof(LmDev));
         c->bar = (unsigned long long *)qtc_dmalloc(c, 64);
+        c->cl_err = (int *)qtc_dmalloc(c, 16);
+        if (c->cl_err) cudaMemset(c->cl_err, 0, 16);
         c->head_cnt = (unsigned *)qtc_dmalloc(c, (size_t)(heads > 0 ? heads : 1) * 4);
         c->attn_part = (float *)qtc_dmalloc(c, (size_t)(heads > 0 ? heads : 1) * 16 * (hd + 2) * 4);   /* FUSED_MAX_SPLIT */
         if (!c->talker_dev || !c->sub_dev || !c->bar || !c->head_cnt || !c->attn_part) { qwen_tts_cuda_release(c); return NULL; }
@@ -235,7 +241,7 @@ extern "C" void qwen_tts_cuda_get_perf(const qtc_ctx_t *c, qtc_perf_t *out) {
     out->kv_pages_in_use = used;
 }
 extern "C" int qwen_tts_cuda_set_mode(qtc_ctx_t *c, int mode) {
-    if (!c || mode < 0 || mode > 1) return -1;
+    if (!c || mode < 0 || mode > 2) return -1;
     c->mode = mode; c->graph_key = -1;
     return 0;
 }

@@ -1,0 +1,510 @@
+/*
+ * qtc_cluster.cuh - k_lm_cluster (mode 2): one decoder-stack step with TWO grid-wide exchanges per layer
+ * instead of five (talker_attention_single, c/qwen_tts_talker.c:119-248; ST_FORWARD :638-691).
+ *
+ * Round 1/2 measurements (profiles/r01_phase_clocks_*_v9.txt): of the 36.0 us a talker layer takes in k_lm_fused,
+ * 13.1 us are its five grid barriers; of the sub-talker's 22.0 us, 11.4 us.  Cheaper barriers lost (mode 3); this
+ * kernel removes three of them by changing who owns what:
+ *
+ *   grid = up to 15 clusters x 8 CTAs of 512 threads (a B200 holds 15 clusters of 8 at one CTA per SM, 7 of 16:
+ *   scripts/probe/cluster_capacity.cu; k_lm_fused at 64 CTAs is only 14-20 % slower than at 148 - the step is bound by
+ *   exchanges, not by SM count).
+ *   Phase A (cluster g < kv_heads owns KV head g and its two query heads; the other clusters go straight to the barrier):
+ *     RMSNorm -> the 512 rows [q_2g | q_2g+1 | k_g | v_g] of the QKV projection, 64 rows per CTA, results pushed
+ *     into every peer's shared memory (st.shared::cluster) -> cluster barrier -> attention over the cached
+ *     positions split 8 ways (both query heads share each K/V row), CTA partials (max, sum, out) combined through
+ *     DSMEM -> the O projection restricted to this cluster's 256 input columns (weights re-laid out at upload so the
+ *     slice is contiguous) = a PARTIAL sum for every row of x.
+ *   Phase B (every CTA owns a run of 8-column chunks of the MLP's inner dimension): RMSNorm -> gate/up -> SwiGLU in
+ *     shared memory -> the down projection restricted to those input columns (re-laid out [I/8][H][8]) = a partial
+ *     for every row of x, reduced over the 8 CTAs of the cluster through DSMEM in a fixed order.
+ *   The partial sums of both phases meet in HBM/L2 as 64-bit FIXED-POINT atomic adds (scale 2^32): integer addition
+ *   is associative, so the result does not depend on arrival order - the step stays bit-reproducible - and the
+ *   residual stream is carried exactly.  Three accumulators rotate: phase p reads buf[p % 3], adds into
+ *   buf[(p + 1) % 3] (pre-zeroed), zeroes buf[(p + 2) % 3]; one grid barrier per phase.
+ *
+ * Arithmetic: fast mode only (fp32 FMA, tree reductions); results differ from k_lm_fused by summation order.
+ */
+#pragma once
+#include <cooperative_groups.h>
+#include "qtc_fused_main.cuh"
+
+namespace cg = cooperative_groups;
+
+#define CL_SIZE 8
+#define CL_THREADS 512
+#define CL_WARPS 16
+#define CL_ATT_CAP 64                 /* staged positions per CTA (contexts up to 8 x 64 = 512; longer ones read K/V through L2) */
+#define CL_REC 132                    /* partial record: max, sum, -, -, out[128] */
+#define CL_FX 4294967296.0f           /* 2^32 */
+#define CL_FX_INV 2.3283064365386963e-10f
+
+struct ClusterArgs {
+    const LmDev *lm;
+    float *x;                          /* [H] input on entry, post-final-norm hidden on exit (talker) */
+    long long *xacc;                   /* [3][H] fixed-point residual stream */
+    int *phase;                        /* device: phase counter mod 3, carried across launches */
+    float *kc, *vc; const int *table; const float *cos, *sin; int kv_max;
+    const int *pos_ptr; int pos_add;
+    const uint16_t *head_w; int head_rows; float *logits;
+    unsigned long long *bar;
+    GenState *st;
+    int xs_floats;                     /* staged-vector / sampler region */
+    int flags;
+    long long *prof; int prof_layer;
+    int *err;                          /* set to 1 if a barrier wait gave up */
+};
+
+__device__ __forceinline__ void red_add_s64(long long *p, long long v) {
+    asm volatile("red.relaxed.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ long long to_fx(float v) { return __float2ll_rn(v * CL_FX); }
+__device__ __forceinline__ float from_fx(long long v) { return __ll2float_rn(v) * CL_FX_INV; }
+
+/* grid barrier with a bounded spin: a lost CTA must not hang the device */
+__device__ __forceinline__ void cl_barrier_wait(unsigned long long *bar, const unsigned long long &target, int *err) {
+    if (threadIdx.x == 0) {
+        unsigned spins = 0;
+        while (ld_acquire_u64(bar) < target) {
+            if (++spins > (1u << 26)) { if (err) *err = 1; break; }
+        }
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void cl_barrier_arrive(unsigned long long *bar, unsigned long long &target, unsigned nb) {
+    __syncthreads();
+    if (threadIdx.x == 0) { target += nb; red_release_inc(bar); }
+}
+
+/* xs = rmsnorm(x) * w for H <= 4096; x comes as fp32 (the step's input) or from a fixed-point accumulator */
+__device__ __forceinline__ void cl_stage_norm(float *xs, const float *xf, const long long *xq, const float *w, int n, float eps, float *red) {
+    const int i0 = threadIdx.x * 4, i1 = i0 + CL_THREADS * 4;
+    float4 v0 = make_float4(0, 0, 0, 0), v1 = v0, w0 = v0, w1 = v0;
+    if (xf) {
+        if (i0 < n) v0 = __ldcg(reinterpret_cast<const float4 *>(xf + i0));
+        if (i1 < n) v1 = __ldcg(reinterpret_cast<const float4 *>(xf + i1));
+    } else {
+        if (i0 < n) {
+            const longlong2 a = __ldcg(reinterpret_cast<const longlong2 *>(xq + i0)), b = __ldcg(reinterpret_cast<const longlong2 *>(xq + i0 + 2));
+            v0 = make_float4(from_fx(a.x), from_fx(a.y), from_fx(b.x), from_fx(b.y));
+        }
+        if (i1 < n) {
+            const longlong2 a = __ldcg(reinterpret_cast<const longlong2 *>(xq + i1)), b = __ldcg(reinterpret_cast<const longlong2 *>(xq + i1 + 2));
+            v1 = make_float4(from_fx(a.x), from_fx(a.y), from_fx(b.x), from_fx(b.y));
+        }
+    }
+    if (i0 < n) w0 = *reinterpret_cast<const float4 *>(w + i0);
+    if (i1 < n) w1 = *reinterpret_cast<const float4 *>(w + i1);
+    float ss = v0.x * v0.x;
+    ss = fmaf(v0.y, v0.y, ss); ss = fmaf(v0.z, v0.z, ss); ss = fmaf(v0.w, v0.w, ss);
+    ss = fmaf(v1.x, v1.x, ss); ss = fmaf(v1.y, v1.y, ss); ss = fmaf(v1.z, v1.z, ss); ss = fmaf(v1.w, v1.w, ss);
+    ss = csum(ss, red);
+    const float inv = 1.0f / sqrtf(ss / (float)n + eps);
+    if (i0 < n) *reinterpret_cast<float4 *>(xs + i0) = make_float4(v0.x * inv * w0.x, v0.y * inv * w0.y, v0.z * inv * w0.z, v0.w * inv * w0.w);
+    if (i1 < n) *reinterpret_cast<float4 *>(xs + i1) = make_float4(v1.x * inv * w1.x, v1.y * inv * w1.y, v1.z * inv * w1.z, v1.w * inv * w1.w);
+    __syncthreads();
+}
+
+/* trip_issue of qtc_fused_main.cuh with every register written on every call: a conditionally written WTrip stays live around
+ * the whole layer loop (the old value might survive) and ptxas then parks it in local memory - measured: 70 STL right after the loads */
+__device__ __forceinline__ void cl_trip_issue(WTrip &t, const uint16_t *ra, const uint16_t *rb, int cols) {
+    const int lane = threadIdx.x & 31, n8 = cols >> 3;
+    const uint4 *w0 = reinterpret_cast<const uint4 *>(ra), *w1 = reinterpret_cast<const uint4 *>(rb);
+#pragma unroll
+    for (int j = 0; j < PFJ; j++) {
+        const int p = lane + 32 * j;
+        if (p < n8) { t.a[j] = ldg_stream(w0 + p); t.b[j] = ldg_stream(w1 + p); }
+        else { t.a[j] = make_uint4(0, 0, 0, 0); t.b[j] = make_uint4(0, 0, 0, 0); }
+    }
+}
+
+/* row j (0..511) of cluster g's QKV block: [q head 2g | q head 2g+1 | k head g | v head g] */
+__device__ __forceinline__ const uint16_t *cl_qkv_row(const LmLayerDev &w, int g, int j, int H) {
+    if (j < 256) return w.wq + ((size_t)(g * 256 + j)) * H;
+    if (j < 384) return w.wk + ((size_t)(g * 128 + j - 256)) * H;
+    return w.wv + ((size_t)(g * 128 + j - 384)) * H;
+}
+
+/* per-warp: RMS-normalise a 128-wide head held in shared memory and rotate it (lane i owns dims 4i..4i+3) */
+__device__ __forceinline__ float4 cl_norm_rope(const float *src, const float *nw, const float4 c4, const float4 s4, float eps) {
+    const int lane = threadIdx.x & 31;
+    const float4 v = reinterpret_cast<const float4 *>(src)[lane], n4 = reinterpret_cast<const float4 *>(nw)[lane];
+    float ss = v.x * v.x;
+    ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
+    ss = warp_sum(ss);
+    const float inv = 1.0f / sqrtf(ss / 128.0f + eps);
+    const float4 y = make_float4(v.x * inv * n4.x, v.y * inv * n4.y, v.z * inv * n4.z, v.w * inv * n4.w);
+    const float px = __shfl_xor_sync(0xffffffffu, y.x, 16), py = __shfl_xor_sync(0xffffffffu, y.y, 16);
+    const float pz = __shfl_xor_sync(0xffffffffu, y.z, 16), pw = __shfl_xor_sync(0xffffffffu, y.w, 16);
+    return lane < 16 ? make_float4(y.x * c4.x - px * s4.x, y.y * c4.y - py * s4.y, y.z * c4.z - pz * s4.z, y.w * c4.w - pw * s4.w)
+                     : make_float4(y.x * c4.x + px * s4.x, y.y * c4.y + py * s4.y, y.z * c4.z + pz * s4.z, y.w * c4.w + pw * s4.w);
+}
+__device__ __forceinline__ float dot4(const float4 a, const float4 b) {
+    float d = a.x * b.x;
+    d = fmaf(a.y, b.y, d); d = fmaf(a.z, b.z, d); d = fmaf(a.w, b.w, d);
+    return d;
+}
+
+/* Attention of cluster g at position pos: positions [t0, t1) of this CTA, both query heads per K/V row.
+ * qkv: this CTA's copy of the cluster's 512 projection outputs.  Leaves the CTA's partial records in cpart[2][CL_REC]. */
+__device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int t0, int t1, bool staged,
+                                             const float *qkv, float *wpart, float *cpart, const float *kvs) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, kvd = lm.kv_heads * 128;
+    const LmLayerDev &w = lm.layer[l];
+    float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
+    const float4 c4 = reinterpret_cast<const float4 *>(a.cos + (size_t)pos * 128)[lane], s4 = reinterpret_cast<const float4 *>(a.sin + (size_t)pos * 128)[lane];
+    const bool mine = warp < t1 - t0;                                  /* this warp has at least one position */
+    const bool has_new = t1 == pos + 1 && pos >= t0 && ((pos - t0) % CL_WARPS) == warp;
+    float m0 = -3.402823466e+38f, m1 = m0, l0 = 0.0f, l1 = 0.0f;
+    float4 o0 = make_float4(0, 0, 0, 0), o1 = o0;
+    if (mine) {
+        const float4 q0 = cl_norm_rope(qkv, w.q_norm, c4, s4, lm.eps), q1 = cl_norm_rope(qkv + 128, w.q_norm, c4, s4, lm.eps);
+        float4 k_new = make_float4(0, 0, 0, 0), v_new = k_new;
+        if (has_new) {
+            k_new = cl_norm_rope(qkv + 256, w.k_norm, c4, s4, lm.eps);
+            v_new = reinterpret_cast<const float4 *>(qkv + 384)[lane];
+            const size_t off = kv_off(a.table, pos, kvd);
+            *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
+            *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
+        }
+        const float *Ks = kvs, *Vs = kvs + CL_ATT_CAP * 128;
+        const float scale = 0.08838834764831845f;                      /* 1 / sqrt(128) */
+        for (int tb = t0 + warp; tb < t1; tb += 4 * CL_WARPS) {
+            float d0[4], d1[4];
+            float4 vr[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int t = tb + CL_WARPS * j;
+                float4 kr = make_float4(0, 0, 0, 0);
+                vr[j] = kr;
+                if (t < t1) {
+                    if (t < pos) {
+                        if (staged) {
+                            kr = *reinterpret_cast<const float4 *>(Ks + (size_t)(t - t0) * 128 + lane * 4);
+                            vr[j] = *reinterpret_cast<const float4 *>(Vs + (size_t)(t - t0) * 128 + lane * 4);
+                        } else {
+                            const size_t off = kv_off(a.table, t, kvd);
+                            kr = __ldcg(reinterpret_cast<const float4 *>(kc + off) + lane);
+                            vr[j] = __ldcg(reinterpret_cast<const float4 *>(vc + off) + lane);
+                        }
+                    } else { kr = k_new; vr[j] = v_new; }
+                }
+                d0[j] = dot4(q0, kr); d1[j] = dot4(q1, kr);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                float u0[4], u1[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { u0[j] = __shfl_xor_sync(0xffffffffu, d0[j], o); u1[j] = __shfl_xor_sync(0xffffffffu, d1[j], o); }
+#pragma unroll
+                for (int j = 0; j < 4; j++) { d0[j] += u0[j]; d1[j] += u1[j]; }
+            }
+            float b0 = m0, b1 = m1;
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (tb + CL_WARPS * j < t1) { d0[j] *= scale; d1[j] *= scale; b0 = fmaxf(b0, d0[j]); b1 = fmaxf(b1, d1[j]); }
+            const float f0 = __expf(m0 - b0), f1 = __expf(m1 - b1);      /* first batch: exp(-huge) = 0 on zeros */
+            l0 *= f0; o0.x *= f0; o0.y *= f0; o0.z *= f0; o0.w *= f0;
+            l1 *= f1; o1.x *= f1; o1.y *= f1; o1.z *= f1; o1.w *= f1;
+            m0 = b0; m1 = b1;
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (tb + CL_WARPS * j < t1) {
+                    const float e0 = __expf(d0[j] - m0), e1 = __expf(d1[j] - m1);
+                    l0 += e0; l1 += e1;
+                    o0.x = fmaf(e0, vr[j].x, o0.x); o0.y = fmaf(e0, vr[j].y, o0.y); o0.z = fmaf(e0, vr[j].z, o0.z); o0.w = fmaf(e0, vr[j].w, o0.w);
+                    o1.x = fmaf(e1, vr[j].x, o1.x); o1.y = fmaf(e1, vr[j].y, o1.y); o1.z = fmaf(e1, vr[j].z, o1.z); o1.w = fmaf(e1, vr[j].w, o1.w);
+                }
+        }
+    }
+    /* warp records: [warp][head][max, sum, -, -, out[128]] */
+    float *r0 = wpart + (size_t)(warp * 2) * CL_REC, *r1 = r0 + CL_REC;
+    if (lane == 0) { r0[0] = m0; r0[1] = l0; r1[0] = m1; r1[1] = l1; }
+    *reinterpret_cast<float4 *>(r0 + 4 + lane * 4) = o0;
+    *reinterpret_cast<float4 *>(r1 + 4 + lane * 4) = o1;
+    __syncthreads();
+    if (tid < 256) {
+        const int hh = tid >> 7, d = tid & 127;
+        float M = -3.402823466e+38f;
+#pragma unroll
+        for (int k = 0; k < CL_WARPS; k++) M = fmaxf(M, wpart[(size_t)(k * 2 + hh) * CL_REC]);
+        float L = 0.0f, o = 0.0f;
+#pragma unroll
+        for (int k = 0; k < CL_WARPS; k++) {
+            const float *r = wpart + (size_t)(k * 2 + hh) * CL_REC;
+            const float f = r[1] > 0.0f ? __expf(r[0] - M) : 0.0f;
+            L = fmaf(r[1], f, L);
+            o = fmaf(r[4 + d], f, o);
+        }
+        float *c = cpart + hh * CL_REC;
+        c[4 + d] = o;
+        if (d == 0) { c[0] = M; c[1] = L; }
+    }
+}
+
+/* rank r of the cluster combines attention outputs [32 r, 32 r + 32) (head r / 4) over the 8 CTA partials and pushes the
+ * 32 final values into every peer's att[256].  Warp 0: lane = (quarter of the 32 dims, peer). */
+__device__ __forceinline__ void cl_attention_combine(cg::cluster_group &cl, int rank, float *cpart, float *att) {
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x, peer = lane & 7, quarter = lane >> 3, hh = rank >> 2, d0 = (rank & 3) * 32 + quarter * 8;
+    const float *rp = cl.map_shared_rank(cpart, peer) + hh * CL_REC;
+    const float m = rp[0], lsum = rp[1];
+    const float4 a0 = *reinterpret_cast<const float4 *>(rp + 4 + d0), a1 = *reinterpret_cast<const float4 *>(rp + 8 + d0);
+    float M = m;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+    const float f = lsum > 0.0f ? __expf(m - M) : 0.0f;
+    float L = lsum * f;
+    float v[8] = {a0.x * f, a0.y * f, a0.z * f, a0.w * f, a1.x * f, a1.y * f, a1.z * f, a1.w * f};
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        L += __shfl_xor_sync(0xffffffffu, L, o);
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
+    }
+    const float inv = 1.0f / L;
+    float *dst = cl.map_shared_rank(att, peer) + hh * 128 + d0;
+    *reinterpret_cast<float4 *>(dst) = make_float4(v[0] * inv, v[1] * inv, v[2] * inv, v[3] * inv);
+    *reinterpret_cast<float4 *>(dst + 4) = make_float4(v[4] * inv, v[5] * inv, v[6] * inv, v[7] * inv);
+}
+
+/* gate/up units [u0, u1) of this CTA: warp w takes u0 + w, u0 + w + 16, ...; the first pair of rows is already in `t` */
+__device__ __forceinline__ void cl_swiglu_run(const WTrip &t, const uint16_t *gate, const uint16_t *up, float *gs, int u0, int u1, int cols, const float *xs) {
+    const int lane = threadIdx.x & 31;
+    int u = u0 + (threadIdx.x >> 5);
+    if (u >= u1) return;
+    float va, vb;
+    trip_finish(t, gate + (size_t)u * cols, up + (size_t)u * cols, xs, cols, va, vb);
+    if (lane == 0) gs[u - u0] = swiglu_act<QTC_FAST>(va, vb);
+    for (u += CL_WARPS; u < u1; u += CL_WARPS) {
+        warp_dot2(gate + (size_t)u * cols, up + (size_t)u * cols, xs, cols, va, vb);
+        if (lane == 0) gs[u - u0] = swiglu_act<QTC_FAST>(va, vb);
+    }
+}
+
+/* dynamic shared memory (floats): [ xs | qkv 512 | att 256 | cpart 2 x 132 | wpart 16 x 2 x 132 | g 64 | dp H | kv stage 2 x 64 x 128 ] */
+__host__ __device__ inline int cl_smem_floats(int xs_floats, int H) {
+    return xs_floats + 512 + 256 + 2 * CL_REC + CL_WARPS * 2 * CL_REC + 64 + H + 2 * CL_ATT_CAP * 128;
+}
+
+__global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs a0, const SubProg sp) {
+    extern __shared__ __align__(128) float cl_smem[];
+    __shared__ float red[32];
+    __shared__ SampleSmem S_samp;
+    __shared__ int s_codes[QTC_MAX_GROUPS];
+    __shared__ uint32_t s_rng;
+    cg::cluster_group cl = cg::this_cluster();
+    const ClusterArgs &a = a0;                          /* stays in the constant bank: no copy, no registers */
+    const uint16_t *head_w = a0.head_w;
+    const LmDev &lm = *a.lm;
+    const int cta = blockIdx.x, ncta = gridDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int rank = (int)cl.block_rank(), g = cta / CL_SIZE;
+    const int H = lm.hidden, I = lm.inter, L = lm.layers;
+    const bool att_cluster = g < lm.kv_heads;           /* this cluster owns a KV head in phase A */
+    float *sm = cl_smem, *qkv = sm + a.xs_floats, *att = qkv + 512, *cpart = att + 256, *wpart = cpart + 2 * CL_REC;
+    float *gs = wpart + CL_WARPS * 2 * CL_REC, *dp = gs + 64, *kvs = dp + H;
+    const int pos_base = *a.pos_ptr + a.pos_add;
+    int p = *a.phase;                                   /* phase counter mod 3 */
+    unsigned long long target = 0;
+    if (tid == 0) { const unsigned long long v = ld_acquire_u64(a.bar); target = v - v % (unsigned long long)ncta; }
+    const int nsteps = sp.G > 0 ? sp.G : 1;
+    if (sp.G > 0 && tid == 0) s_codes[0] = sp.codes[0];
+    const int RPC = H / CL_SIZE;                        /* rows of x a CTA owns inside its cluster: 128 or 256 */
+    const int NCH = I / 8;                              /* 8-column chunks of the MLP's inner dimension, dealt out contiguously */
+    const int c0 = (int)(((unsigned)NCH * (unsigned)cta) / (unsigned)ncta), c1 = (int)(((unsigned)NCH * (unsigned)(cta + 1)) / (unsigned)ncta);
+    const int u0 = c0 * 8, u1 = c1 * 8, NC = c1 - c0;   /* gate/up units of this CTA; NC <= 8 */
+    const int zper = (H + ncta - 1) / ncta, z0 = cta * zper;
+    Seg3 s; int cols;
+    WTrip tp;
+    const int ja = 64 * rank + warp, jb = ja + CL_WARPS;   /* the warp's first pair of QKV rows; the second pair is +32 */
+    if (sp.G == 0 && att_cluster) cl_trip_issue(tp, cl_qkv_row(lm.layer[0], g, ja, H), cl_qkv_row(lm.layer[0], g, jb, H), H);
+
+#define PROF(i) do { if (a.prof && tid == 0 && l == a.prof_layer) a.prof[cta * 32 + (i)] = clock64(); } while (0)
+    for (int gstep = 0; gstep < nsteps; gstep++) {
+        const int pos = pos_base + gstep;
+        const int n = pos + 1, chunk = (n + CL_SIZE - 1) / CL_SIZE;
+        int t0 = rank * chunk, t1 = t0 + chunk < n ? t0 + chunk : n;
+        if (t0 > n) t0 = n;
+        if (t1 < t0) t1 = t0;
+        const bool staged = chunk <= CL_ATT_CAP;
+        if (sp.G > 0) {
+            /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x (fp32, like the step's input) */
+            __syncthreads();
+            if (gstep == 0) stage_vec(sm, sp.hidden, sp.Hin);
+            else {
+                const uint16_t *row = (gstep == 1 ? sp.emb0 : sp.emb[gstep - 2]) + (size_t)s_codes[gstep - 1] * sp.Hin;
+                for (int i = tid; i < sp.Hin; i += CL_THREADS) sm[i] = bf16_to_f32(row[i]);
+                __syncthreads();
+            }
+            if (sp.in_w) {
+                s.n = 1; s.w[0] = sp.in_w; s.out[0] = a.x; s.rows[0] = H; cols = sp.Hin;
+                cta_gemv(s, cols, sm, sp.in_b, cta, ncta);
+            } else if (cta == 0) {
+                for (int i = tid; i < H; i += CL_THREADS) a.x[i] = i < sp.Hin ? sm[i] : 0.0f;
+            }
+            head_w = gstep >= 1 ? sp.heads[gstep - 1] : NULL;
+            cl_barrier_arrive(a.bar, target, ncta);
+            if (att_cluster) cl_trip_issue(tp, cl_qkv_row(lm.layer[0], g, ja, H), cl_qkv_row(lm.layer[0], g, jb, H), H);
+            cl_barrier_wait(a.bar, target, a.err);
+        }
+        for (int l = 0; l < L; l++) {
+            const LmLayerDev &w = lm.layer[l];
+            long long *xin = a.xacc + (size_t)(p % 3) * H, *xmid = a.xacc + (size_t)((p + 1) % 3) * H, *xout = a.xacc + (size_t)((p + 2) % 3) * H;
+            /* ================= phase A: reads x (fp32 input at l == 0, else xin), adds the attention block's output into xmid, zeroes xout */
+            PROF(0);
+            if (tid < zper && z0 + tid < H) xout[z0 + tid] = 0;
+            if (att_cluster) {
+                if (staged && t1 > t0) {                /* K/V rows of earlier positions: on their way while the projections run */
+                    const int kvd = lm.kv_heads * 128;
+                    const float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
+                    const int rows = (t1 < pos ? t1 : pos) - t0;
+                    for (int i = tid; i < rows * 64; i += CL_THREADS) {
+                        const int which = i >= rows * 32, j = which ? i - rows * 32 : i, r = j >> 5, c = j & 31;
+                        const float *src = (which ? vc : kc) + kv_off(a.table, t0 + r, kvd) + c * 4;
+                        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(kvs + (size_t)which * CL_ATT_CAP * 128 + r * 128 + c * 4);
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src));
+                    }
+                }
+                asm volatile("cp.async.commit_group;");
+                cl_stage_norm(sm, l == 0 ? a.x : NULL, xin, w.in_norm, H, lm.eps, red);
+                PROF(1);
+                {
+                    float va, vb, vc2, vd;
+                    trip_finish(tp, cl_qkv_row(w, g, ja, H), cl_qkv_row(w, g, jb, H), sm, H, va, vb);
+                    warp_dot2(cl_qkv_row(w, g, ja + 32, H), cl_qkv_row(w, g, jb + 32, H), sm, H, vc2, vd);
+                    if (lane < CL_SIZE) { float *peer = cl.map_shared_rank(qkv, lane); peer[ja] = va; peer[jb] = vb; peer[ja + 32] = vc2; peer[jb + 32] = vd; }
+                }
+                PROF(2);
+                asm volatile("cp.async.wait_all;" ::: "memory");
+                cl.sync();
+                PROF(3);
+                cl_attention(a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs);
+                /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
+                const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
+                uint4 ow[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(warp + CL_WARPS * i) * 256) + lane);
+                PROF(4);
+                cl.sync();
+                PROF(5);
+                cl_attention_combine(cl, rank, cpart, att);
+                cl.sync();
+                PROF(6);
+                const float4 a0v = reinterpret_cast<const float4 *>(att)[2 * lane], a1v = reinterpret_cast<const float4 *>(att)[2 * lane + 1];
+                for (int rb = 0; rb < RPC; rb += 8 * CL_WARPS) {           /* RPC = 128: one pass; 256: two */
+                    long long resid = 0;
+                    if (g == 0 && lane < 8) {
+                        const int row = rank * RPC + rb + warp + CL_WARPS * lane;
+                        resid = l == 0 ? to_fx(__ldcg(a.x + row)) : __ldcg(xin + row);
+                    }
+                    if (rb > 0) {
+#pragma unroll
+                        for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(rb + warp + CL_WARPS * i) * 256) + lane);
+                    }
+                    float acc[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) acc[i] = dot8f(ow[i], a0v, a1v, 0.0f);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        float t8[8];
+#pragma unroll
+                        for (int i = 0; i < 8; i++) t8[i] = __shfl_xor_sync(0xffffffffu, acc[i], o);
+#pragma unroll
+                        for (int i = 0; i < 8; i++) acc[i] += t8[i];
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; i++)
+                        if (lane == i) red_add_s64(xmid + rank * RPC + rb + warp + CL_WARPS * i, to_fx(acc[i]) + resid);
+                }
+            }
+            PROF(7);
+            cl_barrier_arrive(a.bar, target, ncta);
+            cl_trip_issue(tp, w.gate + (size_t)(u0 + warp) * H, w.up + (size_t)(u0 + warp) * H, H);      /* every warp has a first unit: >= 16 per CTA */
+            cl_barrier_wait(a.bar, target, a.err);
+            p++;
+            PROF(8);
+            /* ================= phase B: reads xmid, adds the MLP's output into xout, zeroes xin */
+            if (tid < zper && z0 + tid < H) xin[z0 + tid] = 0;
+            cl_stage_norm(sm, NULL, xmid, w.post_norm, H, lm.eps, red);
+            PROF(9);
+            cl_swiglu_run(tp, w.gate, w.up, gs, u0, u1, H, sm);
+            __syncthreads();
+            PROF(10);
+            {
+                /* down partial: dp[r] = sum over this CTA's columns; pieces (chunk c, row r) are 16 bytes at (c H + r) */
+                const uint4 *dw = reinterpret_cast<const uint4 *>(w.down_t) + (size_t)c0 * H;
+                for (int r = tid; r < H; r += 2 * CL_THREADS) {
+                    const int r2 = r + CL_THREADS;
+                    float sa = 0.0f, sb = 0.0f;
+                    for (int cb = 0; cb < NC; cb += 4) {
+                        uint4 wa[4], wb[4];
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            wa[c] = cb + c < NC ? ldg_stream(dw + (size_t)(cb + c) * H + r) : make_uint4(0, 0, 0, 0);
+                            wb[c] = cb + c < NC && r2 < H ? ldg_stream(dw + (size_t)(cb + c) * H + r2) : make_uint4(0, 0, 0, 0);
+                        }
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            if (cb + c < NC) {
+                                const float4 g0 = reinterpret_cast<const float4 *>(gs)[2 * (cb + c)], g1 = reinterpret_cast<const float4 *>(gs)[2 * (cb + c) + 1];
+                                sa = dot8f(wa[c], g0, g1, sa);
+                                sb = dot8f(wb[c], g0, g1, sb);
+                            }
+                    }
+                    dp[r] = sa;
+                    if (r2 < H) dp[r2] = sb;
+                }
+            }
+            PROF(11);
+            cl.sync();
+            PROF(12);
+            {
+                /* rank r folds rows [r RPC, (r+1) RPC) over the 8 peers: lane group of 8 = the peers, fixed butterfly order */
+                const int peer = tid & 7, grp = tid >> 3;
+                if (grp < RPC / 4) {
+                    const int row = rank * RPC + 4 * grp;
+                    float4 v = *reinterpret_cast<const float4 *>(cl.map_shared_rank(dp, peer) + row);
+#pragma unroll
+                    for (int o = 4; o > 0; o >>= 1) {
+                        v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+                        v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+                    }
+                    if (peer < 4) {
+                        const float mine = peer == 0 ? v.x : peer == 1 ? v.y : peer == 2 ? v.z : v.w;
+                        long long fx = to_fx(mine);
+                        if (g == 0) fx += __ldcg(xmid + row + peer);
+                        red_add_s64(xout + row + peer, fx);
+                    }
+                }
+            }
+            PROF(13);
+            cl_barrier_arrive(a.bar, target, ncta);
+            if (l + 1 < L && att_cluster) cl_trip_issue(tp, cl_qkv_row(lm.layer[l + 1], g, ja, H), cl_qkv_row(lm.layer[l + 1], g, jb, H), H);
+            cl_barrier_wait(a.bar, target, a.err);
+            p++;
+            PROF(14);
+        }
+        /* final norm of the stack's output (buf[p % 3]) into shared memory; talker: CTA 0 publishes it as the hidden state */
+        if (sp.G == 0 || head_w) cl_stage_norm(sm, NULL, a.xacc + (size_t)(p % 3) * H, lm.final_norm, H, lm.eps, red);
+        if (sp.G == 0 && cta == 0) {
+            for (int i = tid; i < H; i += CL_THREADS) a.x[i] = sm[i];
+            if (tid == 0 && a.st && !a.st->done) a.st->pos += 1;
+        }
+        if (head_w) {
+            s.n = 1; s.w[0] = head_w; s.out[0] = a.logits; s.rows[0] = sp.G > 0 ? sp.vocab : a.head_rows; cols = H;
+            cta_gemv(s, cols, sm, NULL, cta, ncta);
+        }
+        if (sp.G > 0 && gstep >= 1) {
+            cl_barrier_arrive(a.bar, target, ncta);
+            cl_barrier_wait(a.bar, target, a.err);
+            const int V = sp.vocab;
+            float *lg = sm, *vv = sm + V;
+            for (int i = tid; i < V; i += CL_THREADS) lg[i] = __ldcg(a.logits + i);
+            if (gstep == 1 && tid == 0) s_rng = sp.seed_bits;
+            __syncthreads();
+            const int tok = block_sample(lg, vv, V, sp.cfg.top_k, sp.cfg.top_p, sp.cfg.temperature, &s_rng, S_samp, sp.scratch_f, sp.scratch_i);
+            if (tid == 0) { s_codes[gstep] = tok; if (cta == 0) sp.codes[gstep] = tok; }
+        }
+    }
+#undef PROF
+    if (cta == 0 && tid == 0) *a.phase = p % 3;
+}

@@ -53,6 +53,9 @@ static inline cudaError_t qtc_launch_pdl(cudaStream_t st, void (*k)(KArgs...), d
 struct LmLayerDev {
     const uint16_t *wq, *wk, *wv, *wo, *gate, *up, *down;   /* bf16, row-major as in the reference */
     const float *q_norm, *k_norm, *in_norm, *post_norm;
+    /* mode 2 (qtc_cluster.cuh), built at upload when the geometry fits: wo_t [kv_heads][H][256] = the O projection's columns
+     * of one KV group made contiguous; down_t [I/8][H][8] = the down projection in 16-byte pieces, column chunk major */
+    const uint16_t *wo_t, *down_t;
 };
 struct LmDev {
     int vocab, hidden, inter, layers, heads, kv_heads, head_dim;
@@ -103,6 +106,8 @@ struct LmBuffers {
     int kv_max;
     float *cos, *sin;             /* [kv_max, head_dim], host-computed with the oracle's expression */
     float *x, *xn, *q, *kk, *vv, *att, *g, *logits;
+    long long *xacc;              /* mode 2: [3][H] fixed-point residual accumulators (zero at upload) */
+    int *cl_phase;                /* mode 2: which accumulator is current (device int, carried across launches) */
 };
 
 struct CodecDev;   /* qtc_codec.cu */
@@ -156,7 +161,9 @@ struct qtc_ctx {
     PfBuf *pf;
     qtc_gen_params_t params;
     qtc_perf_t perf;
-    int mode;                     /* 0 per-op kernels, 1 fused persistent kernels (default) */
+    int mode;                     /* 0 per-op kernels, 1 fused persistent kernel (148 CTAs, 5 exchanges per layer), 2 cluster kernel (default where it fits) */
+    int cluster_ok;               /* 8 clusters of 16 CTAs can be co-resident on this device */
+    int *cl_err;                  /* device flag: a mode-2 barrier wait gave up */
     int arith;                    /* QTC_FAST / QTC_STRICT */
     cudaStream_t stream;
     cudaStream_t cstream;         /* stream the codec kernels are enqueued on: == stream, or stream2 while a generate overlaps decode and frame loop */
@@ -195,6 +202,7 @@ int qtc_prefill_gemm(qtc_ctx *c, const float *embeds_dev, int seq_len, int base)
 bool qtc_prefill_gemm_ok(const qtc_ctx *c);
 void qtc_prefill_release(qtc_ctx *c);
 int qtc_kv_pool_init(qtc_ctx *c, int max_batch);
+int qtc_cluster_prepare(qtc_ctx *c, LmDev *d);      /* mode 2 weight layouts (qtc_lm.cu); 0 also when the geometry does not fit */
 int qtc_kv_reserve(qtc_ctx *c, int slot, int positions);      /* the slot holds pages for at least `positions` positions */
 void qtc_kv_release_all(qtc_ctx *c);
 #define QTC_COUNT_MALLOC(c) ((c)->dev_mallocs++)

@@ -8,6 +8,7 @@
  * captured into a CUDA graph and replayed.
  */
 #include "qtc_fused_main.cuh"
+#include "qtc_cluster.cuh"
 #include "qtc_gemv.cuh"
 #include "qtc_internal.h"
 #include "qtc_lm_kernels.cuh"
@@ -188,6 +189,127 @@ int qtc_ensure_kv(qtc_ctx *c, LmBuffers *b, const LmDev *lm, int need) {
     return 0;
 }
 
+
+/* ---- mode 2: the cluster kernel (qtc_cluster.cuh) ------------------------------------------------------------------ */
+#define CL_MAX_CLUSTERS 15            /* 8-CTA clusters a B200 holds at one CTA per SM (scripts/probe/cluster_capacity.cu) */
+static bool cluster_geometry(const LmDev *lm) {
+    return lm->head_dim == 128 && lm->kv_heads > 0 && lm->kv_heads <= CL_MAX_CLUSTERS && lm->heads == 2 * lm->kv_heads &&
+           lm->hidden % 1024 == 0 && lm->hidden <= 2048 && lm->inter % 8 == 0 && lm->inter / 8 >= 2 * CL_MAX_CLUSTERS * CL_SIZE &&
+           lm->inter / 8 <= 8 * CL_MAX_CLUSTERS * CL_SIZE && lm->layers > 0;
+}
+__global__ void k_relayout_wo(uint16_t *dst, const uint16_t *wo, int H, int qd) {            /* dst[g][r][c] = wo[r][256 g + c] */
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)H * qd) return;
+    const int c = (int)(i % 256), r = (int)((i / 256) % H), g = (int)(i / ((size_t)256 * H));
+    dst[i] = wo[(size_t)r * qd + g * 256 + c];
+}
+__global__ void k_relayout_down(uint16_t *dst, const uint16_t *down, int H, int I) {         /* dst[c8][r][j] = down[r][8 c8 + j] */
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)H * I) return;
+    const int j = (int)(i % 8), r = (int)((i / 8) % H), c8 = (int)(i / ((size_t)8 * H));
+    dst[i] = down[(size_t)r * I + c8 * 8 + j];
+}
+int qtc_cluster_prepare(qtc_ctx *c, LmDev *d) {
+    for (int l = 0; l < d->layers; l++) { d->layer[l].wo_t = NULL; d->layer[l].down_t = NULL; }
+    if (!cluster_geometry(d)) return 0;
+    const size_t H = d->hidden, qd = (size_t)d->heads * d->head_dim, I = d->inter;
+    for (int l = 0; l < d->layers; l++) {
+        uint16_t *wo_t = (uint16_t *)qtc_dmalloc(c, H * qd * 2), *down_t = (uint16_t *)qtc_dmalloc(c, H * I * 2);
+        if (!wo_t || !down_t) return -1;
+        k_relayout_wo<<<(unsigned)((H * qd + 255) / 256), 256>>>(wo_t, d->layer[l].wo, (int)H, (int)qd);
+        k_relayout_down<<<(unsigned)((H * I + 255) / 256), 256>>>(down_t, d->layer[l].down, (int)H, (int)I);
+        QTC_CUDA(cudaGetLastError());
+        d->layer[l].wo_t = wo_t; d->layer[l].down_t = down_t;
+    }
+    QTC_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+static int g_cluster_attr = 0, g_cluster_max_smem = 0, g_cluster_fit = -1;
+static int cluster_setup(qtc_ctx *c) {
+    if (g_cluster_attr) return 0;
+    cudaFuncAttributes fa;
+    QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_cluster));
+    g_cluster_max_smem = 227 * 1024 - (int)fa.sharedSizeBytes;
+    QTC_CUDA(cudaFuncSetAttribute(k_lm_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, g_cluster_max_smem));
+    QTC_CUDA(cudaFuncSetAttribute(k_lm_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    /* how many 8-CTA clusters the device holds at once (B200, one CTA per SM: 15) */
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CL_MAX_CLUSTERS * CL_SIZE); cfg.blockDim = dim3(CL_THREADS); cfg.dynamicSmemBytes = (size_t)cl_smem_floats(4096, 2048) * 4;
+    cudaLaunchAttribute at[1];
+    memset(at, 0, sizeof(at));
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = CL_SIZE; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int ncl = 0;
+    if (cudaOccupancyMaxActiveClusters(&ncl, k_lm_cluster, &cfg) != cudaSuccess) { cudaGetLastError(); ncl = 0; }
+    g_cluster_fit = ncl;
+    { const char *e = getenv("QTC_CLUSTERS"); if (e && atoi(e) > 0 && atoi(e) < g_cluster_fit) g_cluster_fit = atoi(e); }   /* experiment: fewer clusters */
+    g_cluster_attr = 1;
+    (void)c;
+    return 0;
+}
+static bool cluster_fits(qtc_ctx *c, const LmDev *lm) {
+    if (c->mode < 2 || c->arith != QTC_FAST || !cluster_geometry(lm) || !lm->layer[0].wo_t) return false;
+    if (cluster_setup(c)) return false;
+    /* clusters needed: one per KV head in phase A, and at most 8 chunks of the MLP's inner dimension per CTA in phase B */
+    const int need = (lm->inter / 8 + 8 * CL_SIZE - 1) / (8 * CL_SIZE);
+    return g_cluster_fit >= lm->kv_heads && g_cluster_fit >= need;
+}
+/* debug: how many 16-CTA clusters fit the device (-1 before the first mode-2 step) and whether a mode-2 barrier wait ever gave up */
+extern "C" int qwen_tts_cuda_cluster_status(qtc_ctx_t *c, int *capacity, int *gave_up) {
+    if (!c) return -1;
+    if (capacity) *capacity = g_cluster_fit;
+    int e = 0;
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->cl_err) QTC_CUDA(cudaMemcpy(&e, c->cl_err, 4, cudaMemcpyDeviceToHost));
+    if (gave_up) *gave_up = e;
+    return 0;
+}
+static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
+                        const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog) {
+    ClusterArgs a;
+    memset(&a, 0, sizeof(a));
+    a.lm = lm == &c->talker ? c->talker_dev : c->sub_dev;
+    a.x = b->x; a.xacc = b->xacc; a.phase = b->cl_phase;
+    a.kc = b->k; a.vc = b->v; a.table = b->table; a.cos = b->cos; a.sin = b->sin; a.kv_max = b->kv_max;
+    a.pos_ptr = pos_ptr; a.pos_add = pos_add;
+    a.head_w = head_w; a.head_rows = head_rows; a.logits = logits;
+    a.bar = c->bar + 4;                              /* its own counter: this grid has 120 CTAs, k_lm_fused 148 */
+    a.st = st; a.err = c->cl_err;
+    a.prof = (c->prof_sub ? lm == &c->sub : lm == &c->talker) ? c->prof : NULL; a.prof_layer = c->prof_layer;
+    { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
+    int vec = lm->hidden;
+    SubProg sp;
+    memset(&sp, 0, sizeof(sp));
+    if (prog) {
+        sp = *prog;
+        if (2 * sp.vocab > vec) vec = 2 * sp.vocab;
+        if (sp.Hin > vec) vec = sp.Hin;
+    }
+    a.xs_floats = (vec + 31) & ~31;
+    const size_t smem = (size_t)cl_smem_floats(a.xs_floats, lm->hidden) * 4;
+    if (smem > (size_t)g_cluster_max_smem) { qtc_set_error("cluster step: %zu bytes of shared memory needed, %d available", smem, g_cluster_max_smem); return -1; }
+    cudaLaunchConfig_t cfg = {};
+    const int ncl = g_cluster_fit < CL_MAX_CLUSTERS ? g_cluster_fit : CL_MAX_CLUSTERS;
+    cfg.gridDim = dim3(ncl * CL_SIZE); cfg.blockDim = dim3(CL_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
+    cudaLaunchAttribute at[2];
+    memset(at, 0, sizeof(at));
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = CL_SIZE; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
+    /* cooperative as well where the driver takes both attributes (co-residency then is checked, not assumed); the grid is
+     * 128 CTAs at one per SM on an otherwise idle stream-ordered device either way */
+    static int coop = 1;
+    cfg.attrs = at; cfg.numAttrs = coop ? 2 : 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_lm_cluster, a, sp);
+    if (e != cudaSuccess && coop) {
+        cudaGetLastError();
+        coop = 0; cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, k_lm_cluster, a, sp);
+    }
+    if (e != cudaSuccess) { qtc_set_error("cluster step launch -> %s", cudaGetErrorString(e)); return -1; }
+    c->launches++;
+    return 0;
+}
+
 /* mode 1: the whole step (+ optional head GEMV, + pos bump) as one persistent cooperative kernel */
 static int g_fused_attr = 0, g_fused_max_smem = 0;
 static bool fused_ok(const qtc_ctx *c, const LmDev *lm) {
@@ -197,6 +319,7 @@ static bool fused_ok(const qtc_ctx *c, const LmDev *lm) {
 }
 static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_ptr, int pos_add,
                       const uint16_t *head_w, int head_rows, float *logits, GenState *st, const SubProg *prog = NULL) {
+    if (cluster_fits(c, lm)) return cluster_step(c, lm, b, pos_ptr, pos_add, head_w, head_rows, logits, st, prog);
     if (!g_fused_attr) {
         cudaFuncAttributes fa;
         QTC_CUDA(cudaFuncGetAttributes(&fa, k_lm_fused));
@@ -234,7 +357,10 @@ static int fused_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *pos_
     const size_t smem = (size_t)(a.xs_floats + a.att_floats + 2 * ATT_STAGE_MAX * lm->head_dim) * 4;
     if (smem > (size_t)g_fused_max_smem) { qtc_set_error("fused step: %zu bytes of shared memory needed, %d available", smem, g_fused_max_smem); return -1; }
     void *args[] = {&a, &sp};
-    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(c->num_sms), dim3(FUSED_BLOCK), args, smem, c->stream));
+    static int grid_env = -1;            /* experiment: QTC_FUSED_CTAS = CTAs of the mode-1 grid (default: one per SM) */
+    if (grid_env < 0) { const char *e = getenv("QTC_FUSED_CTAS"); grid_env = e ? atoi(e) : 0; }
+    const int grid = grid_env > 0 && grid_env <= c->num_sms ? grid_env : c->num_sms;
+    QTC_CUDA(cudaLaunchCooperativeKernel((void *)k_lm_fused, dim3(grid), dim3(FUSED_BLOCK), args, smem, c->stream));
     c->launches++;
     return 0;
 }
