@@ -407,7 +407,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="1.7b", choices=list(mg.PRESETS))
     ap.add_argument("--frames", type=int, default=FRAMES)
-    ap.add_argument("--mode", type=int, default=1, help="1: fused persistent decode kernels (default); 0: one kernel per op")
+    ap.add_argument("--mode", type=int, default=2, help="2: cluster kernel, two grid-wide exchanges per layer (default); 1: 148-CTA fused kernel, five; 0: one kernel per op")
     ap.add_argument("--strict", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
     ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")

@@ -32,9 +32,19 @@
 namespace cg = cooperative_groups;
 
 #define CL_SIZE 8
+/* build-time variants for A/B measurements (scripts/probe): each defaults to the measured-best setting */
+#ifndef CL_NW_LOOP
+#define CL_NW_LOOP 1          /* fold only the warps that had a position */
+#endif
+#ifndef CL_PIPE
+#define CL_PIPE 1             /* second QKV pair and second O batch requested before the first is reduced */
+#endif
+#ifndef CL_STAGE_AUX
+#define CL_STAGE_AUX 1        /* RoPE row, head norms, layer norms staged to shared memory across the grid barriers */
+#endif
 #define CL_THREADS 512
 #define CL_WARPS 16
-#define CL_ATT_CAP 64                 /* staged positions per CTA (contexts up to 8 x 64 = 512; longer ones read K/V through L2) */
+#define CL_ATT_CAP 64                 /* most positions per CTA the shared-memory K/V stage is sized for (contexts up to 8 x 64 = 512; longer ones read K/V through L2) */
 #define CL_REC 132                    /* partial record: max, sum, -, -, out[128] */
 #define CL_FX 4294967296.0f           /* 2^32 */
 #define CL_FX_INV 2.3283064365386963e-10f
@@ -50,9 +60,11 @@ struct ClusterArgs {
     unsigned long long *bar;
     GenState *st;
     int xs_floats;                     /* staged-vector / sampler region */
+    int att_cap;                       /* positions per CTA the K/V stage holds (<= CL_ATT_CAP): shared memory is sized by it, and the less of it, the more L1 */
     int flags;
     long long *prof; int prof_layer;
     int *err;                          /* set to 1 if a barrier wait gave up */
+    int pf_frac, pf_gap;               /* idle-cluster L2 prefetch of the MLP weights: percent of every consumer's slice, and nanoseconds between a warp's requests */
 };
 
 __device__ __forceinline__ void red_add_s64(long long *p, long long v) {
@@ -76,25 +88,31 @@ __device__ __forceinline__ void cl_barrier_arrive(unsigned long long *bar, unsig
     if (threadIdx.x == 0) { target += nb; red_release_inc(bar); }
 }
 
-/* xs = rmsnorm(x) * w for H <= 4096; x comes as fp32 (the step's input) or from a fixed-point accumulator */
-__device__ __forceinline__ void cl_stage_norm(float *xs, const float *xf, const long long *xq, const float *w, int n, float eps, float *red) {
+/* xs = rmsnorm(x) * w for H <= 4096; x comes as fp32 (the step's input) or from a fixed-point accumulator.  In two halves so
+ * that independent work (the K/V staging copies) can be issued while the loads are in flight. */
+struct XRegs { float4 v0, v1, w0, w1; };
+__device__ __forceinline__ void cl_x_load(XRegs &x, const float *xf, const long long *xq, const float *w, int n) {
     const int i0 = threadIdx.x * 4, i1 = i0 + CL_THREADS * 4;
-    float4 v0 = make_float4(0, 0, 0, 0), v1 = v0, w0 = v0, w1 = v0;
+    x.v0 = make_float4(0, 0, 0, 0); x.v1 = x.v0; x.w0 = x.v0; x.w1 = x.v0;
     if (xf) {
-        if (i0 < n) v0 = __ldcg(reinterpret_cast<const float4 *>(xf + i0));
-        if (i1 < n) v1 = __ldcg(reinterpret_cast<const float4 *>(xf + i1));
+        if (i0 < n) x.v0 = __ldcg(reinterpret_cast<const float4 *>(xf + i0));
+        if (i1 < n) x.v1 = __ldcg(reinterpret_cast<const float4 *>(xf + i1));
     } else {
         if (i0 < n) {
             const longlong2 a = __ldcg(reinterpret_cast<const longlong2 *>(xq + i0)), b = __ldcg(reinterpret_cast<const longlong2 *>(xq + i0 + 2));
-            v0 = make_float4(from_fx(a.x), from_fx(a.y), from_fx(b.x), from_fx(b.y));
+            x.v0 = make_float4(from_fx(a.x), from_fx(a.y), from_fx(b.x), from_fx(b.y));
         }
         if (i1 < n) {
             const longlong2 a = __ldcg(reinterpret_cast<const longlong2 *>(xq + i1)), b = __ldcg(reinterpret_cast<const longlong2 *>(xq + i1 + 2));
-            v1 = make_float4(from_fx(a.x), from_fx(a.y), from_fx(b.x), from_fx(b.y));
+            x.v1 = make_float4(from_fx(a.x), from_fx(a.y), from_fx(b.x), from_fx(b.y));
         }
     }
-    if (i0 < n) w0 = *reinterpret_cast<const float4 *>(w + i0);
-    if (i1 < n) w1 = *reinterpret_cast<const float4 *>(w + i1);
+    if (i0 < n) x.w0 = *reinterpret_cast<const float4 *>(w + i0);
+    if (i1 < n) x.w1 = *reinterpret_cast<const float4 *>(w + i1);
+}
+__device__ __forceinline__ void cl_norm_finish(float *xs, const XRegs &x, int n, float eps, float *red) {
+    const int i0 = threadIdx.x * 4, i1 = i0 + CL_THREADS * 4;
+    const float4 v0 = x.v0, v1 = x.v1, w0 = x.w0, w1 = x.w1;
     float ss = v0.x * v0.x;
     ss = fmaf(v0.y, v0.y, ss); ss = fmaf(v0.z, v0.z, ss); ss = fmaf(v0.w, v0.w, ss);
     ss = fmaf(v1.x, v1.x, ss); ss = fmaf(v1.y, v1.y, ss); ss = fmaf(v1.z, v1.z, ss); ss = fmaf(v1.w, v1.w, ss);
@@ -104,18 +122,70 @@ __device__ __forceinline__ void cl_stage_norm(float *xs, const float *xf, const 
     if (i1 < n) *reinterpret_cast<float4 *>(xs + i1) = make_float4(v1.x * inv * w1.x, v1.y * inv * w1.y, v1.z * inv * w1.z, v1.w * inv * w1.w);
     __syncthreads();
 }
+__device__ __forceinline__ void cl_stage_norm(float *xs, const float *xf, const long long *xq, const float *w, int n, float eps, float *red) {
+    XRegs x;
+    cl_x_load(x, xf, xq, w, n);
+    cl_norm_finish(xs, x, n, eps, red);
+}
 
-/* trip_issue of qtc_fused_main.cuh with every register written on every call: a conditionally written WTrip stays live around
- * the whole layer loop (the old value might survive) and ptxas then parks it in local memory - measured: 70 STL right after the loads */
-__device__ __forceinline__ void cl_trip_issue(WTrip &t, const uint16_t *ra, const uint16_t *rb, int cols) {
-    const int lane = threadIdx.x & 31, n8 = cols >> 3;
-    const uint4 *w0 = reinterpret_cast<const uint4 *>(ra), *w1 = reinterpret_cast<const uint4 *>(rb);
+/* ---- weight streaming in register stages ------------------------------------------------------------------------------------
+ * A Stage holds 1024 columns of two rows: lane's 16-byte pieces lane + 32 j, j < 4, of each row = 8 loads.  Two stages are kept in
+ * flight per warp: while one is multiplied out the other's loads (and the next one's, issued right after the multiply) are under
+ * way, so a phase is a continuous stream of requests instead of load - wait - multiply round trips; the first two stages of a phase
+ * are issued BEFORE the grid barrier in front of it.  Every register of a stage is written on every issue (zeros where there is
+ * nothing to load): a conditionally written stage would stay live around the whole layer loop and be spilled. */
+struct Stage { uint4 a[4], b[4]; };
+__device__ __forceinline__ void st_issue(Stage &s, const uint16_t *ra, const uint16_t *rb, int half) {
+    const uint4 *w0 = reinterpret_cast<const uint4 *>(ra) + half * 128 + (threadIdx.x & 31), *w1 = reinterpret_cast<const uint4 *>(rb) + half * 128 + (threadIdx.x & 31);
 #pragma unroll
-    for (int j = 0; j < PFJ; j++) {
-        const int p = lane + 32 * j;
-        if (p < n8) { t.a[j] = ldg_stream(w0 + p); t.b[j] = ldg_stream(w1 + p); }
-        else { t.a[j] = make_uint4(0, 0, 0, 0); t.b[j] = make_uint4(0, 0, 0, 0); }
+    for (int j = 0; j < 4; j++) { s.a[j] = ldg_stream(w0 + 32 * j); s.b[j] = ldg_stream(w1 + 32 * j); }
+}
+__device__ __forceinline__ void st_zero(Stage &s) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) { s.a[j] = make_uint4(0, 0, 0, 0); s.b[j] = make_uint4(0, 0, 0, 0); }
+}
+__device__ __forceinline__ void st_consume(const Stage &s, const float *xs, int half, float &a, float &b) {
+    const float4 *x4 = reinterpret_cast<const float4 *>(xs) + 2 * (half * 128 + (threadIdx.x & 31));
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const float4 x0 = x4[64 * j], x1 = x4[64 * j + 1];
+        a = dot8f(s.a[j], x0, x1, a);
+        b = dot8f(s.b[j], x0, x1, b);
     }
+}
+__device__ __forceinline__ void warp_sum2(float &a, float &b) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ta = __shfl_xor_sync(0xffffffffu, a, o), tb = __shfl_xor_sync(0xffffffffu, b, o);
+        a += ta; b += tb;
+    }
+}
+/* npairs row pairs of HS x 1024 columns each, streamed through (s0, s1).  On entry s0 holds stage 0 and s1 stage 1 (a stage = one
+ * pair at HS == 1, half a pair at HS == 2).  rows(k, ra, rb): the k-th pair's row pointers; out(k, a, b): its two dot products. */
+template <class RowFn, class OutFn>
+__device__ __forceinline__ void cl_stream(Stage &s0, Stage &s1, int npairs, int HS, const float *xs, RowFn rows, OutFn out) {
+    const int nst = npairs * HS;
+    float a = 0.0f, b = 0.0f;
+    const uint16_t *ra, *rb;
+    for (int i = 0; i < nst; i += 2) {
+        st_consume(s0, xs, 0, a, b);
+        if (HS == 1) { warp_sum2(a, b); out(i, a, b); a = 0.0f; b = 0.0f; }
+        if (i + 2 < nst) { rows(HS == 2 ? (i + 2) >> 1 : i + 2, ra, rb); st_issue(s0, ra, rb, 0); }
+        if (i + 1 < nst) {
+            st_consume(s1, xs, HS == 2 ? 1 : 0, a, b);
+            warp_sum2(a, b);
+            out(HS == 2 ? i >> 1 : i + 1, a, b);
+            a = 0.0f; b = 0.0f;
+            if (i + 3 < nst) { rows(HS == 2 ? (i + 3) >> 1 : i + 3, ra, rb); st_issue(s1, ra, rb, HS == 2 ? 1 : 0); }
+        }
+    }
+}
+/* stages 0 and 1 of such a stream (issued ahead of a barrier) */
+template <class RowFn>
+__device__ __forceinline__ void cl_stream_prefetch(Stage &s0, Stage &s1, int npairs, int HS, RowFn rows) {
+    const uint16_t *ra, *rb;
+    if (npairs > 0) { rows(0, ra, rb); st_issue(s0, ra, rb, 0); } else st_zero(s0);
+    if (npairs * HS > 1) { rows(HS == 2 ? 0 : 1, ra, rb); st_issue(s1, ra, rb, HS == 2 ? 1 : 0); } else st_zero(s1);
 }
 
 /* row j (0..511) of cluster g's QKV block: [q head 2g | q head 2g+1 | k head g | v head g] */
@@ -148,26 +218,28 @@ __device__ __forceinline__ float dot4(const float4 a, const float4 b) {
 /* Attention of cluster g at position pos: positions [t0, t1) of this CTA, both query heads per K/V row.
  * qkv: this CTA's copy of the cluster's 512 projection outputs.  Leaves the CTA's partial records in cpart[2][CL_REC]. */
 __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int t0, int t1, bool staged,
-                                             const float *qkv, float *wpart, float *cpart, const float *kvs) {
+                                             const float *qkv, float *wpart, float *cpart, const float *kvs, const float *aux) {
+    const int cap = a.att_cap;
+    /* aux (staged with the K/V rows): [cos row | sin row | q_norm | k_norm], 128 floats each */
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, kvd = lm.kv_heads * 128;
-    const LmLayerDev &w = lm.layer[l];
+    const float *q_norm = aux + 256, *k_norm = aux + 384;
     float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
-    const float4 c4 = reinterpret_cast<const float4 *>(a.cos + (size_t)pos * 128)[lane], s4 = reinterpret_cast<const float4 *>(a.sin + (size_t)pos * 128)[lane];
+    const float4 c4 = reinterpret_cast<const float4 *>(aux)[lane], s4 = reinterpret_cast<const float4 *>(aux + 128)[lane];
     const bool mine = warp < t1 - t0;                                  /* this warp has at least one position */
     const bool has_new = t1 == pos + 1 && pos >= t0 && ((pos - t0) % CL_WARPS) == warp;
     float m0 = -3.402823466e+38f, m1 = m0, l0 = 0.0f, l1 = 0.0f;
     float4 o0 = make_float4(0, 0, 0, 0), o1 = o0;
     if (mine) {
-        const float4 q0 = cl_norm_rope(qkv, w.q_norm, c4, s4, lm.eps), q1 = cl_norm_rope(qkv + 128, w.q_norm, c4, s4, lm.eps);
+        const float4 q0 = cl_norm_rope(qkv, q_norm, c4, s4, lm.eps), q1 = cl_norm_rope(qkv + 128, q_norm, c4, s4, lm.eps);
         float4 k_new = make_float4(0, 0, 0, 0), v_new = k_new;
         if (has_new) {
-            k_new = cl_norm_rope(qkv + 256, w.k_norm, c4, s4, lm.eps);
+            k_new = cl_norm_rope(qkv + 256, k_norm, c4, s4, lm.eps);
             v_new = reinterpret_cast<const float4 *>(qkv + 384)[lane];
             const size_t off = kv_off(a.table, pos, kvd);
             *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
             *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
         }
-        const float *Ks = kvs, *Vs = kvs + CL_ATT_CAP * 128;
+        const float *Ks = kvs, *Vs = kvs + cap * 128;
         const float scale = 0.08838834764831845f;                      /* 1 / sqrt(128) */
         for (int tb = t0 + warp; tb < t1; tb += 4 * CL_WARPS) {
             float d0[4], d1[4];
@@ -216,20 +288,26 @@ __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &
                 }
         }
     }
-    /* warp records: [warp][head][max, sum, -, -, out[128]] */
-    float *r0 = wpart + (size_t)(warp * 2) * CL_REC, *r1 = r0 + CL_REC;
-    if (lane == 0) { r0[0] = m0; r0[1] = l0; r1[0] = m1; r1[1] = l1; }
-    *reinterpret_cast<float4 *>(r0 + 4 + lane * 4) = o0;
-    *reinterpret_cast<float4 *>(r1 + 4 + lane * 4) = o1;
+    /* warp records: [warp][head][max, sum, -, -, out[128]]; only warps that had a position write and are folded */
+#if CL_NW_LOOP
+    const int nw = t1 - t0 < CL_WARPS ? t1 - t0 : CL_WARPS;
+    if (mine) {
+#else
+    const int nw = CL_WARPS;
+    {
+#endif
+        float *r0 = wpart + (size_t)(warp * 2) * CL_REC, *r1 = r0 + CL_REC;
+        if (lane == 0) { r0[0] = m0; r0[1] = l0; r1[0] = m1; r1[1] = l1; }
+        *reinterpret_cast<float4 *>(r0 + 4 + lane * 4) = o0;
+        *reinterpret_cast<float4 *>(r1 + 4 + lane * 4) = o1;
+    }
     __syncthreads();
     if (tid < 256) {
         const int hh = tid >> 7, d = tid & 127;
         float M = -3.402823466e+38f;
-#pragma unroll
-        for (int k = 0; k < CL_WARPS; k++) M = fmaxf(M, wpart[(size_t)(k * 2 + hh) * CL_REC]);
+        for (int k = 0; k < nw; k++) M = fmaxf(M, wpart[(size_t)(k * 2 + hh) * CL_REC]);
         float L = 0.0f, o = 0.0f;
-#pragma unroll
-        for (int k = 0; k < CL_WARPS; k++) {
+        for (int k = 0; k < nw; k++) {
             const float *r = wpart + (size_t)(k * 2 + hh) * CL_REC;
             const float f = r[1] > 0.0f ? __expf(r[0] - M) : 0.0f;
             L = fmaf(r[1], f, L);
@@ -241,55 +319,77 @@ __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &
     }
 }
 
-/* rank r of the cluster combines attention outputs [32 r, 32 r + 32) (head r / 4) over the 8 CTA partials and pushes the
- * 32 final values into every peer's att[256].  Warp 0: lane = (quarter of the 32 dims, peer). */
-__device__ __forceinline__ void cl_attention_combine(cg::cluster_group &cl, int rank, float *cpart, float *att) {
-    if (threadIdx.x >= 32) return;
-    const int lane = threadIdx.x, peer = lane & 7, quarter = lane >> 3, hh = rank >> 2, d0 = (rank & 3) * 32 + quarter * 8;
-    const float *rp = cl.map_shared_rank(cpart, peer) + hh * CL_REC;
-    const float m = rp[0], lsum = rp[1];
-    const float4 a0 = *reinterpret_cast<const float4 *>(rp + 4 + d0), a1 = *reinterpret_cast<const float4 *>(rp + 8 + d0);
-    float M = m;
+/* every CTA folds the 8 CTA partials of both heads for itself, straight out of its peers' shared memory: thread (head, dim)
+ * reads 8 x (max, sum, out[dim]) - no push, no third cluster barrier */
+__device__ __forceinline__ void cl_attention_combine(cg::cluster_group &cl, float *cpart, float *att) {
+    const int tid = threadIdx.x;
+    if (tid < 256) {
+        const int hh = tid >> 7, d = tid & 127;
+        float m[CL_SIZE], lsum[CL_SIZE], o[CL_SIZE];
 #pragma unroll
-    for (int o = 4; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
-    const float f = lsum > 0.0f ? __expf(m - M) : 0.0f;
-    float L = lsum * f;
-    float v[8] = {a0.x * f, a0.y * f, a0.z * f, a0.w * f, a1.x * f, a1.y * f, a1.z * f, a1.w * f};
+        for (int k = 0; k < CL_SIZE; k++) {
+            const float *rp = cl.map_shared_rank(cpart, k) + hh * CL_REC;
+            m[k] = rp[0]; lsum[k] = rp[1]; o[k] = rp[4 + d];
+        }
+        float M = m[0];
 #pragma unroll
-    for (int o = 4; o > 0; o >>= 1) {
-        L += __shfl_xor_sync(0xffffffffu, L, o);
+        for (int k = 1; k < CL_SIZE; k++) M = fmaxf(M, m[k]);
+        float L = 0.0f, acc = 0.0f;
 #pragma unroll
-        for (int j = 0; j < 8; j++) v[j] += __shfl_xor_sync(0xffffffffu, v[j], o);
+        for (int k = 0; k < CL_SIZE; k++) {
+            const float f = lsum[k] > 0.0f ? __expf(m[k] - M) : 0.0f;
+            L = fmaf(lsum[k], f, L);
+            acc = fmaf(o[k], f, acc);
+        }
+        att[hh * 128 + d] = acc / L;
     }
-    const float inv = 1.0f / L;
-    float *dst = cl.map_shared_rank(att, peer) + hh * 128 + d0;
-    *reinterpret_cast<float4 *>(dst) = make_float4(v[0] * inv, v[1] * inv, v[2] * inv, v[3] * inv);
-    *reinterpret_cast<float4 *>(dst + 4) = make_float4(v[4] * inv, v[5] * inv, v[6] * inv, v[7] * inv);
+    __syncthreads();
 }
 
-/* gate/up units [u0, u1) of this CTA: warp w takes u0 + w, u0 + w + 16, ...; the first pair of rows is already in `t` */
-__device__ __forceinline__ void cl_swiglu_run(const WTrip &t, const uint16_t *gate, const uint16_t *up, float *gs, int u0, int u1, int cols, const float *xs) {
-    const int lane = threadIdx.x & 31;
-    int u = u0 + (threadIdx.x >> 5);
-    if (u >= u1) return;
-    float va, vb;
-    trip_finish(t, gate + (size_t)u * cols, up + (size_t)u * cols, xs, cols, va, vb);
-    if (lane == 0) gs[u - u0] = swiglu_act<QTC_FAST>(va, vb);
-    for (u += CL_WARPS; u < u1; u += CL_WARPS) {
-        warp_dot2(gate + (size_t)u * cols, up + (size_t)u * cols, xs, cols, va, vb);
-        if (lane == 0) gs[u - u0] = swiglu_act<QTC_FAST>(va, vb);
+/* L2 prefetch of slice `part` of `nparts` of [base, base + bytes): 32 KB bulk prefetches issued by lane 0 of every warp */
+__device__ __forceinline__ void cl_prefetch_slice(const void *base, size_t bytes, int part, int nparts) {
+    if ((threadIdx.x & 31) != 0) return;
+    const size_t per = ((bytes / nparts) + 127) & ~(size_t)127;
+    size_t lo = per * part, hi = lo + per;
+    if (part == nparts - 1 || hi > bytes) hi = bytes;
+    const char *p = reinterpret_cast<const char *>(base);
+    for (size_t off = lo + (size_t)(threadIdx.x >> 5) * 32768; off < hi; off += (size_t)CL_WARPS * 32768) {
+        const size_t nb = hi - off < 32768 ? hi - off : 32768;
+        prefetch_l2_bulk(p + off, (unsigned)(nb & ~(size_t)15));
     }
 }
 
-/* dynamic shared memory (floats): [ xs | qkv 512 | att 256 | cpart 2 x 132 | wpart 16 x 2 x 132 | g 64 | dp H | kv stage 2 x 64 x 128 ] */
-__host__ __device__ inline int cl_smem_floats(int xs_floats, int H) {
-    return xs_floats + 512 + 256 + 2 * CL_REC + CL_WARPS * 2 * CL_REC + 64 + H + 2 * CL_ATT_CAP * 128;
+/* paced L2 prefetch of the first `bytes` of a range: 16 KB requests dealt out over the CTA's warps (lane 0 issues), `gap` ns apart */
+__device__ __forceinline__ void cl_prefetch_paced(const void *base, size_t bytes, unsigned gap, int &slot) {
+    if ((threadIdx.x & 31) != 0) return;
+    const char *p = reinterpret_cast<const char *>(base);
+    for (size_t off = 0; off < bytes; off += 16384, slot++) {
+        if ((slot & (CL_WARPS - 1)) != (int)(threadIdx.x >> 5)) continue;
+        const size_t nb = bytes - off < 16384 ? bytes - off : 16384;
+        prefetch_l2_bulk(p + off, (unsigned)(nb & ~(size_t)15));
+        if (gap) __nanosleep(gap);
+    }
+}
+
+/* dynamic shared memory (floats): [ xs (= dp in the second half of phase B) | qkv 512 | att 256 | cpart 2 x 132 | wpart 16 x 2 x 132 | g 64 |
+ * aux 512 | in_norm H | post_norm H | kv stage 2 x att_cap x 128 ]; the in-kernel sampler's workspace overlays qkv.. (sampling happens
+ * between steps).  Kept small on purpose: shared memory is carved out of the SM's 228 KB and what is left is L1, whose size bounds
+ * the loads an SM keeps in flight - measured: +17 KB of shared memory (a 132 -> 164 KB carve-out) cost the talker step 12 %. */
+__host__ __device__ inline int cl_smem_floats(int xs_floats, int H, int att_cap) {
+    return xs_floats + 512 + 256 + 2 * CL_REC + CL_WARPS * 2 * CL_REC + 64 + 512 + 2 * H + 2 * att_cap * 128;
+}
+__device__ __forceinline__ void cl_cp16(float *dst_smem, const float *src) {
+    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src));
+}
+/* n floats (multiple of 4) global -> shared, cp.async, strided over the CTA */
+__device__ __forceinline__ void cl_stage_async(float *dst, const float *src, int n) {
+    for (int i = threadIdx.x * 4; i < n; i += CL_THREADS * 4) cl_cp16(dst + i, src + i);
 }
 
 __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs a0, const SubProg sp) {
     extern __shared__ __align__(128) float cl_smem[];
     __shared__ float red[32];
-    __shared__ SampleSmem S_samp;
     __shared__ int s_codes[QTC_MAX_GROUPS];
     __shared__ uint32_t s_rng;
     cg::cluster_group cl = cg::this_cluster();
@@ -301,7 +401,8 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     const int H = lm.hidden, I = lm.inter, L = lm.layers;
     const bool att_cluster = g < lm.kv_heads;           /* this cluster owns a KV head in phase A */
     float *sm = cl_smem, *qkv = sm + a.xs_floats, *att = qkv + 512, *cpart = att + 256, *wpart = cpart + 2 * CL_REC;
-    float *gs = wpart + CL_WARPS * 2 * CL_REC, *dp = gs + 64, *kvs = dp + H;
+    float *gs = wpart + CL_WARPS * 2 * CL_REC, *dp = sm, *aux = gs + 64, *nin = aux + 512, *npost = nin + H, *kvs = npost + H;
+    SampleSmem &S_samp = *reinterpret_cast<SampleSmem *>(qkv);      /* 17.4 KB over qkv | att | cpart | wpart (21 KB) */
     const int pos_base = *a.pos_ptr + a.pos_add;
     int p = *a.phase;                                   /* phase counter mod 3 */
     unsigned long long target = 0;
@@ -314,9 +415,40 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     const int u0 = c0 * 8, u1 = c1 * 8, NC = c1 - c0;   /* gate/up units of this CTA; NC <= 8 */
     const int zper = (H + ncta - 1) / ncta, z0 = cta * zper;
     Seg3 s; int cols;
-    WTrip tp;
+    Stage s0, s1;
+    const int HS = H >> 10;                                /* 1024-column stages per weight row */
     const int ja = 64 * rank + warp, jb = ja + CL_WARPS;   /* the warp's first pair of QKV rows; the second pair is +32 */
-    if (sp.G == 0 && att_cluster) cl_trip_issue(tp, cl_qkv_row(lm.layer[0], g, ja, H), cl_qkv_row(lm.layer[0], g, jb, H), H);
+    const int gu_pairs = (u1 - u0 - warp + CL_WARPS - 1) / CL_WARPS;      /* gate/up units of this warp: u0 + warp + 16 k */
+    auto qkv_rows = [&](const LmLayerDev &wl) { return [&wl, g, ja, jb, H](int k, const uint16_t *&ra, const uint16_t *&rb) { ra = cl_qkv_row(wl, g, ja + 32 * k, H); rb = cl_qkv_row(wl, g, jb + 32 * k, H); }; };
+    auto gu_rows = [&](const LmLayerDev &wl) { return [&wl, u0, warp, H](int k, const uint16_t *&ra, const uint16_t *&rb) { const size_t u = (size_t)(u0 + warp + CL_WARPS * k); ra = wl.gate + u * H; rb = wl.up + u * H; }; };
+    /* Everything phase A of layer ll reads that does not depend on this step's activations goes to shared memory by cp.async while
+     * the CTA waits at the grid barrier before it: the K/V rows of this CTA's position range, the RoPE row, the head norms and the
+     * input norm's weights.  (Read on demand, each of these was a DRAM round trip on the critical path: the 2.8 GB streamed per
+     * step evict them from L2 every time.) */
+    auto stage_phase_a = [&](int ll, int pos, int t0, int t1, bool staged) {
+        const LmLayerDev &wl = lm.layer[ll];
+        if (att_cluster) {
+            if (staged && t1 > t0) {
+                const int kvd = lm.kv_heads * 128;
+                const float *kc = a.kc + (size_t)ll * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)ll * a.kv_max * kvd + g * 128;
+                const int rows = (t1 < pos ? t1 : pos) - t0;
+                for (int i = tid; i < rows * 64; i += CL_THREADS) {
+                    const int which = i >= rows * 32, j = which ? i - rows * 32 : i, r = j >> 5, c = j & 31;
+                    cl_cp16(kvs + (size_t)which * a.att_cap * 128 + r * 128 + c * 4, (which ? vc : kc) + kv_off(a.table, t0 + r, kvd) + c * 4);
+                }
+            }
+#if CL_STAGE_AUX
+            if (tid < 128) {
+                const int k = tid >> 5, c = tid & 31;
+                const float *src = k == 0 ? a.cos + (size_t)pos * 128 : k == 1 ? a.sin + (size_t)pos * 128 : k == 2 ? wl.q_norm : wl.k_norm;
+                cl_cp16(aux + k * 128 + c * 4, src + c * 4);
+            }
+            cl_stage_async(nin, wl.in_norm, H);
+#endif
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+    if (sp.G == 0 && att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
 
 #define PROF(i) do { if (a.prof && tid == 0 && l == a.prof_layer) a.prof[cta * 32 + (i)] = clock64(); } while (0)
     for (int gstep = 0; gstep < nsteps; gstep++) {
@@ -325,7 +457,8 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
         int t0 = rank * chunk, t1 = t0 + chunk < n ? t0 + chunk : n;
         if (t0 > n) t0 = n;
         if (t1 < t0) t1 = t0;
-        const bool staged = chunk <= CL_ATT_CAP;
+        const bool staged = chunk <= a.att_cap;
+        if (sp.G == 0) stage_phase_a(0, pos, t0, t1, staged);
         if (sp.G > 0) {
             /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x (fp32, like the step's input) */
             __syncthreads();
@@ -343,7 +476,8 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             }
             head_w = gstep >= 1 ? sp.heads[gstep - 1] : NULL;
             cl_barrier_arrive(a.bar, target, ncta);
-            if (att_cluster) cl_trip_issue(tp, cl_qkv_row(lm.layer[0], g, ja, H), cl_qkv_row(lm.layer[0], g, jb, H), H);
+            if (att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
+            stage_phase_a(0, pos, t0, t1, staged);
             cl_barrier_wait(a.bar, target, a.err);
         }
         for (int l = 0; l < L; l++) {
@@ -353,31 +487,32 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             PROF(0);
             if (tid < zper && z0 + tid < H) xout[z0 + tid] = 0;
             if (att_cluster) {
-                if (staged && t1 > t0) {                /* K/V rows of earlier positions: on their way while the projections run */
-                    const int kvd = lm.kv_heads * 128;
-                    const float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
-                    const int rows = (t1 < pos ? t1 : pos) - t0;
-                    for (int i = tid; i < rows * 64; i += CL_THREADS) {
-                        const int which = i >= rows * 32, j = which ? i - rows * 32 : i, r = j >> 5, c = j & 31;
-                        const float *src = (which ? vc : kc) + kv_off(a.table, t0 + r, kvd) + c * 4;
-                        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(kvs + (size_t)which * CL_ATT_CAP * 128 + r * 128 + c * 4);
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(src));
-                    }
-                }
+                asm volatile("cp.async.wait_all;" ::: "memory");       /* this thread's share of nin (and of the K/V rows, aux) has landed */
+                XRegs xr;
+#if CL_STAGE_AUX
+                cl_x_load(xr, l == 0 ? a.x : NULL, xin, nin, H);
+                cl_stage_async(npost, w.post_norm, H);
                 asm volatile("cp.async.commit_group;");
-                cl_stage_norm(sm, l == 0 ? a.x : NULL, xin, w.in_norm, H, lm.eps, red);
+#else
+                cl_x_load(xr, l == 0 ? a.x : NULL, xin, w.in_norm, H);
+                if (tid < 128) {                                        /* read on demand (the variant without staging) */
+                    const int k = tid >> 5, c = tid & 31;
+                    const float *src = k == 0 ? a.cos + (size_t)pos * 128 : k == 1 ? a.sin + (size_t)pos * 128 : k == 2 ? w.q_norm : w.k_norm;
+                    *reinterpret_cast<float4 *>(aux + k * 128 + c * 4) = *reinterpret_cast<const float4 *>(src + c * 4);
+                }
+#endif
+                cl_norm_finish(sm, xr, H, lm.eps, red);
                 PROF(1);
                 {
-                    float va, vb, vc2, vd;
-                    trip_finish(tp, cl_qkv_row(w, g, ja, H), cl_qkv_row(w, g, jb, H), sm, H, va, vb);
-                    warp_dot2(cl_qkv_row(w, g, ja + 32, H), cl_qkv_row(w, g, jb + 32, H), sm, H, vc2, vd);
-                    if (lane < CL_SIZE) { float *peer = cl.map_shared_rank(qkv, lane); peer[ja] = va; peer[jb] = vb; peer[ja + 32] = vc2; peer[jb + 32] = vd; }
+                    cl_stream(s0, s1, 2, HS, sm, qkv_rows(w), [&](int k, float va, float vb) {
+                        if (lane < CL_SIZE) { float *peer = cl.map_shared_rank(qkv, lane); peer[ja + 32 * k] = va; peer[jb + 32 * k] = vb; }
+                    });
                 }
                 PROF(2);
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 cl.sync();
                 PROF(3);
-                cl_attention(a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs);
+                cl_attention(a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
                 /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
                 const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
                 uint4 ow[8];
@@ -386,23 +521,23 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 PROF(4);
                 cl.sync();
                 PROF(5);
-                cl_attention_combine(cl, rank, cpart, att);
-                cl.sync();
+                cl_attention_combine(cl, cpart, att);
+                if (a.flags & 8) cl.sync();                             /* experiment: the third cluster barrier of the push variant */
                 PROF(6);
                 const float4 a0v = reinterpret_cast<const float4 *>(att)[2 * lane], a1v = reinterpret_cast<const float4 *>(att)[2 * lane + 1];
-                for (int rb = 0; rb < RPC; rb += 8 * CL_WARPS) {           /* RPC = 128: one pass; 256: two */
+                uint4 ow2[8];                                           /* H = 2048: rows 128..255 of this CTA, requested before the first eight are reduced */
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    ow2[i] = CL_PIPE && RPC > 8 * CL_WARPS ? ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(8 * CL_WARPS + warp + CL_WARPS * i) * 256) + lane) : make_uint4(0, 0, 0, 0);
+                auto o_batch = [&](const uint4 (&wv)[8], int rb) {
                     long long resid = 0;
                     if (g == 0 && lane < 8) {
                         const int row = rank * RPC + rb + warp + CL_WARPS * lane;
                         resid = l == 0 ? to_fx(__ldcg(a.x + row)) : __ldcg(xin + row);
                     }
-                    if (rb > 0) {
-#pragma unroll
-                        for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(rb + warp + CL_WARPS * i) * 256) + lane);
-                    }
                     float acc[8];
 #pragma unroll
-                    for (int i = 0; i < 8; i++) acc[i] = dot8f(ow[i], a0v, a1v, 0.0f);
+                    for (int i = 0; i < 8; i++) acc[i] = dot8f(wv[i], a0v, a1v, 0.0f);
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) {
                         float t8[8];
@@ -414,44 +549,93 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
 #pragma unroll
                     for (int i = 0; i < 8; i++)
                         if (lane == i) red_add_s64(xmid + rank * RPC + rb + warp + CL_WARPS * i, to_fx(acc[i]) + resid);
+                };
+                o_batch(ow, 0);
+                if (RPC > 8 * CL_WARPS) {
+#if !CL_PIPE
+#pragma unroll
+                    for (int i = 0; i < 8; i++) ow2[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(8 * CL_WARPS + warp + CL_WARPS * i) * 256) + lane);
+#endif
+                    o_batch(ow2, 8 * CL_WARPS);
+                }
+            }
+#if CL_STAGE_AUX
+            else {
+                cl_stage_async(npost, w.post_norm, H);
+                asm volatile("cp.async.commit_group;");
+            }
+#endif
+            if (!att_cluster && a.pf_frac > 0) {
+                /* clusters without a KV head: pull (the first pf_frac percent of) every CTA's slice of this layer's MLP weights into L2
+                 * while the attention block runs; consumer CTAs are dealt out over the idle CTAs */
+                const int nidle = ncta - lm.kv_heads * CL_SIZE, me = cta - lm.kv_heads * CL_SIZE;
+                int slot = 0;
+                for (int cons = me; cons < ncta; cons += nidle) {
+                    const int cc0 = (int)(((unsigned)NCH * (unsigned)cons) / (unsigned)ncta), cc1 = (int)(((unsigned)NCH * (unsigned)(cons + 1)) / (unsigned)ncta);
+                    const size_t rows = (size_t)((cc1 - cc0) * 8 * a.pf_frac / 100), chunks = (size_t)((cc1 - cc0) * a.pf_frac / 100);
+                    cl_prefetch_paced(w.gate + (size_t)cc0 * 8 * H, rows * H * 2, (unsigned)a.pf_gap, slot);
+                    cl_prefetch_paced(w.up + (size_t)cc0 * 8 * H, rows * H * 2, (unsigned)a.pf_gap, slot);
+                    cl_prefetch_paced(w.down_t + (size_t)cc0 * H * 8, chunks * H * 16, (unsigned)a.pf_gap, slot);
                 }
             }
             PROF(7);
             cl_barrier_arrive(a.bar, target, ncta);
-            cl_trip_issue(tp, w.gate + (size_t)(u0 + warp) * H, w.up + (size_t)(u0 + warp) * H, H);      /* every warp has a first unit: >= 16 per CTA */
+            cl_stream_prefetch(s0, s1, gu_pairs, HS, gu_rows(w));
             cl_barrier_wait(a.bar, target, a.err);
             p++;
             PROF(8);
             /* ================= phase B: reads xmid, adds the MLP's output into xout, zeroes xin */
             if (tid < zper && z0 + tid < H) xin[z0 + tid] = 0;
+            if (att_cluster && l + 1 < L && !(a.flags & 2) && sp.G > 0) {
+                /* next layer's attention-block weights of this CTA -> L2 while the MLP phase runs (its own weights came in during phase A) */
+                const LmLayerDev &wn = lm.layer[l + 1];
+                const int j0 = 64 * rank;                               /* rows j0..j0+63 of the cluster's QKV block lie inside one of its four 128-row parts */
+                cl_prefetch_slice(cl_qkv_row(wn, g, j0, H), (size_t)64 * H * 2, 0, 1);
+                cl_prefetch_slice(wn.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256, (size_t)RPC * 512, 0, 1);
+            }
+#if CL_STAGE_AUX
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            cl_stage_norm(sm, NULL, xmid, npost, H, lm.eps, red);
+#else
             cl_stage_norm(sm, NULL, xmid, w.post_norm, H, lm.eps, red);
+#endif
             PROF(9);
-            cl_swiglu_run(tp, w.gate, w.up, gs, u0, u1, H, sm);
-            __syncthreads();
-            PROF(10);
+            cl_stream(s0, s1, gu_pairs, HS, sm, gu_rows(w), [&](int k, float va, float vb) {
+                if (lane == 0) gs[warp + CL_WARPS * k] = swiglu_act<QTC_FAST>(va, vb);
+            });
             {
-                /* down partial: dp[r] = sum over this CTA's columns; pieces (chunk c, row r) are 16 bytes at (c H + r) */
+                /* down partial: dp[r] = sum over this CTA's columns of W_down[r][.] g[.]; pieces (chunk c, row r) are 16 bytes at
+                 * (c H + r).  A batch = rows (r, r + 512) x 4 chunks = 8 loads in a Stage; batches: row pairs x chunk groups, two in flight;
+                 * the first two are requested before the SwiGLU values are complete (they do not depend on them). */
                 const uint4 *dw = reinterpret_cast<const uint4 *>(w.down_t) + (size_t)c0 * H;
-                for (int r = tid; r < H; r += 2 * CL_THREADS) {
-                    const int r2 = r + CL_THREADS;
-                    float sa = 0.0f, sb = 0.0f;
-                    for (int cb = 0; cb < NC; cb += 4) {
-                        uint4 wa[4], wb[4];
+                const int CB = NC > 4 ? 2 : 1, nb = HS * CB;                 /* H = 1024: one row pair per thread; 2048: two */
+                auto d_issue = [&](Stage &st, int bi) {
+                    const int r = tid + 2 * CL_THREADS * (bi / CB), cb = 4 * (bi % CB);
 #pragma unroll
-                        for (int c = 0; c < 4; c++) {
-                            wa[c] = cb + c < NC ? ldg_stream(dw + (size_t)(cb + c) * H + r) : make_uint4(0, 0, 0, 0);
-                            wb[c] = cb + c < NC && r2 < H ? ldg_stream(dw + (size_t)(cb + c) * H + r2) : make_uint4(0, 0, 0, 0);
-                        }
-#pragma unroll
-                        for (int c = 0; c < 4; c++)
-                            if (cb + c < NC) {
-                                const float4 g0 = reinterpret_cast<const float4 *>(gs)[2 * (cb + c)], g1 = reinterpret_cast<const float4 *>(gs)[2 * (cb + c) + 1];
-                                sa = dot8f(wa[c], g0, g1, sa);
-                                sb = dot8f(wb[c], g0, g1, sb);
-                            }
+                    for (int c = 0; c < 4; c++) {
+                        st.a[c] = cb + c < NC ? ldg_stream(dw + (size_t)(cb + c) * H + r) : make_uint4(0, 0, 0, 0);
+                        st.b[c] = cb + c < NC ? ldg_stream(dw + (size_t)(cb + c) * H + r + CL_THREADS) : make_uint4(0, 0, 0, 0);
                     }
-                    dp[r] = sa;
-                    if (r2 < H) dp[r2] = sb;
+                };
+                float sa = 0.0f, sb = 0.0f;
+                auto d_consume = [&](const Stage &st, int bi) {
+                    const int r = tid + 2 * CL_THREADS * (bi / CB), cb = 4 * (bi % CB);
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const float4 g0 = reinterpret_cast<const float4 *>(gs)[2 * (cb + c)], g1 = reinterpret_cast<const float4 *>(gs)[2 * (cb + c) + 1];
+                        sa = dot8f(st.a[c], g0, g1, sa);
+                        sb = dot8f(st.b[c], g0, g1, sb);
+                    }
+                    if (bi % CB == CB - 1) { dp[r] = sa; dp[r + CL_THREADS] = sb; sa = 0.0f; sb = 0.0f; }
+                };
+                d_issue(s0, 0);
+                if (nb > 1) d_issue(s1, 1); else st_zero(s1);
+                __syncthreads();                                        /* gs complete; xs (= dp) no longer read */
+                PROF(10);
+                for (int bi = 0; bi < nb; bi += 2) {
+                    d_consume(s0, bi);
+                    if (bi + 2 < nb) d_issue(s0, bi + 2);
+                    if (bi + 1 < nb) { d_consume(s1, bi + 1); if (bi + 3 < nb) d_issue(s1, bi + 3); }
                 }
             }
             PROF(11);
@@ -478,7 +662,8 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             }
             PROF(13);
             cl_barrier_arrive(a.bar, target, ncta);
-            if (l + 1 < L && att_cluster) cl_trip_issue(tp, cl_qkv_row(lm.layer[l + 1], g, ja, H), cl_qkv_row(lm.layer[l + 1], g, jb, H), H);
+            if (l + 1 < L && att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[l + 1]));
+            if (l + 1 < L) stage_phase_a(l + 1, pos, t0, t1, staged);
             cl_barrier_wait(a.bar, target, a.err);
             p++;
             PROF(14);

@@ -154,7 +154,7 @@ static int params_key(const qtc_ctx *c) {
     for (size_t i = 0; i < sizeof(c->params); i++) h = (h ^ p[i]) * 16777619u;
     h = (h ^ (uint32_t)c->mode) * 16777619u;
     h = (h ^ (uint32_t)c->arith) * 16777619u;
-    if (c->mode == 0 || c->arith) h = (h ^ (uint32_t)c->kv.used[0]) * 16777619u;   /* per-op attention: the score buffer (dynamic smem) is sized by the capacity */
+    if (c->mode == 0 || c->mode == 2 || c->arith) h = (h ^ (uint32_t)c->kv.used[0]) * 16777619u;   /* per-op attention and the cluster kernel size their shared memory by the capacity */
     return (int)(h & 0x7fffffff);
 }
 

@@ -234,7 +234,7 @@ static int cluster_setup(qtc_ctx *c) {
     QTC_CUDA(cudaFuncSetAttribute(k_lm_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     /* how many 8-CTA clusters the device holds at once (B200, one CTA per SM: 15) */
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(CL_MAX_CLUSTERS * CL_SIZE); cfg.blockDim = dim3(CL_THREADS); cfg.dynamicSmemBytes = (size_t)cl_smem_floats(4096, 2048) * 4;
+    cfg.gridDim = dim3(CL_MAX_CLUSTERS * CL_SIZE); cfg.blockDim = dim3(CL_THREADS); cfg.dynamicSmemBytes = (size_t)cl_smem_floats(4096, 2048, CL_ATT_CAP) * 4;
     cudaLaunchAttribute at[1];
     memset(at, 0, sizeof(at));
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = CL_SIZE; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
@@ -277,6 +277,15 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
     a.st = st; a.err = c->cl_err;
     a.prof = (c->prof_sub ? lm == &c->sub : lm == &c->talker) ? c->prof : NULL; a.prof_layer = c->prof_layer;
     { static int fl = -1; if (fl < 0) { const char *e = getenv("QTC_FUSED_FLAGS"); fl = e ? atoi(e) : 0; } a.flags = fl; }
+    {   /* idle-cluster L2 prefetch of the MLP weights (measured on B200, scripts/probe/pf_sweep.sh): the sub-talker takes all of it
+         * unpaced (1837 -> 1784 us per frame); the talker's 75 MB per layer must not crowd out the attention block's own loads:
+         * half of every slice, 2 us between a warp's requests (1030 -> 982 us per step; all of it unpaced: 1043) */
+        static int fr = -2, gp = -1;
+        if (fr == -2) { const char *e = getenv("QTC_PF_FRAC"); fr = e ? atoi(e) : -1; e = getenv("QTC_PF_GAP"); gp = e ? atoi(e) : -1; }
+        const bool tk = lm == &c->talker;
+        a.pf_frac = fr >= 0 ? fr : (tk ? 50 : 100);
+        a.pf_gap = gp >= 0 ? gp : (tk ? 2000 : 0);
+    }
     int vec = lm->hidden;
     SubProg sp;
     memset(&sp, 0, sizeof(sp));
@@ -286,7 +295,12 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
         if (sp.Hin > vec) vec = sp.Hin;
     }
     a.xs_floats = (vec + 31) & ~31;
-    const size_t smem = (size_t)cl_smem_floats(a.xs_floats, lm->hidden) * 4;
+    /* K/V stage: positions this sequence can reach split 8 ways (the sub-talker: G + 2; the talker: the pages it holds), in steps of 16 */
+    const int reach = b == &c->tk ? c->kv.used[0] * QTC_KV_PAGE_POS : b->kv_max;
+    a.att_cap = (((reach + CL_SIZE - 1) / CL_SIZE + 15) / 16) * 16;
+    if (a.att_cap > CL_ATT_CAP) a.att_cap = CL_ATT_CAP;
+    if (a.att_cap < 16) a.att_cap = 16;
+    const size_t smem = (size_t)cl_smem_floats(a.xs_floats, lm->hidden, a.att_cap) * 4;
     if (smem > (size_t)g_cluster_max_smem) { qtc_set_error("cluster step: %zu bytes of shared memory needed, %d available", smem, g_cluster_max_smem); return -1; }
     cudaLaunchConfig_t cfg = {};
     const int ncl = g_cluster_fit < CL_MAX_CLUSTERS ? g_cluster_fit : CL_MAX_CLUSTERS;

@@ -42,7 +42,7 @@ def test_fused_generate(cuda, fused_ctx, name, params, spk, lang):
     assert snr_db(want_pcm, pcm) >= 80.0
 
 
-@pytest.mark.parametrize("mode", [1], ids=["fused"])
+@pytest.mark.parametrize("mode", [1, 2], ids=["fused", "cluster"])
 def test_fused_long_context_splits(cuda, orc, mode):
     """KV length past 64 / 128 / ... positions exercises the split-KV attention and its combine step:
     teacher-forced talker steps on the `small` preset (16 Q / 8 KV heads of 128) against the oracle"""
