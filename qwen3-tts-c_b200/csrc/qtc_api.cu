@@ -180,6 +180,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
         c->sub_in_w = qtc_upload(c, desc->sub_input_proj_w, (size_t)desc->sub.hidden * H);
         c->sub_in_b = qtc_upload(c, desc->sub_input_proj_b, desc->sub.hidden);
         if (alloc_lm_buffers(c, &c->tk, &c->talker) || alloc_lm_buffers(c, &c->st, &c->sub)) { qwen_tts_cuda_release(c); return NULL; }
+        if (qtc_build_proj_tables(c)) { qwen_tts_cuda_release(c); return NULL; }
         if (qtc_ensure_kv(c, &c->st, &c->sub, c->G + 2) || qtc_kv_pool_init(c, c->max_batch)) { qwen_tts_cuda_release(c); return NULL; }
     } else {
         c->talker.vocab = desc->talker.vocab; c->talker.hidden = desc->talker.hidden;

@@ -372,8 +372,8 @@ __device__ __forceinline__ void cl_prefetch_paced(const void *base, size_t bytes
 }
 
 /* dynamic shared memory (floats): [ xs (= dp in the second half of phase B) | qkv 512 | att 256 | cpart 2 x 132 | wpart 16 x 2 x 132 | g 64 |
- * aux 512 | in_norm H | post_norm H | kv stage 2 x att_cap x 128 ]; the in-kernel sampler's workspace overlays qkv.. (sampling happens
- * between steps).  Kept small on purpose: shared memory is carved out of the SM's 228 KB and what is left is L1, whose size bounds
+ * aux 512 | in_norm H | post_norm H | kv stage 2 x att_cap x 128 ]; the in-kernel sampler's workspace overlays aux.. (sampling happens
+ * between steps; only this CTA writes there).  Kept small on purpose: shared memory is carved out of the SM's 228 KB and what is left is L1, whose size bounds
  * the loads an SM keeps in flight - measured: +17 KB of shared memory (a 132 -> 164 KB carve-out) cost the talker step 12 %. */
 __host__ __device__ inline int cl_smem_floats(int xs_floats, int H, int att_cap) {
     return xs_floats + 512 + 256 + 2 * CL_REC + CL_WARPS * 2 * CL_REC + 64 + 512 + 2 * H + 2 * att_cap * 128;
@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     const bool att_cluster = g < lm.kv_heads;           /* this cluster owns a KV head in phase A */
     float *sm = cl_smem, *qkv = sm + a.xs_floats, *att = qkv + 512, *cpart = att + 256, *wpart = cpart + 2 * CL_REC;
     float *gs = wpart + CL_WARPS * 2 * CL_REC, *dp = sm, *aux = gs + 64, *nin = aux + 512, *npost = nin + H, *kvs = npost + H;
-    SampleSmem &S_samp = *reinterpret_cast<SampleSmem *>(qkv);      /* 17.4 KB over qkv | att | cpart | wpart (21 KB) */
+    SampleSmem &S_samp = *reinterpret_cast<SampleSmem *>(aux);      /* 17.2 KB over aux | in_norm | post_norm | kv stage: regions only this CTA writes (peers push into qkv) */
     const int pos_base = *a.pos_ptr + a.pos_add;
     int p = *a.phase;                                   /* phase counter mod 3 */
     unsigned long long target = 0;
@@ -459,7 +459,16 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
         if (t1 < t0) t1 = t0;
         const bool staged = chunk <= a.att_cap;
         if (sp.G == 0) stage_phase_a(0, pos, t0, t1, staged);
-        if (sp.G > 0) {
+        const float *x_in = a.x;                        /* fp32 input of layer 0 */
+        if (sp.G > 0 && gstep >= 1 && sp.ptab[gstep - 1]) {
+            /* ST_PROJECT_INPUT by table: the projected embedding of every code was computed at upload, and every CTA knows the code it
+             * sampled - no gather, no GEMV, no grid barrier between the sample and the first layer */
+            __syncthreads();                            /* the sampler's workspace (over aux..) is free */
+            x_in = sp.ptab[gstep - 1] + (size_t)s_codes[gstep - 1] * H;
+            head_w = sp.heads[gstep - 1];
+            if (att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
+            stage_phase_a(0, pos, t0, t1, staged);
+        } else if (sp.G > 0) {
             /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x (fp32, like the step's input) */
             __syncthreads();
             if (gstep == 0) stage_vec(sm, sp.hidden, sp.Hin);
@@ -490,11 +499,11 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 asm volatile("cp.async.wait_all;" ::: "memory");       /* this thread's share of nin (and of the K/V rows, aux) has landed */
                 XRegs xr;
 #if CL_STAGE_AUX
-                cl_x_load(xr, l == 0 ? a.x : NULL, xin, nin, H);
+                cl_x_load(xr, l == 0 ? x_in : NULL, xin, nin, H);
                 cl_stage_async(npost, w.post_norm, H);
                 asm volatile("cp.async.commit_group;");
 #else
-                cl_x_load(xr, l == 0 ? a.x : NULL, xin, w.in_norm, H);
+                cl_x_load(xr, l == 0 ? x_in : NULL, xin, w.in_norm, H);
                 if (tid < 128) {                                        /* read on demand (the variant without staging) */
                     const int k = tid >> 5, c = tid & 31;
                     const float *src = k == 0 ? a.cos + (size_t)pos * 128 : k == 1 ? a.sin + (size_t)pos * 128 : k == 2 ? w.q_norm : w.k_norm;
@@ -533,7 +542,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                     long long resid = 0;
                     if (g == 0 && lane < 8) {
                         const int row = rank * RPC + rb + warp + CL_WARPS * lane;
-                        resid = l == 0 ? to_fx(__ldcg(a.x + row)) : __ldcg(xin + row);
+                        resid = l == 0 ? to_fx(__ldcg(x_in + row)) : __ldcg(xin + row);
                     }
                     float acc[8];
 #pragma unroll
@@ -586,7 +595,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             PROF(8);
             /* ================= phase B: reads xmid, adds the MLP's output into xout, zeroes xin */
             if (tid < zper && z0 + tid < H) xin[z0 + tid] = 0;
-            if (att_cluster && l + 1 < L && !(a.flags & 2) && sp.G > 0) {
+            if (att_cluster && l + 1 < L && !(a.flags & 2)) {
                 /* next layer's attention-block weights of this CTA -> L2 while the MLP phase runs (its own weights came in during phase A) */
                 const LmLayerDev &wn = lm.layer[l + 1];
                 const int j0 = 64 * rank;                               /* rows j0..j0+63 of the cluster's QKV block lie inside one of its four 128-row parts */

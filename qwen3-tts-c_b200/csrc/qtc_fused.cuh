@@ -69,6 +69,7 @@ struct SubProg {
     uint32_t seed_bits;                     /* the RNG is re-seeded every frame (c/qwen_tts_talker.c:718) */
     float *scratch_f; int *scratch_i;       /* slow-path sampler scratch */
     float *vec;                             /* [Hin] cross-CTA scratch for the gathered / projected input */
+    const float *ptab[QTC_MAX_GROUPS - 1];  /* mode 2: ptab[g-1][code] = the projected input of position g >= 1, fp32 [vocab, h], built at upload (NULL: project in the kernel) */
 };
 
 /* the 512 compute threads synchronise on named barrier 1; the producer warp (threads 512..543) never joins */

@@ -124,6 +124,7 @@ struct qtc_ctx {
     const uint16_t *sub_emb[QTC_MAX_GROUPS - 1], *sub_head[QTC_MAX_GROUPS - 1];
     const uint16_t *sub_in_w;
     const float *sub_in_b;
+    const float *sub_ptab[QTC_MAX_GROUPS - 1];   /* mode 2: projected sub-talker inputs per code, fp32 [vocab, sub.hidden] per position g >= 1 (qtc_lm.cu) */
     LmBuffers tk, st;
     KvPool kv;
     long long dev_mallocs;        /* cudaMalloc calls made for this context after upload returned (steady state: none) */
@@ -202,7 +203,8 @@ int qtc_prefill_gemm(qtc_ctx *c, const float *embeds_dev, int seq_len, int base)
 bool qtc_prefill_gemm_ok(const qtc_ctx *c);
 void qtc_prefill_release(qtc_ctx *c);
 int qtc_kv_pool_init(qtc_ctx *c, int max_batch);
-int qtc_cluster_prepare(qtc_ctx *c, LmDev *d);      /* mode 2 weight layouts (qtc_lm.cu); 0 also when the geometry does not fit */
+int qtc_cluster_prepare(qtc_ctx *c, LmDev *d);
+int qtc_build_proj_tables(qtc_ctx *c);              /* sub-talker input tables for mode 2 (after the embeddings are uploaded) */      /* mode 2 weight layouts (qtc_lm.cu); 0 also when the geometry does not fit */
 int qtc_kv_reserve(qtc_ctx *c, int slot, int positions);      /* the slot holds pages for at least `positions` positions */
 void qtc_kv_release_all(qtc_ctx *c);
 #define QTC_COUNT_MALLOC(c) ((c)->dev_mallocs++)

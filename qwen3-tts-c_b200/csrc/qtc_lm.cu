@@ -224,6 +224,61 @@ int qtc_cluster_prepare(qtc_ctx *c, LmDev *d) {
     QTC_CUDA(cudaDeviceSynchronize());
     return 0;
 }
+/* ptab[g-1][v][r] = sum_c in_w[r][c] * emb_g[v][c] + in_b[r] (or the embedding row itself, zero-padded, without an input projection):
+ * what the sub-talker's position g >= 1 feeds its first layer when code v was sampled at position g - 1.  A block takes 8 codes: their
+ * embedding rows sit in shared memory as fp32, each warp streams weight rows once for all 8; the sum order is the decode kernels'
+ * (lane's 16-byte pieces lane + 32 i in turn, then the butterfly), so the table holds what the in-kernel projection would produce. */
+__global__ void __launch_bounds__(256) k_proj_table(float *out, const uint16_t *emb, const uint16_t *in_w, const float *in_b, int vocab, int Hin, int h) {
+    extern __shared__ __align__(16) float xs8[];
+    const int v0 = blockIdx.x * 8, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 8 * Hin; i += 256) { const int k = i / Hin, c = i - k * Hin; xs8[i] = v0 + k < vocab ? bf16_to_f32(emb[(size_t)(v0 + k) * Hin + c]) : 0.0f; }
+    __syncthreads();
+    if (!in_w) {
+        for (int i = tid; i < 8 * h; i += 256) { const int k = i / h, r = i - k * h; if (v0 + k < vocab) out[(size_t)(v0 + k) * h + r] = r < Hin ? xs8[k * Hin + r] : 0.0f; }
+        return;
+    }
+    const int n8 = Hin >> 3;
+    for (int r = warp; r < h; r += 8) {
+        const uint4 *w4 = reinterpret_cast<const uint4 *>(in_w + (size_t)r * Hin);
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int i = lane; i < n8; i += 32) {
+            const uint4 wv = ldg_stream(w4 + i);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const float4 *x4 = reinterpret_cast<const float4 *>(xs8 + k * Hin);
+                acc[k] = dot8f(wv, x4[2 * i], x4[2 * i + 1], acc[k]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) acc[k] = warp_sum(acc[k]);
+        if (lane < 8 && v0 + lane < vocab) {
+            float vsel = acc[0];
+#pragma unroll
+            for (int k = 1; k < 8; k++) if (lane == k) vsel = acc[k];
+            out[(size_t)(v0 + lane) * h + r] = (in_b ? in_b[r] : 0.0f) + vsel;
+        }
+    }
+}
+int qtc_build_proj_tables(qtc_ctx *c) {
+    for (int g = 0; g < QTC_MAX_GROUPS - 1; g++) c->sub_ptab[g] = NULL;
+    const LmDev *lm = &c->sub;
+    if (!cluster_geometry(lm) || c->G < 2 || c->H % 8) return 0;
+    const int Hin = c->H, h = lm->hidden;
+    if ((size_t)8 * Hin * 4 > 160 * 1024) return 0;
+    QTC_CUDA(cudaFuncSetAttribute(k_proj_table, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * Hin * 4));
+    for (int g = 1; g < c->G; g++) {
+        const int vocab = g == 1 ? c->talker.vocab : lm->vocab;
+        const uint16_t *emb = g == 1 ? c->codec_embedding : c->sub_emb[g - 2];
+        float *t = (float *)qtc_dmalloc(c, (size_t)vocab * h * 4);
+        if (!t) return -1;
+        k_proj_table<<<(vocab + 7) / 8, 256, (size_t)8 * Hin * 4>>>(t, emb, c->sub_in_w, c->sub_in_b, vocab, Hin, h);
+        QTC_CUDA(cudaGetLastError());
+        c->sub_ptab[g - 1] = t;
+    }
+    QTC_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+
 static int g_cluster_attr = 0, g_cluster_max_smem = 0, g_cluster_fit = -1;
 static int cluster_setup(qtc_ctx *c) {
     if (g_cluster_attr) return 0;
@@ -300,6 +355,7 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
     a.att_cap = (((reach + CL_SIZE - 1) / CL_SIZE + 15) / 16) * 16;
     if (a.att_cap > CL_ATT_CAP) a.att_cap = CL_ATT_CAP;
     if (a.att_cap < 16) a.att_cap = 16;
+    while (prog && (size_t)(512 + 2 * lm->hidden + 2 * a.att_cap * 128) * 4 < sizeof(SampleSmem)) a.att_cap += 16;   /* the sampler's workspace overlays aux.. */
     const size_t smem = (size_t)cl_smem_floats(a.xs_floats, lm->hidden, a.att_cap) * 4;
     if (smem > (size_t)g_cluster_max_smem) { qtc_set_error("cluster step: %zu bytes of shared memory needed, %d available", smem, g_cluster_max_smem); return -1; }
     cudaLaunchConfig_t cfg = {};
@@ -482,6 +538,7 @@ int qtc_subtalker_dev(qtc_ctx *c, const float *hidden_dev, const int *first_code
         sp.cfg.temperature = c->params.subtalker_temperature; sp.cfg.suppress_from = -1; sp.cfg.eos_id = -1; sp.cfg.rep_penalty = 1.0f;
         { float f = (float)c->params.sample_seed; memcpy(&sp.seed_bits, &f, 4); }
         sp.scratch_f = c->sample_scratch_f; sp.scratch_i = c->sample_scratch; sp.vec = c->st_embed;
+        for (int g = 0; g < G - 1; g++) sp.ptab[g] = c->sub_ptab[g];
         return fused_step(c, lm, &c->st, c->zero_pos, 0, NULL, lm->vocab, c->st.logits, NULL, &sp);
     }
     const int *g_zero_pos = c->zero_pos;          /* device int 0: the sub-talker's position base */
