@@ -367,7 +367,8 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
     at[1].id = cudaLaunchAttributeCooperative; at[1].val.cooperative = 1;
     /* cooperative as well where the driver takes both attributes (co-residency then is checked, not assumed); the grid is
      * 128 CTAs at one per SM on an otherwise idle stream-ordered device either way */
-    static int coop = 1;
+    static int coop = -1;
+    if (coop < 0) { const char *e = getenv("QTC_CL_COOP"); coop = e ? atoi(e) : 1; }      /* 0: cluster attribute only (ncu could not replay the cooperative + cluster launch) */
     cfg.attrs = at; cfg.numAttrs = coop ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, k_lm_cluster, a, sp);
     if (e != cudaSuccess && coop) {
