@@ -202,7 +202,7 @@ __device__ __forceinline__ float4 cl_norm_rope(const float *src, const float *nw
     float ss = v.x * v.x;
     ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
     ss = warp_sum(ss);
-    const float inv = 1.0f / sqrtf(ss / 128.0f + eps);
+    const float inv = rsqrtf(ss * 0.0078125f + eps);
     const float4 y = make_float4(v.x * inv * n4.x, v.y * inv * n4.y, v.z * inv * n4.z, v.w * inv * n4.w);
     const float px = __shfl_xor_sync(0xffffffffu, y.x, 16), py = __shfl_xor_sync(0xffffffffu, y.y, 16);
     const float pz = __shfl_xor_sync(0xffffffffu, y.z, 16), pw = __shfl_xor_sync(0xffffffffu, y.w, 16);
@@ -217,9 +217,10 @@ __device__ __forceinline__ float dot4(const float4 a, const float4 b) {
 
 /* Attention of cluster g at position pos: positions [t0, t1) of this CTA, both query heads per K/V row.
  * qkv: this CTA's copy of the cluster's 512 projection outputs.  Leaves the CTA's partial records in cpart[2][CL_REC]. */
-__device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int t0, int t1, bool staged,
+__device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int t0, int t1, bool staged,
                                              const float *qkv, float *wpart, float *cpart, const float *kvs, const float *aux) {
     const int cap = a.att_cap;
+#define APROF(i) do { if (a.prof && threadIdx.x == 0 && l == a.prof_layer) a.prof[blockIdx.x * 32 + (i)] = clock64(); } while (0)
     /* aux (staged with the K/V rows): [cos row | sin row | q_norm | k_norm], 128 floats each */
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, kvd = lm.kv_heads * 128;
     const float *q_norm = aux + 256, *k_norm = aux + 384;
@@ -239,6 +240,7 @@ __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &
             *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
             *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
         }
+        APROF(16);
         const float *Ks = kvs, *Vs = kvs + cap * 128;
         const float scale = 0.08838834764831845f;                      /* 1 / sqrt(128) */
         for (int tb = t0 + warp; tb < t1; tb += 4 * CL_WARPS) {
@@ -288,6 +290,7 @@ __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &
                 }
         }
     }
+    APROF(17);
     /* warp records: [warp][head][max, sum, -, -, out[128]]; only warps that had a position write and are folded */
 #if CL_NW_LOOP
     const int nw = t1 - t0 < CL_WARPS ? t1 - t0 : CL_WARPS;
@@ -302,6 +305,7 @@ __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &
         *reinterpret_cast<float4 *>(r1 + 4 + lane * 4) = o1;
     }
     __syncthreads();
+    APROF(18);
     if (tid < 256) {
         const int hh = tid >> 7, d = tid & 127;
         float M = -3.402823466e+38f;
@@ -313,22 +317,84 @@ __device__ __forceinline__ void cl_attention(const ClusterArgs &a, const LmDev &
             L = fmaf(r[1], f, L);
             o = fmaf(r[4 + d], f, o);
         }
-        float *c = cpart + hh * CL_REC;
-        c[4 + d] = o;
-        if (d == 0) { c[0] = M; c[1] = L; }
+        /* the CTA's record goes into every peer's table: after the cluster barrier each CTA folds the 8 records locally */
+        float *mine = cpart + (size_t)(cl.block_rank() * 2 + hh) * CL_REC;
+#pragma unroll
+        for (int k = 0; k < CL_SIZE; k++) {
+            float *dst = cl.map_shared_rank(mine, k);
+            dst[4 + d] = o;
+            if (d == 0) { dst[0] = M; dst[1] = L; }
+        }
     }
+    APROF(19);
+}
+#undef APROF
+
+/* Contexts of at most 32 positions (every sub-talker step): the whole head in ONE warp of CTA rank hh (0 / 1) - lane i owns dims
+ * 4i..4i+3, scores eight rows at a time with interleaved butterflies, lane t keeps score t - and the 128 outputs go straight into
+ * every peer's att[]: no partial records, no fold, no block barrier.  kvs holds all earlier rows [0, pos) of K then V. */
+__device__ __forceinline__ void cl_attention_small(cg::cluster_group &cl, const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int hh,
+                                                   const float *qkv, float *att, const float *kvs, const float *aux) {
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x, kvd = lm.kv_heads * 128, n = pos + 1, cap = a.att_cap;
+    const float4 c4 = reinterpret_cast<const float4 *>(aux)[lane], s4 = reinterpret_cast<const float4 *>(aux + 128)[lane];
+    const float4 q4 = cl_norm_rope(qkv + hh * 128, aux + 256, c4, s4, lm.eps);
+    const float4 k_new = cl_norm_rope(qkv + 256, aux + 384, c4, s4, lm.eps);
+    const float4 v_new = reinterpret_cast<const float4 *>(qkv + 384)[lane];
+    if (hh == 0) {
+        float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
+        const size_t off = kv_off(a.table, pos, kvd);
+        *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
+        *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
+    }
+    const float *Ks = kvs, *Vs = kvs + cap * 128;
+    const float scale = 0.08838834764831845f;
+    float sc = -3.402823466e+38f;
+    for (int tb = 0; tb < n; tb += 8) {
+        float d[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int t = tb + u;
+            float4 kr = make_float4(0, 0, 0, 0);
+            if (t < pos) kr = *reinterpret_cast<const float4 *>(Ks + (size_t)t * 128 + lane * 4);
+            else if (t == pos) kr = k_new;
+            d[u] = dot4(q4, kr);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float t8[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) t8[u] = __shfl_xor_sync(0xffffffffu, d[u], o);
+#pragma unroll
+            for (int u = 0; u < 8; u++) d[u] += t8[u];
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) if (lane == tb + u && tb + u < n) sc = d[u] * scale;
+    }
+    const float mx = warp_max(sc);
+    const float e = lane < n ? __expf(sc - mx) : 0.0f;
+    const float tot = warp_sum(e);
+    float4 o4 = make_float4(0, 0, 0, 0);
+    for (int t = 0; t < n; t++) {
+        const float pr = __shfl_sync(0xffffffffu, e, t);
+        const float4 vr = t < pos ? *reinterpret_cast<const float4 *>(Vs + (size_t)t * 128 + lane * 4) : v_new;
+        o4.x = fmaf(pr, vr.x, o4.x); o4.y = fmaf(pr, vr.y, o4.y); o4.z = fmaf(pr, vr.z, o4.z); o4.w = fmaf(pr, vr.w, o4.w);
+    }
+    const float inv = __fdividef(1.0f, tot);
+    const float4 r4 = make_float4(o4.x * inv, o4.y * inv, o4.z * inv, o4.w * inv);
+#pragma unroll
+    for (int k = 0; k < CL_SIZE; k++) *reinterpret_cast<float4 *>(cl.map_shared_rank(att, k) + hh * 128 + lane * 4) = r4;
 }
 
-/* every CTA folds the 8 CTA partials of both heads for itself, straight out of its peers' shared memory: thread (head, dim)
- * reads 8 x (max, sum, out[dim]) - no push, no third cluster barrier */
-__device__ __forceinline__ void cl_attention_combine(cg::cluster_group &cl, float *cpart, float *att) {
+/* every CTA folds the 8 CTA records of both heads (pushed into its table cpart[rank][head] by the peers) for itself */
+__device__ __forceinline__ void cl_attention_combine(const float *cpart, float *att) {
     const int tid = threadIdx.x;
     if (tid < 256) {
         const int hh = tid >> 7, d = tid & 127;
         float m[CL_SIZE], lsum[CL_SIZE], o[CL_SIZE];
 #pragma unroll
         for (int k = 0; k < CL_SIZE; k++) {
-            const float *rp = cl.map_shared_rank(cpart, k) + hh * CL_REC;
+            const float *rp = cpart + (size_t)(k * 2 + hh) * CL_REC;
             m[k] = rp[0]; lsum[k] = rp[1]; o[k] = rp[4 + d];
         }
         float M = m[0];
@@ -341,7 +407,7 @@ __device__ __forceinline__ void cl_attention_combine(cg::cluster_group &cl, floa
             L = fmaf(lsum[k], f, L);
             acc = fmaf(o[k], f, acc);
         }
-        att[hh * 128 + d] = acc / L;
+        att[hh * 128 + d] = __fdividef(acc, L);
     }
     __syncthreads();
 }
@@ -371,12 +437,12 @@ __device__ __forceinline__ void cl_prefetch_paced(const void *base, size_t bytes
     }
 }
 
-/* dynamic shared memory (floats): [ xs (= dp in the second half of phase B) | qkv 512 | att 256 | cpart 2 x 132 | wpart 16 x 2 x 132 | g 64 |
+/* dynamic shared memory (floats): [ xs (= dp in the second half of phase B) | qkv 512 | att 256 | cpart 8 x 2 x 132 | wpart 16 x 2 x 132 | fold factors 64 | g 64 |
  * aux 512 | in_norm H | post_norm H | kv stage 2 x att_cap x 128 ]; the in-kernel sampler's workspace overlays aux.. (sampling happens
  * between steps; only this CTA writes there).  Kept small on purpose: shared memory is carved out of the SM's 228 KB and what is left is L1, whose size bounds
  * the loads an SM keeps in flight - measured: +17 KB of shared memory (a 132 -> 164 KB carve-out) cost the talker step 12 %. */
 __host__ __device__ inline int cl_smem_floats(int xs_floats, int H, int att_cap) {
-    return xs_floats + 512 + 256 + 2 * CL_REC + CL_WARPS * 2 * CL_REC + 64 + 512 + 2 * H + 2 * att_cap * 128;
+    return xs_floats + 512 + 256 + CL_SIZE * 2 * CL_REC + CL_WARPS * 2 * CL_REC + 64 + 64 + 512 + 2 * H + 2 * att_cap * 128;
 }
 __device__ __forceinline__ void cl_cp16(float *dst_smem, const float *src) {
     const uint32_t sa = (uint32_t)__cvta_generic_to_shared(dst_smem);
@@ -400,8 +466,8 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     const int rank = (int)cl.block_rank(), g = cta / CL_SIZE;
     const int H = lm.hidden, I = lm.inter, L = lm.layers;
     const bool att_cluster = g < lm.kv_heads;           /* this cluster owns a KV head in phase A */
-    float *sm = cl_smem, *qkv = sm + a.xs_floats, *att = qkv + 512, *cpart = att + 256, *wpart = cpart + 2 * CL_REC;
-    float *gs = wpart + CL_WARPS * 2 * CL_REC, *dp = sm, *aux = gs + 64, *nin = aux + 512, *npost = nin + H, *kvs = npost + H;
+    float *sm = cl_smem, *qkv = sm + a.xs_floats, *att = qkv + 512, *cpart = att + 256, *wpart = cpart + CL_SIZE * 2 * CL_REC;
+    float *gs = wpart + CL_WARPS * 2 * CL_REC + 64, *dp = sm, *aux = gs + 64, *nin = aux + 512, *npost = nin + H, *kvs = npost + H;
     SampleSmem &S_samp = *reinterpret_cast<SampleSmem *>(aux);      /* 17.2 KB over aux | in_norm | post_norm | kv stage: regions only this CTA writes (peers push into qkv) */
     const int pos_base = *a.pos_ptr + a.pos_add;
     int p = *a.phase;                                   /* phase counter mod 3 */
@@ -453,11 +519,13 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
 #define PROF(i) do { if (a.prof && tid == 0 && l == a.prof_layer) a.prof[cta * 32 + (i)] = clock64(); } while (0)
     for (int gstep = 0; gstep < nsteps; gstep++) {
         const int pos = pos_base + gstep;
-        const int n = pos + 1, chunk = (n + CL_SIZE - 1) / CL_SIZE;
-        int t0 = rank * chunk, t1 = t0 + chunk < n ? t0 + chunk : n;
+        const int n = pos + 1;
+        const bool small_att = n <= 32 && n - 1 <= a.att_cap;      /* ranks 0 / 1 take a whole head each, one warp */
+        const int chunk = small_att ? n : (n + CL_SIZE - 1) / CL_SIZE;
+        int t0 = small_att ? 0 : rank * chunk, t1 = small_att ? (rank < 2 ? n : 0) : (t0 + chunk < n ? t0 + chunk : n);
         if (t0 > n) t0 = n;
         if (t1 < t0) t1 = t0;
-        const bool staged = chunk <= a.att_cap;
+        const bool staged = small_att || chunk <= a.att_cap;
         if (sp.G == 0) stage_phase_a(0, pos, t0, t1, staged);
         const float *x_in = a.x;                        /* fp32 input of layer 0 */
         if (sp.G > 0 && gstep >= 1 && sp.ptab[gstep - 1]) {
@@ -521,27 +589,28 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 cl.sync();
                 PROF(3);
-                cl_attention(a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
+                if (small_att) { if (rank < 2) cl_attention_small(cl, a, lm, l, g, pos, rank, qkv, att, kvs, aux); }
+                else cl_attention(cl, a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
                 /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
                 const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
                 uint4 ow[8];
 #pragma unroll
-                for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(warp + CL_WARPS * i) * 256) + lane);
+                for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(warp * 8 + i) * 256) + lane);
                 PROF(4);
                 cl.sync();
                 PROF(5);
-                cl_attention_combine(cl, cpart, att);
+                if (!small_att) cl_attention_combine(cpart, att);
                 if (a.flags & 8) cl.sync();                             /* experiment: the third cluster barrier of the push variant */
                 PROF(6);
                 const float4 a0v = reinterpret_cast<const float4 *>(att)[2 * lane], a1v = reinterpret_cast<const float4 *>(att)[2 * lane + 1];
                 uint4 ow2[8];                                           /* H = 2048: rows 128..255 of this CTA, requested before the first eight are reduced */
 #pragma unroll
                 for (int i = 0; i < 8; i++)
-                    ow2[i] = CL_PIPE && RPC > 8 * CL_WARPS ? ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(8 * CL_WARPS + warp + CL_WARPS * i) * 256) + lane) : make_uint4(0, 0, 0, 0);
+                    ow2[i] = CL_PIPE && RPC > 8 * CL_WARPS ? ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(8 * CL_WARPS + warp * 8 + i) * 256) + lane) : make_uint4(0, 0, 0, 0);
                 auto o_batch = [&](const uint4 (&wv)[8], int rb) {
                     long long resid = 0;
                     if (g == 0 && lane < 8) {
-                        const int row = rank * RPC + rb + warp + CL_WARPS * lane;
+                        const int row = rank * RPC + rb + warp * 8 + lane;
                         resid = l == 0 ? to_fx(__ldcg(x_in + row)) : __ldcg(xin + row);
                     }
                     float acc[8];
@@ -555,15 +624,18 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
 #pragma unroll
                         for (int i = 0; i < 8; i++) acc[i] += t8[i];
                     }
+                    if (rb == 0) PROF(23);
 #pragma unroll
                     for (int i = 0; i < 8; i++)
-                        if (lane == i) red_add_s64(xmid + rank * RPC + rb + warp + CL_WARPS * i, to_fx(acc[i]) + resid);
+                        if (lane == i && !(a.flags & 32)) red_add_s64(xmid + rank * RPC + rb + warp * 8 + i, to_fx(acc[i]) + resid);
                 };
+                PROF(20);
                 o_batch(ow, 0);
+                PROF(21);
                 if (RPC > 8 * CL_WARPS) {
 #if !CL_PIPE
 #pragma unroll
-                    for (int i = 0; i < 8; i++) ow2[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(8 * CL_WARPS + warp + CL_WARPS * i) * 256) + lane);
+                    for (int i = 0; i < 8; i++) ow2[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(8 * CL_WARPS + warp * 8 + i) * 256) + lane);
 #endif
                     o_batch(ow2, 8 * CL_WARPS);
                 }

@@ -355,6 +355,7 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
     a.att_cap = (((reach + CL_SIZE - 1) / CL_SIZE + 15) / 16) * 16;
     if (a.att_cap > CL_ATT_CAP) a.att_cap = CL_ATT_CAP;
     if (a.att_cap < 16) a.att_cap = 16;
+    if (b != &c->tk && reach <= 64 && a.att_cap < 32) a.att_cap = 32;      /* the sub-talker: ranks 0 / 1 stage every earlier row (one warp per head) */
     while (prog && (size_t)(512 + 2 * lm->hidden + 2 * a.att_cap * 128) * 4 < sizeof(SampleSmem)) a.att_cap += 16;   /* the sampler's workspace overlays aux.. */
     const size_t smem = (size_t)cl_smem_floats(a.xs_floats, lm->hidden, a.att_cap) * 4;
     if (smem > (size_t)g_cluster_max_smem) { qtc_set_error("cluster step: %zu bytes of shared memory needed, %d available", smem, g_cluster_max_smem); return -1; }

@@ -44,6 +44,11 @@ def main():
         if i in (0, 6) or (1 <= i <= 5):
             pass
         print(f"  {name:34s} {rows.min():7.2f} {np.median(rows):7.2f} {rows.max():7.2f}")
+    for nm, a_, b_ in (("attn: q/k norm + rope", 3, 16), ("attn: scores + softmax + V", 16, 17), ("attn: records + block barrier", 17, 18), ("attn: fold warps", 18, 22), ("attn: push records to peers", 22, 19),
+                       ("attn: request O rows", 19, 4), ("O: request batch 2 + att load", 6, 20), ("O: batch 1 dots + butterflies", 20, 23), ("O: batch 1 convert + atomics", 23, 21), ("O: batch 2", 21, 7)):
+        if raw[att, b_].any() and raw[att, a_].any():
+            dd = (raw[att, b_] - raw[att, a_]) / 1.965e3
+            print(f"    [{nm:30s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
     idle = ~att
     if idle.any():
         w = (raw[idle, 8] - raw[idle, 0]) / 1.965e3
