@@ -569,6 +569,9 @@ def main():
                 "clocks": sampler.summary()}
         if batched is not None:
             line["batched"] = batched
+        cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+        line["upload"] = {"ms": perf.upload_ms, "gb": perf.upload_bytes / 1e9, "gb_per_s": perf.upload_bytes / 1e6 / max(perf.upload_ms, 1e-9),
+                          "note": "qwen_tts_cuda_upload: model from pageable host memory through pinned staging, incl. device-side re-layouts (untimed setup)"}
         if not args.no_cpu and world == 1:
             rtf_cpu, dt = cpu_baseline_sample(hm, spec, main_t, frames=1)
             line["cpu_baseline"] = {"value": rtf_cpu, "unit": "audio_s/s", "cores": os.cpu_count(), "kind": "port",

@@ -180,6 +180,7 @@ typedef struct {
     long long device_mallocs;   /* cudaMalloc calls since upload returned: workspaces grown on first use; 0 in steady state */
     long long kv_page_allocs;   /* pages handed out by the pool's free list so far */
     int    kv_pool_pages, kv_pages_in_use;
+    double upload_ms, upload_bytes;   /* qwen_tts_cuda_upload: wall time and bytes copied host -> device (pinned staging) */
 } qtc_perf_t;
 
 /* streamed PCM: called as chunks land in host memory (see qwen_tts_cuda_set_stream_callback) */
@@ -327,6 +328,10 @@ double qwen_tts_cuda_subtalker_frame_bytes(const qtc_ctx_t *ctx);
 /* per-phase SM-clock stamps of the fused talker step (layer `layer`, KV position `pos`): 16 slots per CTA,
  * out[num_sms*16]; returns the CTA count.  Evidence for profiles/, not part of the reference's interface. */
 int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *ctx, int pos, int layer, long long *out);
+/* 16-bit PCM of the last decode (qwen_tts_cuda_generate / codec_decode), converted on the device exactly as the reference's WAV
+ * writer does on the host (c/qwen_tts_audio.c:70-82: clamp to [-1, 1], times 32767.0f, truncate) - half the device-to-host bytes
+ * of the float PCM.  Returns the samples written (<= max_samples) or -1. */
+int qwen_tts_cuda_last_pcm_s16(qtc_ctx_t *ctx, int16_t *out, int max_samples);
 /* mode 2 (cluster kernel) diagnostics: *capacity = 16-CTA clusters the device holds at once (-1 before the first mode-2 step;
  * mode 2 needs kv_heads of them), *gave_up = 1 if a grid-barrier wait of that kernel ever hit its spin bound.  No reference counterpart. */
 int qwen_tts_cuda_cluster_status(qtc_ctx_t *ctx, int *capacity, int *gave_up);

@@ -6,6 +6,7 @@
  */
 #include "qtc_internal.h"
 
+#include <chrono>
 #include <math.h>
 #include <stdarg.h>
 #include <strings.h>
@@ -60,11 +61,79 @@ void *qtc_dmalloc(qtc_ctx *c, size_t bytes) {
     c->allocs.push_back(p);
     return p;
 }
+/* ---- load path ---------------------------------------------------------------------------------
+ * The reference hands over pageable host pointers (mmap'ed safetensors, malloc'ed f32 copies: c/qwen_tts.c:481-489, 604-769).
+ * A cudaMemcpy from such memory is synchronous and staged by the driver in small pieces; here tensors go through three 32 MB
+ * pinned buffers: up to four host threads copy a piece into a pinned buffer (page faults of an mmap'ed file included) while
+ * the previous pieces are on the wire (cudaMemcpyAsync on a blocking stream, so later null-stream kernels - the weight
+ * re-layouts - order after them).  Upload time and bytes are reported in qtc_perf_t. */
+#include <thread>
+struct Uploader {
+    static const int NBUF = 3;
+    static const size_t BUF = 32u << 20;
+    char *pin[NBUF] = {NULL, NULL, NULL};
+    cudaEvent_t ev[NBUF];
+    cudaStream_t stream = NULL;
+    int next = 0;
+    bool ok = false;
+    double bytes = 0;
+    bool init() {
+        if (ok) return true;
+        if (cudaStreamCreate(&stream) != cudaSuccess) return false;
+        for (int i = 0; i < NBUF; i++)
+            if (cudaMallocHost(&pin[i], BUF) != cudaSuccess || cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess) return false;
+        ok = true;
+        return true;
+    }
+    static void host_copy(char *dst, const char *src, size_t n) {
+        const int nt = n >= (8u << 20) ? 4 : 1;
+        if (nt == 1) { memcpy(dst, src, n); return; }
+        std::thread th[4];
+        const size_t per = ((n / nt) + 4095) & ~(size_t)4095;
+        for (int t = 0; t < nt; t++) {
+            const size_t lo = per * t, hi = lo + per < n ? lo + per : n;
+            th[t] = std::thread([=]() { if (hi > lo) memcpy(dst + lo, src + lo, hi - lo); });
+        }
+        for (int t = 0; t < nt; t++) th[t].join();
+    }
+    bool copy(void *dev, const void *host, size_t n) {
+        if (!init()) return false;
+        const char *src = (const char *)host;
+        char *dst = (char *)dev;
+        for (size_t off = 0; off < n; off += BUF) {
+            const size_t nb = n - off < BUF ? n - off : BUF;
+            const int b = next;
+            next = (next + 1) % NBUF;
+            if (cudaEventSynchronize(ev[b]) != cudaSuccess) return false;      /* the buffer's previous piece is on the device */
+            host_copy(pin[b], src + off, nb);
+            if (cudaMemcpyAsync(dst + off, pin[b], nb, cudaMemcpyHostToDevice, stream) != cudaSuccess) return false;
+            cudaEventRecord(ev[b], stream);
+        }
+        bytes += (double)n;
+        return true;
+    }
+    bool finish() { return !ok || cudaStreamSynchronize(stream) == cudaSuccess; }
+    void release() {
+        if (!ok) return;
+        cudaStreamSynchronize(stream);
+        for (int i = 0; i < NBUF; i++) { cudaFreeHost(pin[i]); cudaEventDestroy(ev[i]); pin[i] = NULL; }
+        cudaStreamDestroy(stream);
+        ok = false;
+    }
+};
+static Uploader g_up;
 template <class T> T *qtc_upload(qtc_ctx *c, const T *host, size_t n) {
     if (!host || n == 0) return NULL;
     T *d = (T *)qtc_dmalloc(c, n * sizeof(T));
     if (!d) return NULL;
-    if (cudaMemcpy(d, host, n * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) { qtc_set_error("H2D copy of %zu bytes failed", n * sizeof(T)); return NULL; }
+    static int plain = -1;
+    if (plain < 0) { const char *e = getenv("QTC_UPLOAD_PLAIN"); plain = e ? atoi(e) : 0; }      /* A/B: the synchronous pageable copy */
+    if (plain) {
+        if (cudaMemcpy(d, host, n * sizeof(T), cudaMemcpyHostToDevice) != cudaSuccess) { qtc_set_error("H2D copy of %zu bytes failed", n * sizeof(T)); return NULL; }
+        g_up.bytes += (double)(n * sizeof(T));
+        return d;
+    }
+    if (!g_up.copy(d, host, n * sizeof(T))) { qtc_set_error("H2D copy of %zu bytes failed: %s", n * sizeof(T), cudaGetErrorString(cudaGetLastError())); return NULL; }
     return d;
 }
 template float *qtc_upload<float>(qtc_ctx *, const float *, size_t);
@@ -124,7 +193,7 @@ extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     cudaFree(c->codes); cudaFree(c->trailing); cudaFree(c->prefill);
     cudaFreeHost(c->state_host); cudaFreeHost(c->codes_host); cudaFreeHost(c->host_stage);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
-    cudaFree(c->pcm_dev); cudaFreeHost(c->first_pcm_host);
+    cudaFree(c->pcm_dev); cudaFreeHost(c->first_pcm_host); cudaFree(c->s16_dev);
     for (cudaEvent_t e : c->frame_ev) cudaEventDestroy(e);
     for (cudaEvent_t e : c->chunk_ev) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream); cudaStreamDestroy(c->stream2);
@@ -135,6 +204,8 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     if (g_device < 0) { qtc_set_error("upload before qwen_tts_cuda_init"); return NULL; }
     if (!desc) { qtc_set_error("null model descriptor"); return NULL; }
     qtc_ctx *c = new qtc_ctx();
+    const auto t_up0 = std::chrono::steady_clock::now();
+    g_up.bytes = 0;
     c->host = *desc;
     c->H = desc->talker.hidden; c->G = desc->num_code_groups; c->max_batch = max_batch > 0 ? max_batch : 1;
     c->bb = NULL; c->pf = NULL; c->batch_pieces = 3; c->dev_mallocs = 0;
@@ -156,6 +227,7 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     c->codes_host = NULL;
     c->cstream = c->stream;
     { const char *e = getenv("QTC_CODEC_TC"); c->codec_tc = e ? atoi(e) : 1; }
+    c->last_pcm_dev = NULL; c->last_pcm_n = 0; c->s16_dev = NULL; c->s16_cap = 0;
     c->pcm_dev = NULL; c->pcm_cap = 0; c->first_pcm_host = NULL; c->stream_first = 8; c->stream_chunk = 0;      /* decode at the end unless qwen_tts_cuda_set_streaming asks for chunks */ c->stream_cb = NULL; c->stream_user = NULL;
     if (!ok) { qtc_set_error("stream/event/pinned allocation failed"); qwen_tts_cuda_release(c); return NULL; }
     if (c->G < 1 || c->G > QTC_MAX_GROUPS) { qtc_set_error("num_code_groups %d out of range", c->G); qwen_tts_cuda_release(c); return NULL; }
@@ -225,7 +297,10 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
         c->codec = qtc_codec_upload(c, &desc->codec);
         if (!c->codec) { qwen_tts_cuda_release(c); return NULL; }
     }
-    if (cudaDeviceSynchronize() != cudaSuccess) { qtc_set_error("upload: device error"); qwen_tts_cuda_release(c); return NULL; }
+    if (!g_up.finish() || cudaDeviceSynchronize() != cudaSuccess) { qtc_set_error("upload: device error"); qwen_tts_cuda_release(c); return NULL; }
+    g_up.release();                                   /* 96 MB of pinned memory are not kept after the model is resident */
+    c->perf.upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_up0).count();
+    c->perf.upload_bytes = g_up.bytes;
     c->dev_mallocs = 0;           /* from here on every cudaMalloc is counted (qtc_perf_t.device_mallocs) */
     return c;
 }

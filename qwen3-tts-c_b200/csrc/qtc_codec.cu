@@ -307,6 +307,7 @@ static void stream_free(CodecDev *d) {
 
 /* start a decode of up to max_frames frames (one-shot decodes are a session of one chunk) */
 int qtc_codec_stream_begin(qtc_ctx *c, int max_frames) {
+    c->last_pcm_dev = NULL; c->last_pcm_n = 0;        /* the workspace is about to be reused */
     CodecDev *d = c->codec;
     if (!d || max_frames <= 0) { qtc_set_error("codec stream: no codec / bad frame count"); return -1; }
     const qtc_codec_t *k = &d->h;
@@ -587,7 +588,34 @@ float *qtc_codec_decode_dev(qtc_ctx *c, const int *codes_dev, int T, int *out_sa
     }
     *out_samples = L;
     if (dev_out) *dev_out = wav;
+    c->last_pcm_dev = wav; c->last_pcm_n = L;
     return host;
+}
+
+/* c/qwen_tts_audio.c:70-82 on the device: clamp to [-1, 1], s * 32767.0f (one rounding), truncate toward zero */
+__global__ void k_pcm_to_s16(int16_t *out, const float *in, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = in[i];
+    if (s > 1.0f) s = 1.0f;
+    if (s < -1.0f) s = -1.0f;
+    out[i] = (int16_t)__float2int_rz(__fmul_rn(s, 32767.0f));
+}
+extern "C" int qwen_tts_cuda_last_pcm_s16(qtc_ctx_t *c, int16_t *out, int max_samples) {
+    if (!c || !out || max_samples <= 0) { qtc_set_error("last_pcm_s16: null or empty argument"); return -1; }
+    if (!c->last_pcm_dev || c->last_pcm_n <= 0) { qtc_set_error("last_pcm_s16: no one-shot decode to convert (a streamed decode keeps no device copy of the utterance)"); return -1; }
+    const int n = c->last_pcm_n < max_samples ? c->last_pcm_n : max_samples;
+    if ((size_t)n > c->s16_cap) {
+        cudaFree(c->s16_dev); c->s16_dev = NULL; c->s16_cap = 0;
+        QTC_COUNT_MALLOC(c);
+        if (cudaMalloc(&c->s16_dev, (size_t)n * 2 + 4096) != cudaSuccess) { qtc_set_error("last_pcm_s16: device buffer"); return -1; }
+        c->s16_cap = (size_t)n + 2048;
+    }
+    k_pcm_to_s16<<<(n + 255) / 256, 256, 0, c->cstream>>>(c->s16_dev, c->last_pcm_dev, n);
+    c->launches++;
+    QTC_CUDA(cudaMemcpyAsync(out, c->s16_dev, (size_t)n * 2, cudaMemcpyDeviceToHost, c->cstream));
+    QTC_CUDA(cudaStreamSynchronize(c->cstream));
+    return n;
 }
 
 /* ---- streaming through the C ABI (host buffers): SURVEY.md 8f rank 3 ------------------------------------------------ */

@@ -174,6 +174,8 @@ struct qtc_ctx {
     long long launches;
     /* streamed decode inside generate: PCM of the whole utterance on the device, chunk schedule, per-frame / per-chunk events */
     float *pcm_dev; size_t pcm_cap;          /* [frames * samples_per_frame] */
+    const float *last_pcm_dev; int last_pcm_n;   /* PCM of the last one-shot decode, still in the codec workspace (qwen_tts_cuda_last_pcm_s16) */
+    int16_t *s16_dev; size_t s16_cap;
     float *first_pcm_host;                   /* pinned landing buffer of the streamed PCM (pcm_cap bytes); chunks are handed on from it */
     int stream_first, stream_chunk;          /* frames in the first chunk / in later chunks; stream_chunk <= 0: decode once at the end */
     qtc_pcm_callback_t stream_cb; void *stream_user;

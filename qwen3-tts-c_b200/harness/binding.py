@@ -96,7 +96,8 @@ class Perf(C.Structure):
                 ("device_ms", C.c_double), ("ttff_ms", C.c_double), ("ttfa_ms", C.c_double),
                 ("frame_ms_p50", C.c_double), ("frame_ms_p99", C.c_double),
                 ("device_mallocs", C.c_longlong), ("kv_page_allocs", C.c_longlong),
-                ("kv_pool_pages", C.c_int), ("kv_pages_in_use", C.c_int)]
+                ("kv_pool_pages", C.c_int), ("kv_pages_in_use", C.c_int),
+                ("upload_ms", C.c_double), ("upload_bytes", C.c_double)]
 
 
 PcmCallback = C.CFUNCTYPE(None, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p)
@@ -162,6 +163,7 @@ def load_cuda():
     lib.qwen_tts_cuda_rms_norm.argtypes = [f32p, f32p, f32p, C.c_int, C.c_float]
     lib.qwen_tts_cuda_sample_top_k.argtypes = [f32p, C.c_int, C.c_int, C.c_float, C.c_float, f32p]
     lib.qwen_tts_cuda_sample_top_k_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.qwen_tts_cuda_last_pcm_s16.argtypes = [vp, C.c_void_p, C.c_int]
     lib.qwen_tts_cuda_causal_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 6
     lib.qwen_tts_cuda_transposed_conv1d.argtypes = [f32p, f32p, f32p, f32p] + [C.c_int] * 5 + [i32p]
     lib.qwen_tts_cuda_snake_beta.argtypes = [f32p, f32p, f32p, f32p, C.c_int, C.c_int]
