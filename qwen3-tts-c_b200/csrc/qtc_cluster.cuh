@@ -330,61 +330,87 @@ __device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const Cluste
 }
 #undef APROF
 
-/* Contexts of at most 32 positions (every sub-talker step): the whole head in ONE warp of CTA rank hh (0 / 1) - lane i owns dims
- * 4i..4i+3, scores eight rows at a time with interleaved butterflies, lane t keeps score t - and the 128 outputs go straight into
- * every peer's att[]: no partial records, no fold, no block barrier.  kvs holds all earlier rows [0, pos) of K then V. */
+/* Contexts of at most 32 positions (every sub-talker step): the whole head in ONE warp of CTA rank hh (0 / 1), and the 128 outputs
+ * go straight into every peer's att[]: no partial records, no fold, no block barrier.  The warp's latency chain is kept short:
+ * the q and k norms run as one interleaved butterfly, scores are position-parallel (lane t takes the whole 128-wide dot product of
+ * position t against q in shared memory - K rows are staged with a 132-float stride so that the lanes' rows fall into different
+ * banks - instead of 40 shuffles per eight positions), V rows are weighted with lane-owns-4-dims.  kvs: rows [0, pos) of K, then V. */
+#define CL_KST_SMALL 132
 __device__ __forceinline__ void cl_attention_small(cg::cluster_group &cl, const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int hh,
-                                                   const float *qkv, float *att, const float *kvs, const float *aux) {
+                                                   const float *qkv, float *att, const float *kvs, const float *aux, float *scr) {
     if (threadIdx.x >= 32) return;
+#define SPROF(i) do { if (a.prof && threadIdx.x == 0 && l == a.prof_layer) a.prof[blockIdx.x * 32 + (i)] = clock64(); } while (0)
+    SPROF(24);
     const int lane = threadIdx.x, kvd = lm.kv_heads * 128, n = pos + 1, cap = a.att_cap;
+    float *qs = scr, *ks = scr + 128;
     const float4 c4 = reinterpret_cast<const float4 *>(aux)[lane], s4 = reinterpret_cast<const float4 *>(aux + 128)[lane];
-    const float4 q4 = cl_norm_rope(qkv + hh * 128, aux + 256, c4, s4, lm.eps);
-    const float4 k_new = cl_norm_rope(qkv + 256, aux + 384, c4, s4, lm.eps);
+    const float4 qv = reinterpret_cast<const float4 *>(qkv + hh * 128)[lane], kv = reinterpret_cast<const float4 *>(qkv + 256)[lane];
+    const float4 qn = reinterpret_cast<const float4 *>(aux + 256)[lane], kn = reinterpret_cast<const float4 *>(aux + 384)[lane];
     const float4 v_new = reinterpret_cast<const float4 *>(qkv + 384)[lane];
+    float sq = dot4(qv, qv), sk = dot4(kv, kv);
+    warp_sum2(sq, sk);
+    const float iq = rsqrtf(sq * 0.0078125f + lm.eps), ik = rsqrtf(sk * 0.0078125f + lm.eps);
+    const float4 qy = make_float4(qv.x * iq * qn.x, qv.y * iq * qn.y, qv.z * iq * qn.z, qv.w * iq * qn.w);
+    const float4 ky = make_float4(kv.x * ik * kn.x, kv.y * ik * kn.y, kv.z * ik * kn.z, kv.w * ik * kn.w);
+    const float sgn = lane < 16 ? -1.0f : 1.0f;          /* rotate-half: first half y cos - partner sin, second half y cos + partner sin */
+    float4 q4, k_new;
+    {
+        const float qx = __shfl_xor_sync(0xffffffffu, qy.x, 16), qyy = __shfl_xor_sync(0xffffffffu, qy.y, 16);
+        const float qz = __shfl_xor_sync(0xffffffffu, qy.z, 16), qw = __shfl_xor_sync(0xffffffffu, qy.w, 16);
+        const float kx = __shfl_xor_sync(0xffffffffu, ky.x, 16), kyy = __shfl_xor_sync(0xffffffffu, ky.y, 16);
+        const float kz = __shfl_xor_sync(0xffffffffu, ky.z, 16), kw = __shfl_xor_sync(0xffffffffu, ky.w, 16);
+        q4 = make_float4(fmaf(sgn * qx, s4.x, qy.x * c4.x), fmaf(sgn * qyy, s4.y, qy.y * c4.y), fmaf(sgn * qz, s4.z, qy.z * c4.z), fmaf(sgn * qw, s4.w, qy.w * c4.w));
+        k_new = make_float4(fmaf(sgn * kx, s4.x, ky.x * c4.x), fmaf(sgn * kyy, s4.y, ky.y * c4.y), fmaf(sgn * kz, s4.z, ky.z * c4.z), fmaf(sgn * kw, s4.w, ky.w * c4.w));
+    }
+    reinterpret_cast<float4 *>(qs)[lane] = q4;
+    reinterpret_cast<float4 *>(ks)[lane] = k_new;
     if (hh == 0) {
         float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
         const size_t off = kv_off(a.table, pos, kvd);
         *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
         *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
     }
+    __syncwarp();
+    SPROF(25);
     const float *Ks = kvs, *Vs = kvs + cap * 128;
-    const float scale = 0.08838834764831845f;
     float sc = -3.402823466e+38f;
-    for (int tb = 0; tb < n; tb += 8) {
-        float d[8];
-#pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const int t = tb + u;
-            float4 kr = make_float4(0, 0, 0, 0);
-            if (t < pos) kr = *reinterpret_cast<const float4 *>(Ks + (size_t)t * 128 + lane * 4);
-            else if (t == pos) kr = k_new;
-            d[u] = dot4(q4, kr);
+    if (lane < n) {
+        const float4 *kr = reinterpret_cast<const float4 *>(lane < pos ? Ks + (size_t)lane * CL_KST_SMALL : ks), *q4p = reinterpret_cast<const float4 *>(qs);
+        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+#pragma unroll 8
+        for (int c = 0; c < 32; c++) {
+            const float4 kk = kr[c], qq = q4p[c];
+            a0 = fmaf(kk.x, qq.x, a0); a1 = fmaf(kk.y, qq.y, a1); a2 = fmaf(kk.z, qq.z, a2); a3 = fmaf(kk.w, qq.w, a3);
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            float t8[8];
-#pragma unroll
-            for (int u = 0; u < 8; u++) t8[u] = __shfl_xor_sync(0xffffffffu, d[u], o);
-#pragma unroll
-            for (int u = 0; u < 8; u++) d[u] += t8[u];
-        }
-#pragma unroll
-        for (int u = 0; u < 8; u++) if (lane == tb + u && tb + u < n) sc = d[u] * scale;
+        sc = ((a0 + a1) + (a2 + a3)) * 0.08838834764831845f;
     }
+    SPROF(26);
     const float mx = warp_max(sc);
     const float e = lane < n ? __expf(sc - mx) : 0.0f;
     const float tot = warp_sum(e);
+    SPROF(27);
     float4 o4 = make_float4(0, 0, 0, 0);
-    for (int t = 0; t < n; t++) {
-        const float pr = __shfl_sync(0xffffffffu, e, t);
-        const float4 vr = t < pos ? *reinterpret_cast<const float4 *>(Vs + (size_t)t * 128 + lane * 4) : v_new;
-        o4.x = fmaf(pr, vr.x, o4.x); o4.y = fmaf(pr, vr.y, o4.y); o4.z = fmaf(pr, vr.z, o4.z); o4.w = fmaf(pr, vr.w, o4.w);
+    for (int tb = 0; tb < n; tb += 8) {                  /* eight rows requested before the first is used: the loop was one shuffle -> load -> FMA chain per row */
+        float pr[8];
+        float4 vr[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int t = tb + u;
+            pr[u] = __shfl_sync(0xffffffffu, e, t & 31);
+            vr[u] = t < pos ? *reinterpret_cast<const float4 *>(Vs + (size_t)t * 128 + lane * 4) : v_new;
+            if (t >= n) pr[u] = 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; u++) { o4.x = fmaf(pr[u], vr[u].x, o4.x); o4.y = fmaf(pr[u], vr[u].y, o4.y); o4.z = fmaf(pr[u], vr[u].z, o4.z); o4.w = fmaf(pr[u], vr[u].w, o4.w); }
     }
+    SPROF(28);
     const float inv = __fdividef(1.0f, tot);
     const float4 r4 = make_float4(o4.x * inv, o4.y * inv, o4.z * inv, o4.w * inv);
 #pragma unroll
     for (int k = 0; k < CL_SIZE; k++) *reinterpret_cast<float4 *>(cl.map_shared_rank(att, k) + hh * 128 + lane * 4) = r4;
+    SPROF(29);
 }
+#undef SPROF
 
 /* every CTA folds the 8 CTA records of both heads (pushed into its table cpart[rank][head] by the peers) for itself */
 __device__ __forceinline__ void cl_attention_combine(const float *cpart, float *att) {
@@ -491,7 +517,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
      * the CTA waits at the grid barrier before it: the K/V rows of this CTA's position range, the RoPE row, the head norms and the
      * input norm's weights.  (Read on demand, each of these was a DRAM round trip on the critical path: the 2.8 GB streamed per
      * step evict them from L2 every time.) */
-    auto stage_phase_a = [&](int ll, int pos, int t0, int t1, bool staged) {
+    auto stage_phase_a = [&](int ll, int pos, int t0, int t1, bool staged, int kst) {
         const LmLayerDev &wl = lm.layer[ll];
         if (att_cluster) {
             if (staged && t1 > t0) {
@@ -500,7 +526,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 const int rows = (t1 < pos ? t1 : pos) - t0;
                 for (int i = tid; i < rows * 64; i += CL_THREADS) {
                     const int which = i >= rows * 32, j = which ? i - rows * 32 : i, r = j >> 5, c = j & 31;
-                    cl_cp16(kvs + (size_t)which * a.att_cap * 128 + r * 128 + c * 4, (which ? vc : kc) + kv_off(a.table, t0 + r, kvd) + c * 4);
+                    cl_cp16(kvs + (size_t)which * a.att_cap * 128 + r * (which ? 128 : kst) + c * 4, (which ? vc : kc) + kv_off(a.table, t0 + r, kvd) + c * 4);
                 }
             }
 #if CL_STAGE_AUX
@@ -520,13 +546,14 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     for (int gstep = 0; gstep < nsteps; gstep++) {
         const int pos = pos_base + gstep;
         const int n = pos + 1;
-        const bool small_att = n <= 32 && n - 1 <= a.att_cap;      /* ranks 0 / 1 take a whole head each, one warp */
+        const bool small_att = n <= 32 && (n - 1) * CL_KST_SMALL <= a.att_cap * 128;      /* ranks 0 / 1 take a whole head each, one warp */
+        const int kst = small_att ? CL_KST_SMALL : 128;    /* K row stride in the stage */
         const int chunk = small_att ? n : (n + CL_SIZE - 1) / CL_SIZE;
         int t0 = small_att ? 0 : rank * chunk, t1 = small_att ? (rank < 2 ? n : 0) : (t0 + chunk < n ? t0 + chunk : n);
         if (t0 > n) t0 = n;
         if (t1 < t0) t1 = t0;
         const bool staged = small_att || chunk <= a.att_cap;
-        if (sp.G == 0) stage_phase_a(0, pos, t0, t1, staged);
+        if (sp.G == 0) stage_phase_a(0, pos, t0, t1, staged, kst);
         const float *x_in = a.x;                        /* fp32 input of layer 0 */
         if (sp.G > 0 && gstep >= 1 && sp.ptab[gstep - 1]) {
             /* ST_PROJECT_INPUT by table: the projected embedding of every code was computed at upload, and every CTA knows the code it
@@ -535,7 +562,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             x_in = sp.ptab[gstep - 1] + (size_t)s_codes[gstep - 1] * H;
             head_w = sp.heads[gstep - 1];
             if (att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
-            stage_phase_a(0, pos, t0, t1, staged);
+            stage_phase_a(0, pos, t0, t1, staged, kst);
         } else if (sp.G > 0) {
             /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x (fp32, like the step's input) */
             __syncthreads();
@@ -554,7 +581,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             head_w = gstep >= 1 ? sp.heads[gstep - 1] : NULL;
             cl_barrier_arrive(a.bar, target, ncta);
             if (att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
-            stage_phase_a(0, pos, t0, t1, staged);
+            stage_phase_a(0, pos, t0, t1, staged, kst);
             cl_barrier_wait(a.bar, target, a.err);
         }
         for (int l = 0; l < L; l++) {
@@ -589,7 +616,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 cl.sync();
                 PROF(3);
-                if (small_att) { if (rank < 2) cl_attention_small(cl, a, lm, l, g, pos, rank, qkv, att, kvs, aux); }
+                if (small_att) { if (rank < 2) cl_attention_small(cl, a, lm, l, g, pos, rank, qkv, att, kvs, aux, wpart); }
                 else cl_attention(cl, a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
                 /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
                 const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
@@ -744,7 +771,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             PROF(13);
             cl_barrier_arrive(a.bar, target, ncta);
             if (l + 1 < L && att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[l + 1]));
-            if (l + 1 < L) stage_phase_a(l + 1, pos, t0, t1, staged);
+            if (l + 1 < L) stage_phase_a(l + 1, pos, t0, t1, staged, kst);
             cl_barrier_wait(a.bar, target, a.err);
             p++;
             PROF(14);

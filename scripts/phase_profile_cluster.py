@@ -49,6 +49,12 @@ def main():
         if raw[att, b_].any() and raw[att, a_].any():
             dd = (raw[att, b_] - raw[att, a_]) / 1.965e3
             print(f"    [{nm:30s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
+    sm = raw[:, 24] > 0
+    if sm.any():
+        for nm, a_, b_ in (("small attn: entry after sync", 3, 24), ("small attn: norms + rope + kv write", 24, 25), ("small attn: scores", 25, 26), ("small attn: softmax", 26, 27),
+                           ("small attn: V", 27, 28), ("small attn: push to peers", 28, 29)):
+            dd = (raw[sm, b_] - raw[sm, a_]) / 1.965e3
+            print(f"    [{nm:36s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
     idle = ~att
     if idle.any():
         w = (raw[idle, 8] - raw[idle, 0]) / 1.965e3
