@@ -616,7 +616,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 cl.sync();
                 PROF(3);
-                if (small_att) { if (rank < 2) cl_attention_small(cl, a, lm, l, g, pos, rank, qkv, att, kvs, aux, wpart); }
+                if (small_att) { if (rank < 2) { cl_attention_small(cl, a, lm, l, g, pos, rank, qkv, att, kvs, aux, wpart); __syncthreads(); } }   /* the other 15 warps park at bar.sync, not in the cluster barrier's wait */
                 else cl_attention(cl, a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
                 /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
                 const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
