@@ -143,3 +143,48 @@ def test_generate_batch_equals_per_utterance_oracle(cuda, orc, tiny):
         snr = 10 * np.log10((want_pcm.astype(np.float64) ** 2).sum() / max(err, 1e-300))
         assert snr >= 80.0, (b, snr)
     cuda.qwen_tts_cuda_release(ctx)
+
+
+def test_generate_batch_mixed_eos_equals_per_utterance_oracle(cuda, orc):
+    """no frame budget: the codec head's EOS row is scaled up so that the four utterances of the batch stop at different frames
+    (the oracle: 11, 4, 19 and 7) - rows that are done keep taking lock-step steps as no-ops until the slowest one ends; every
+    utterance's frame count and codes must equal the oracle's solo run with its seed (the all_done / stop handling)"""
+    _setup_batch_api(cuda)
+    spec = mg.PRESETS["tiny"]
+    main, cod = mg.build_tensors(spec, seed=0)
+    w = mg.bf16_to_f32(main["talker.codec_head.weight"]).copy()
+    w[mg.CODEC_IDS["codec_eos_token_id"]] *= 3.0
+    main["talker.codec_head.weight"] = mg.f32_to_bf16(w)
+    hm = B.HostModel(spec, main, cod)
+    G = spec["groups"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 4)
+    assert ctx
+    cap = 30
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.default_params(max_new_tokens=cap)))
+    base = list(FIXTURE_TOKENS)
+    prompts = [base, base[:4] + [2500, 31, 77] + base[4:], base[:9] + base[10:], base[:6] + [99] + base[6:]]
+    nb = len(prompts)
+    spk = np.full(nb, mg.SPEAKERS["aiden"], dtype=np.int32)
+    lang = np.full(nb, mg.LANGUAGES["english"], dtype=np.int32)
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    codes = np.zeros((nb, cap, G), dtype=np.int32)
+    nfr = np.zeros(nb, dtype=np.int32)
+    rc = cuda.qwen_tts_cuda_generate_batch(ctx, nb, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), None, cap)
+    assert rc == 0, cuda.qwen_tts_cuda_last_error()
+    want_n = []
+    for b in range(nb):
+        s = orc.orc_create(hm.desc)
+        orc.orc_set_params(s, C.byref(B.default_params(max_new_tokens=cap, sample_seed=42 + b)))
+        want = np.zeros((cap, G), dtype=np.int32)
+        ns, nf = C.c_int(0), C.c_int(0)
+        tk = np.array(prompts[b], dtype=np.int32)
+        ptr = orc.orc_generate(s, B.iptr(tk), len(tk), int(spk[b]), int(lang[b]), C.byref(ns), B.iptr(want), cap, C.byref(nf))
+        if ptr:
+            orc.orc_free(ptr)
+        orc.orc_destroy(s)
+        want_n.append(nf.value)
+        assert int(nfr[b]) == nf.value, (b, list(nfr), want_n)
+        assert np.array_equal(codes[b][: nf.value], want[: nf.value]), b
+    assert len(set(want_n)) > 2 and min(want_n) < cap, want_n       # the utterances really stop at different frames
+    cuda.qwen_tts_cuda_release(ctx)
