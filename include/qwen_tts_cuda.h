@@ -199,7 +199,10 @@ qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max_batch);  /
 void       qwen_tts_cuda_release(qtc_ctx_t *ctx);
 void       qwen_tts_cuda_set_params(qtc_ctx_t *ctx, const qtc_gen_params_t *p);
 void       qwen_tts_cuda_get_perf(const qtc_ctx_t *ctx, qtc_perf_t *out);
-/* 0: separate kernels per op (baseline)  1: fused persistent decode kernels (default) */
+/* 0: separate kernels per op (baseline)
+ * 1: one persistent 148-CTA kernel per decoder-stack step, five grid-wide exchanges per layer (round 1's path; fallback)
+ * 2 (default): the cluster kernel - 15 clusters of 8 CTAs, two grid-wide exchanges per layer - where the stack's geometry fits
+ *    (16 query / 8 KV heads of 128, hidden 1024 or 2048, enough 8-CTA clusters on the device); other stacks run mode 1 */
 int        qwen_tts_cuda_set_mode(qtc_ctx_t *ctx, int mode);
 /* Arithmetic of the talker / sub-talker path.
  * 0 (default): fp32 with FMA and tree reductions - weight-streaming speed; differs from the C path by
@@ -332,7 +335,7 @@ int qwen_tts_cuda_debug_phase_clocks(qtc_ctx_t *ctx, int pos, int layer, long lo
  * writer does on the host (c/qwen_tts_audio.c:70-82: clamp to [-1, 1], times 32767.0f, truncate) - half the device-to-host bytes
  * of the float PCM.  Returns the samples written (<= max_samples) or -1. */
 int qwen_tts_cuda_last_pcm_s16(qtc_ctx_t *ctx, int16_t *out, int max_samples);
-/* mode 2 (cluster kernel) diagnostics: *capacity = 16-CTA clusters the device holds at once (-1 before the first mode-2 step;
+/* mode 2 (cluster kernel) diagnostics: *capacity = 8-CTA clusters the device holds at once (-1 before the first mode-2 step;
  * mode 2 needs kv_heads of them), *gave_up = 1 if a grid-barrier wait of that kernel ever hit its spin bound.  No reference counterpart. */
 int qwen_tts_cuda_cluster_status(qtc_ctx_t *ctx, int *capacity, int *gave_up);
 const char *qwen_tts_cuda_last_error(void);
