@@ -795,7 +795,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             if (gstep == 1 && tid == 0) s_rng = sp.seed_bits;
             __syncthreads();
             /* flags & 64 (diagnostic): a fixed code instead of the sample, to time the sampler's share of the frame */
-            const int tok = (a.flags & 64) ? 1 : block_sample(lg, vv, V, sp.cfg.top_k, sp.cfg.top_p, sp.cfg.temperature, &s_rng, S_samp, sp.scratch_f, sp.scratch_i);
+            const int tok = (a.flags & 64) ? 1 : (a.flags & 128) ? block_sample(lg, vv, V, sp.cfg.top_k, sp.cfg.top_p, sp.cfg.temperature, &s_rng, S_samp, sp.scratch_f, sp.scratch_i) : block_sample_thr(lg, vv, V, sp.cfg.top_k, sp.cfg.top_p, sp.cfg.temperature, &s_rng, S_samp, sp.scratch_f, sp.scratch_i, a.prof ? a.prof + cta * 32 + 16 : NULL);
             if (tid == 0) { s_codes[gstep] = tok; if (cta == 0) sp.codes[gstep] = tok; }
         }
     }

@@ -49,6 +49,12 @@ def main():
         if raw[att, b_].any() and raw[att, a_].any():
             dd = (raw[att, b_] - raw[att, a_]) / 1.965e3
             print(f"    [{nm:30s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
+    if pos < 0 and raw[:, 16].any():
+        for nm, a_, b_ in (("sampler: scale + moments", 16, 17), ("sampler: threshold + gather", 17, 18), ("sampler: rank candidates", 18, 19), ("sampler: expf", 19, 20),
+                           ("sampler: sequential sum + walk", 20, 21), ("sampler: last barrier", 21, 22)):
+            dd = (raw[:, b_] - raw[:, a_]) / 1.965e3
+            print(f"    [{nm:36s}] {dd.min():7.2f} {np.median(dd):7.2f} {dd.max():7.2f}")
+        print(f"    [sampler: candidates] {raw[:, 23].min():.0f} .. {raw[:, 23].max():.0f}")
     sm = raw[:, 24] > 0
     if sm.any():
         for nm, a_, b_ in (("small attn: entry after sync", 3, 24), ("small attn: norms + rope + kv write", 24, 25), ("small attn: scores", 25, 26), ("small attn: softmax", 26, 27),
