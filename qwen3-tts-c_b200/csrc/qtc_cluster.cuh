@@ -309,13 +309,17 @@ __device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const Cluste
     if (tid < 256) {
         const int hh = tid >> 7, d = tid & 127;
         float M = -3.402823466e+38f;
+#pragma unroll 8
         for (int k = 0; k < nw; k++) M = fmaxf(M, wpart[(size_t)(k * 2 + hh) * CL_REC]);
         float L = 0.0f, o = 0.0f;
-        for (int k = 0; k < nw; k++) {
+#pragma unroll 8
+        for (int k = 0; k < nw; k++) {                     /* select, not branch: the loads of all records go out together */
             const float *r = wpart + (size_t)(k * 2 + hh) * CL_REC;
-            const float f = r[1] > 0.0f ? __expf(r[0] - M) : 0.0f;
-            L = fmaf(r[1], f, L);
-            o = fmaf(r[4 + d], f, o);
+            const float m = r[0], lw = r[1], ov = r[4 + d];
+            const float e = __expf(m - M);
+            const float f = lw > 0.0f ? e : 0.0f;
+            L = fmaf(lw, f, L);
+            o = fmaf(ov, f, o);
         }
         /* the CTA's record goes into every peer's table: after the cluster barrier each CTA folds the 8 records locally */
         float *mine = cpart + (size_t)(cl.block_rank() * 2 + hh) * CL_REC;
