@@ -41,10 +41,12 @@ template <int NP> struct TcCfg {
 /* EPI 0: Y += acc (fp32 reductions in L2, any K split).
  * EPI 1 (one K split only): the weight rows are gate/up interleaved (row 2u = gate u, 2u+1 = up u); the epilogue forms
  *        silu(gate.x) * (up.x) (c/qwen_tts_kernels.c:229-232) and stores it as bf16 pieces - the next GEMM's input - at
- *        xo[(p*64 + b) * (N/2) + u]: SwiGLU costs no kernel and no fp32 round trip. */
+ *        xo[(p*64 + b) * (N/2) + u]: SwiGLU costs no kernel and no fp32 round trip.
+ * EPI 2: K split s STORES its partial sums at Y + s * split_stride (plain stores, no pre-initialised Y): the consumer adds the
+ *        splits in a fixed order, so the result is bit-reproducible run to run (the batch-1 prefill, qtc_prefill.cuh). */
 template <int NP, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapX,
-                                                            float *Y, int N, int ldy, int kb_per_split, int nbatch, uint16_t *xo, int xo_pieces) {
+                                                            float *Y, int N, int ldy, int kb_per_split, int nbatch, uint16_t *xo, int xo_pieces, int split_stride) {
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
     typedef TcCfg<NP> Cfg;
     constexpr int TC_STAGES = Cfg::STAGES, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
@@ -141,6 +143,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant
 #pragma unroll
                     for (int j = 0; j < 16; j++)
                         if (c0 + j < nbatch) atomicAdd(Y + (size_t)(c0 + j) * ldy + row, acc[j]);
+                }
+            } else if (EPI == 2) {
+                if (row < N) {
+                    float *Ys = Y + (size_t)blockIdx.y * split_stride;
+#pragma unroll
+                    for (int j = 0; j < 16; j++)
+                        if (c0 + j < nbatch) Ys[(size_t)(c0 + j) * ldy + row] = acc[j];
                 }
             } else {
                 const int I = N >> 1, u = row >> 1;
@@ -245,15 +254,33 @@ int qtc_gemm_tc_ex(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint1
     if (swiglu_out && (N & 1)) { qtc_set_error("gemm_tc: interleaved gate/up needs an even row count"); return -1; }
     const dim3 grid(tiles, splits);
     if (swiglu_out) {
-        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
-        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces);
+        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces, 0);
+        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces, 0);
     } else {
-        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 0>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0);
-        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 0>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0);
+        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 0>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0, 0);
+        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 0>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0, 0);
     }
     c->launches++;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { qtc_set_error("gemm_tc launch -> %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
+/* K-split count qtc_gemm_tc_parts will use for a [N, K] weight matrix */
+int qtc_gemm_tc_splits(const qtc_ctx *c, int N, int K) { return pick_splits((N + TC_BM - 1) / TC_BM, K / TC_BK, c->num_sms); }
+/* parts[s][b, n] = sum over K split s of X[b, k] W[n, k] for s < qtc_gemm_tc_splits(c, N, K): split s at parts + s * split_stride,
+ * rows of ldy floats; three exact activation pieces; nothing is accumulated - every element of every split is stored. */
+int qtc_gemm_tc_parts(qtc_ctx *c, float *parts, int ldy, int split_stride, const uint16_t *X, const uint16_t *W, int nbatch, int N, int K) {
+    if (K % TC_BK || nbatch < 1 || nbatch > TC_BN) { qtc_set_error("gemm_tc_parts: K %% 64 != 0 or batch outside 1..64 (K=%d, batch=%d)", K, nbatch); return -1; }
+    static int attr = 0;
+    if (!attr) { QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3>::SMEM)); attr = 1; }
+    const CUtensorMap *mw = qtc_tmap_bf16(W, N, K, TC_BM), *mx = qtc_tmap_bf16(X, TC_BN * 3, K, TC_BN * 3);
+    if (!mw || !mx) return -1;
+    const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = pick_splits(tiles, kblocks, c->num_sms);
+    qtc_launch_pdl(c->stream, k_gemm_tc<3, 2>, dim3(tiles, splits), dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, parts, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0, split_stride);
+    c->launches++;
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { qtc_set_error("gemm_tc_parts launch -> %s", cudaGetErrorString(e)); return -1; }
     return 0;
 }
 

@@ -70,3 +70,38 @@ def test_fused_long_context_splits(cuda, orc, mode):
     assert cuda.qwen_tts_cuda_get_kv_len(ctx) == n_pre + n_steps
     orc.orc_destroy(s)
     cuda.qwen_tts_cuda_release(ctx)
+
+
+@pytest.mark.parametrize("n_pre", [1 + 15, 64, 65, 100], ids=["skinny16", "skinny64", "wide65", "wide100"])
+def test_prefill_both_gemm_paths_vs_oracle(cuda, orc, n_pre):
+    """Batched prefill (c/qwen_tts_talker.c:254-472): prompts of <= 64 rows go through the skinny tcgen05 GEMM (weights as the MMA's
+    128-row operand, K-split partial sums added in a fixed order), longer ones through the convolution kernel.  Either way the
+    hidden state of the last prompt token and the logits of the decode step that follows (which reads every K/V row the prefill
+    wrote) are within 2e-4 of the oracle's, and two runs agree bit for bit."""
+    hm = get_model(orc, "small")
+    H, V = hm.spec["talker"]["hidden"], hm.spec["talker"]["vocab"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
+    assert ctx, cuda.qwen_tts_cuda_last_error()
+    s = orc.orc_create(hm.desc)
+    emb = (np.random.default_rng(n_pre).standard_normal((n_pre + 1, H)) * 0.5).astype(np.float32)
+    orc.orc_reset(s)
+    orc.orc_talker_prefill(s, B.fptr(emb), n_pre)
+    want = np.zeros(V, dtype=np.float32)
+    want_hid = np.ctypeslib.as_array(orc.orc_hidden(s), shape=(H,)).copy()
+    orc.orc_talker_forward(s, B.fptr(emb[n_pre]), B.fptr(want))
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.greedy_params()))
+    runs = []
+    for _ in range(2):
+        cuda.qwen_tts_cuda_reset(ctx)
+        assert cuda.qwen_tts_cuda_talker_prefill(ctx, B.fptr(emb), n_pre) == 0, cuda.qwen_tts_cuda_last_error()
+        hid, got = np.zeros(H, dtype=np.float32), np.zeros(V, dtype=np.float32)
+        assert cuda.qwen_tts_cuda_get_hidden(ctx, B.fptr(hid)) == 0
+        assert cuda.qwen_tts_cuda_talker_forward(ctx, B.fptr(emb[n_pre]), B.fptr(got)) == 0
+        assert np.abs(hid - want_hid).max() <= 2e-4 * np.abs(want_hid).max()
+        assert np.abs(got - want).max() <= 5e-4 * np.abs(want).max()
+        assert int(got.argmax()) == int(want.argmax())
+        runs.append((hid, got))
+    assert np.array_equal(runs[0][0].view(np.uint32), runs[1][0].view(np.uint32))
+    assert np.array_equal(runs[0][1].view(np.uint32), runs[1][1].view(np.uint32))
+    orc.orc_destroy(s)
+    cuda.qwen_tts_cuda_release(ctx)
