@@ -181,6 +181,7 @@ typedef struct {
     long long kv_page_allocs;   /* pages handed out by the pool's free list so far */
     int    kv_pool_pages, kv_pages_in_use;
     double upload_ms, upload_bytes;   /* qwen_tts_cuda_upload: wall time and bytes copied host -> device (pinned staging) */
+    int    queue_admitted;      /* qwen_tts_cuda_generate_queue: utterances admitted into a row (the first `rows` at the start, the others into freed rows) */
 } qtc_perf_t;
 
 /* streamed PCM: called as chunks land in host memory (see qwen_tts_cuda_set_stream_callback) */
@@ -279,6 +280,19 @@ int  qwen_tts_cuda_generate_batch(qtc_ctx_t *ctx, int batch,
                                   const int *speaker_ids, const int *language_ids,
                                   int *out_codes, int *out_n_frames,
                                   float *pcm_out, int max_tokens);
+/* Continuous batching over the same lock-step rows: n_utt utterances queue for `rows` <= 64 rows (<= the max_batch of
+ * qwen_tts_cuda_upload).  The reference stops an utterance at EOS (c/qwen_tts.c:1324-1330) and is batch 1; in a lock-step
+ * batch utterances end at different frames, so a row whose utterance has ended is retired at the next poll (every 8 frames;
+ * with fixed_codec_tokens exactly at the budget): its codes are saved, its KV pages return to the pool's free list, and the
+ * next queued utterance is admitted into the row (pages reserved again, prompt built and prefilled on its own, per-row
+ * state / RNG / repetition history reset) while the other rows are mid-utterance.  Utterance u uses seed
+ * params.sample_seed + u and produces what it produces alone.  Buffers as for generate_batch with n_utt in place of batch.
+ * Needs fast arithmetic (the default). */
+int  qwen_tts_cuda_generate_queue(qtc_ctx_t *ctx, int n_utt, int rows,
+                                  const int *token_ids, const int *offsets,
+                                  const int *speaker_ids, const int *language_ids,
+                                  int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens);
+
 /* activations of the batched GEMMs: 3 = exact split of every fp32 value into three bf16 pieces (default: results differ
  * from the batch-1 fast path by summation order only), 1 = rounded to bf16 (logits within 1e-2 relative) */
 int  qwen_tts_cuda_set_batch_pieces(qtc_ctx_t *ctx, int pieces);

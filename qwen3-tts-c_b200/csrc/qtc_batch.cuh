@@ -294,6 +294,14 @@ __global__ void k_b_sub_input(float *out, const float *hidden, const uint16_t *t
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Hin; i += gridDim.x * blockDim.x)
         out[(size_t)b * Hin + i] = table ? bf16_to_f32(table[(size_t)codes[(size_t)b * code_stride + code_idx] * Hin + i]) : hidden[(size_t)b * Hin + i];
 }
+/* sub-talker input of position g >= 1 by table (qtc_build_proj_tables: the projected embedding of every code, computed at upload):
+ * x[b, :] = ptab[code of utterance b at position g - 1] - one gather instead of gather + pieces + bias rows + a GEMM */
+__global__ void k_b_sub_input_tab(float *x, const float *ptab, const int *codes, int code_stride, int code_idx, int h) {
+    pdl_enter();
+    const int b = blockIdx.y;
+    const float4 *src = reinterpret_cast<const float4 *>(ptab + (size_t)codes[(size_t)b * code_stride + code_idx] * h);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < (h >> 2); i += gridDim.x * blockDim.x) reinterpret_cast<float4 *>(x + (size_t)b * h)[i] = src[i];
+}
 /* y[b, i] = bias[i] (or 0): initial value of a GEMM output that accumulates */
 __global__ void k_b_init_rows(float *y, const float *bias, int n) {
     pdl_enter();
@@ -333,6 +341,8 @@ struct BatchBuf {
     float *trailing; int trailing_cap; /* [B, trailing_cap, H] */
     uint32_t *sub_rng;            /* [B] */
     uint32_t *seeds;              /* [B] bit pattern of (float)(sample_seed + b): RNG seed of utterance b */
+    float *pcm_all = NULL; size_t pcm_cap = 0;   /* PCM of up to 64 decoded utterances, [.., max_tokens * 1920], on its way to the host */
+    int *qcodes = NULL; size_t qcodes_cap = 0;   /* generate_queue: codes of retired utterances [n_utt, limit, G], kept for the decode at the end */
     float *scratch_f; int *scratch_i;  /* slow-path sampler scratch [B, vocab] */
     cudaGraphExec_t g_front, g_talker;
     int graph_key, graph_B;
@@ -520,6 +530,12 @@ static int b_subtalker(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_tab
     if (set_smem_attrs()) return -1;
     for (int g = 0; g < G; g++) {
         const uint16_t *table = g == 0 ? NULL : (g == 1 ? c->codec_embedding : c->sub_emb[g - 2]);
+        static int use_tab = -1;
+        if (use_tab < 0) { const char *e = getenv("QTC_BATCH_PTAB"); use_tab = e ? atoi(e) : 1; }
+        if (g >= 1 && use_tab && c->sub_ptab[g - 1] && h % 4 == 0) {
+            qtc_launch_pdl(c->stream, k_b_sub_input_tab, dim3(dim3((h / 4 + 255) / 256, B)), dim3(256), 0, bb->st.x, c->sub_ptab[g - 1], (const int *)bb->frame_codes, G, g - 1, h);
+            BLAUNCH(c);
+        } else {
         qtc_launch_pdl(c->stream, k_b_sub_input, dim3(dim3((H + 255) / 256, B)), dim3(256), 0, bb->sub_in, bb->hidden, table, bb->frame_codes, G, g > 0 ? g - 1 : 0, H);
         BLAUNCH(c);
         if (c->sub_in_w) {
@@ -531,6 +547,7 @@ static int b_subtalker(qtc_ctx *c, BatchBuf *bb, int B, const uint32_t *seed_tab
         } else {
             qtc_launch_pdl(c->stream, k_b_copy_pad_rows, dim3(dim3((h + 255) / 256, B)), dim3(256), 0, bb->st.x, bb->sub_in, H < h ? H : h, h);
             BLAUNCH(c);
+        }
         }
         if (b_lm_step(c, bb, lm, &bb->st, &c->st, B, NULL, g, NULL, g >= 1 ? c->sub_head[g - 1] : NULL, lm->vocab)) return -1;
         if (g >= 1) {
@@ -601,6 +618,43 @@ static int b_capture(qtc_ctx *c, cudaGraphExec_t *out, int which, int B, long lo
 static int b_pull_state(qtc_ctx *c, BatchBuf *bb, int B) {
     QTC_CUDA(cudaMemcpyAsync(bb->state_host, bb->state, (size_t)B * sizeof(GenState), cudaMemcpyDeviceToHost, c->stream));
     QTC_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+/* codec decode of `count` finished utterances (codes on the device, `codes_stride` ints apart, nfr[u] frames each) into
+ * pcm_out [count, max_tokens * 1920] (host): the decodes are enqueued back to back on the codec stream, each one's PCM parked
+ * in a device-side stash, and the stash goes to the host once per 64 utterances - no host round trip between two decodes
+ * (a decode of 250 frames is ~440 short launches: with a synchronise, a malloc and a pageable copy after every utterance the
+ * device idled between them). */
+static int b_decode_all(qtc_ctx *c, BatchBuf *bb, int count, const int *codes_base, size_t codes_stride, const int *nfr, float *pcm_out, int max_tokens) {
+    const size_t per = (size_t)max_tokens * 1920;
+    std::vector<int> ns(count, 0);
+    for (int lo = 0; lo < count; lo += BROWS) {
+        const int hi = lo + BROWS < count ? lo + BROWS : count;
+        const size_t need = (size_t)(hi - lo) * per;
+        if (bb->pcm_cap < need) {
+            bb->pcm_all = (float *)balloc(bb, need * 4);
+            if (!bb->pcm_all) { bb->pcm_cap = 0; return -1; }
+            bb->pcm_cap = need; c->dev_mallocs++;
+            QTC_CUDA(cudaDeviceSynchronize());           /* balloc clears on the NULL stream */
+        }
+        for (int u = lo; u < hi; u++) {
+            if (nfr[u] <= 0) continue;
+            float *wav = NULL;
+            if (qtc_codec_stream_begin(c, nfr[u])) return -1;
+            const int L = qtc_codec_stream_push(c, codes_base + (size_t)u * codes_stride, nfr[u], &wav);
+            if (L <= 0 || (size_t)L > per) { if (L > 0) qtc_set_error("batch decode: %d samples for a slot of %zu", L, per); return -1; }
+            QTC_CUDA(cudaMemcpyAsync(bb->pcm_all + (size_t)(u - lo) * per, wav, (size_t)L * 4, cudaMemcpyDeviceToDevice, c->cstream));
+            ns[u] = L;
+        }
+        cudaEventRecord(c->ev3, c->cstream);             /* end of device work; what follows is the D2H of the PCM */
+        bool full = true;
+        for (int u = lo; u < hi; u++) full = full && (size_t)ns[u] == per;
+        if (full) QTC_CUDA(cudaMemcpyAsync(pcm_out + (size_t)lo * per, bb->pcm_all, need * 4, cudaMemcpyDeviceToHost, c->cstream));
+        else for (int u = lo; u < hi; u++) if (ns[u] > 0) QTC_CUDA(cudaMemcpyAsync(pcm_out + (size_t)u * per, bb->pcm_all + (size_t)(u - lo) * per, (size_t)ns[u] * 4, cudaMemcpyDeviceToHost, c->cstream));
+        QTC_CUDA(cudaStreamSynchronize(c->cstream));
+    }
+    c->last_pcm_dev = NULL; c->last_pcm_n = 0;
     return 0;
 }
 
@@ -725,15 +779,9 @@ extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *
     c->perf.talker_ms = ms; c->perf.codec_tokens = total_frames;
     if (pcm_out) {
         if (!c->codec) { qtc_set_error("generate_batch: context has no codec weights"); return -1; }
-        for (int b = 0; b < B; b++) {
-            const int n = bb->state_host[b].step;
-            if (n <= 0) continue;
-            int ns = 0;
-            float *pcm = qtc_codec_decode_dev(c, bb->codes + (size_t)b * bb->codes_cap * G, n, &ns, NULL);
-            if (!pcm) return -1;
-            memcpy(pcm_out + (size_t)b * max_tokens * 1920, pcm, (size_t)ns * 4);
-            free(pcm);
-        }
+        std::vector<int> nfr(B);
+        for (int b = 0; b < B; b++) nfr[b] = bb->state_host[b].step;
+        if (b_decode_all(c, bb, B, bb->codes, (size_t)bb->codes_cap * G, nfr.data(), pcm_out, max_tokens)) return -1;
         float dms = 0;
         cudaEventElapsedTime(&dms, c->ev2, c->ev3);
         c->perf.device_ms = dms;
@@ -742,6 +790,180 @@ extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *
         cudaEventElapsedTime(&dms, c->ev2, c->ev1);
         c->perf.device_ms = dms;
     }
+    return 0;
+}
+
+/* ---- continuous batching: a queue of utterances through `rows` lock-step rows -------------------------------------------
+ * The reference is batch 1 (c/qwen_tts.h:8) and stops an utterance at EOS (c/qwen_tts.c:1324-1330); in a lock-step batch the
+ * utterances stop at different frames and qwen_tts_cuda_generate_batch keeps the finished rows as no-ops until the slowest ends.
+ * Here a row whose utterance has ended is RETIRED at the next poll (every 8 frames; with a fixed frame budget exactly when the
+ * first row's budget ends): its codes are saved, its KV pages go back to the pool's free list, and the next utterance of the
+ * queue is ADMITTED into the row - pages reserved, prompt built, prefilled on its own (qtc_prefill.cuh, KV rows straight into
+ * the row's pages), frame-0 logits from the codec head, per-row state / RNG / repetition history reset - while the other rows
+ * are mid-utterance.  Rows never see each other, so utterance u (seed sample_seed + u) produces what it produces alone. */
+__global__ void k_pf_fill_rows_imm(int *slot, int *pos, int R, int s, int base) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < R) { slot[r] = s; pos[r] = base + r; }
+}
+#define QTC_Q_POLL 8
+#define QTC_Q_PARKED (-(1 << 30))         /* position of a row with no utterance: negative = every kernel skips it, and 2^30 steps stay negative */
+extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, const int *token_ids, const int *offsets, const int *speaker_ids,
+                                            const int *language_ids, int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens) {
+    if (!c || c->talker.layers <= 0) { qtc_set_error("generate_queue: context has no talker weights"); return -1; }
+    if (n_utt < 1 || rows < 1 || rows > BROWS || !token_ids || !offsets || !out_codes || max_tokens < 1) { qtc_set_error("generate_queue: rows must be 1..64 and buffers non-null"); return -1; }
+    if (c->talker.hidden % 64 || c->talker.inter % 64 || (c->talker.heads * c->talker.head_dim) % 64 || c->sub.hidden % 64 || c->sub.inter % 64 ||
+        (c->sub.heads * c->sub.head_dim) % 64) { qtc_set_error("generate_queue: model dimensions must be multiples of 64"); return -1; }
+    if (!(pf_ok(c) && prefill_gemm_on())) { qtc_set_error("generate_queue: needs fast arithmetic and the GEMM prefill (a row is prefilled on its own while the others are mid-utterance)"); return -1; }
+    const int B = rows < n_utt ? rows : n_utt, H = c->H, G = c->G, V = c->talker.vocab;
+    if (B > c->kv.slots) { qtc_set_error("generate_queue: %d rows, the context was uploaded with max_batch %d", B, c->kv.slots); return -1; }
+    const int fixed = c->params.fixed_codec_tokens > 0 ? c->params.fixed_codec_tokens : 0;
+    int limit = fixed > 0 ? fixed : c->params.max_new_tokens;
+    if (limit > max_tokens) limit = max_tokens;
+    int max_tr = 1;
+    const int max_plen = 10;
+    for (int u = 0; u < n_utt; u++) {
+        const int n = offsets[u + 1] - offsets[u];
+        if (n < 8) { qtc_set_error("generate_queue: utterance %d has %d token ids, need >= 8", u, n); return -1; }
+        if (n - 8 > max_tr) max_tr = n - 8;
+    }
+    /* a row that ends between two polls keeps stepping until the poll: its pages cover those positions too */
+    const int kv_need = max_plen + limit + QTC_Q_POLL + 4;
+    if (batch_ensure(c, B, kv_need, limit, max_plen + 3, max_tr + 1)) return -1;
+    BatchBuf *bb = c->bb;
+    if (pcm_out && !c->codec) { qtc_set_error("generate_queue: context has no codec weights"); return -1; }
+    if (pcm_out && bb->qcodes_cap < (size_t)n_utt * limit * G) {          /* finished utterances' codes wait on the device for the decode at the end */
+        bb->qcodes_cap = (size_t)n_utt * limit * G;
+        bb->qcodes = (int *)balloc(bb, bb->qcodes_cap * 4);
+        if (!bb->qcodes) return -1;
+        c->dev_mallocs++;
+    }
+    cudaEventRecord(c->ev2, c->stream);
+    std::vector<int> row_utt(B, -1), row_end(B, 0), pos_host(B, QTC_Q_PARKED), nframes(n_utt, 0);
+    std::vector<uint32_t> seed_host(B, 0);
+    int frame_now = 0, next_u = 0, admitted = 0;
+    /* the next utterances of the queue -> the rows in `free_rows` (as many as there are of both); their prompts are prefilled
+     * together as ONE ragged pass.  Everything is enqueued on c->stream behind the frames already launched. */
+    std::vector<int> hs, hp, plen(B, 0), ntr(B, 0);
+    auto admit = [&](const std::vector<int> &free_rows) -> int {
+        std::vector<int> rows_in;
+        for (int b : free_rows) {
+            if (next_u >= n_utt) break;
+            const int u = next_u++;
+            KvPool &kp = c->kv;
+            for (int i = kp.used[b] - 1; i >= 0; i--) kp.free_pages.push_back(kp.tables_host[(size_t)b * kp.max_seq_pages + i]);
+            kp.used[b] = 0;
+            if (qtc_kv_reserve(c, b, kv_need)) return -1;
+            const int spk = speaker_ids ? speaker_ids[u] : -1, lang = language_ids ? language_ids[u] : -1;
+            if (qtc_build_prompt_dev(c, token_ids + offsets[u], offsets[u + 1] - offsets[u], spk, lang, bb->prefill + (size_t)b * bb->prefill_cap * H, &plen[b],
+                                     bb->trailing + (size_t)b * bb->trailing_cap * H, &ntr[b], c->tts_pad)) return -1;
+            row_utt[b] = u; row_end[b] = frame_now + limit; admitted++;
+            rows_in.push_back(b);
+        }
+        if (rows_in.empty()) return 0;
+        hs.clear(); hp.clear();
+        int maxlen = 0;
+        for (int b : rows_in) { for (int t = 0; t < plen[b]; t++) { hs.push_back(b); hp.push_back(t); } if (plen[b] > maxlen) maxlen = plen[b]; }
+        const int R = (int)hs.size();
+        if (pf_reserve(c, R)) return -1;
+        QTC_CUDA(cudaMemcpyAsync(c->pf->slot, hs.data(), (size_t)R * 4, cudaMemcpyHostToDevice, c->stream));
+        QTC_CUDA(cudaMemcpyAsync(c->pf->pos, hp.data(), (size_t)R * 4, cudaMemcpyHostToDevice, c->stream));
+        k_pf_gather_rows<<<dim3((H + 255) / 256, R), 256, 0, c->stream>>>(c->pf->x, bb->prefill, bb->prefill_cap, c->pf->slot, c->pf->pos, H);
+        BLAUNCH(c);
+        if (pf_run(c, R, maxlen - 1)) return -1;
+        int r_last = -1;
+        for (int b : rows_in) {
+            r_last += plen[b];
+            /* final norm -> the row's hidden (ctx->tk_x), codec head -> its logits of frame 0; the other rows' are left alone */
+            if (qtc_rmsnorm(c, bb->hidden + (size_t)b * H, c->pf->x + (size_t)r_last * H, c->talker.final_norm, H, c->talker.eps)) return -1;
+            GemvSeg hseg = {c->codec_head, bb->tk.logits + (size_t)b * V, V};
+            if (qtc_gemv(c, &hseg, 1, bb->hidden + (size_t)b * H, H, EPI_STORE, NULL)) return -1;
+            GenState s;
+            memset(&s, 0, sizeof(s));
+            const float f = (float)(c->params.sample_seed + row_utt[b]);
+            memcpy(&s.rng, &f, 4); memcpy(&seed_host[b], &f, 4);
+            s.limit = limit; s.fixed = fixed > 0; s.n_trailing = ntr[b]; s.stop_step = limit;
+            bb->state_host[b] = s;
+            pos_host[b] = plen[b];
+            QTC_CUDA(cudaMemcpyAsync(bb->state + b, bb->state_host + b, sizeof(GenState), cudaMemcpyHostToDevice, c->stream));
+            QTC_CUDA(cudaMemcpyAsync(bb->pos + b, &pos_host[b], 4, cudaMemcpyHostToDevice, c->stream));
+            QTC_CUDA(cudaMemcpyAsync(bb->seeds + b, &seed_host[b], 4, cudaMemcpyHostToDevice, c->stream));
+            QTC_CUDA(cudaMemsetAsync(bb->hist + (size_t)b * V, 0, (size_t)V * 4, c->stream));
+            QTC_CUDA(cudaMemsetAsync(bb->frame_codes + (size_t)b * G, 0, (size_t)G * 4, c->stream));
+        }
+        QTC_CUDA(cudaStreamSynchronize(c->stream));      /* the host-side staging (state_host, hs, hp, ...) is rewritten by the next poll */
+        return 0;
+    };
+    {
+        std::vector<int> all(B);
+        for (int b = 0; b < B; b++) all[b] = b;
+        if (admit(all)) return -1;
+    }
+    const int key = b_params_key(c, B);
+    if (bb->graph_key != key || bb->graph_B != B || !bb->g_front || !bb->g_talker) {
+        if (b_capture(c, &bb->g_front, 0, B, &bb->n_front) || b_capture(c, &bb->g_talker, 1, B, &bb->n_talker)) return -1;
+        bb->graph_key = key; bb->graph_B = B;
+    }
+    QTC_CUDA(cudaEventRecord(c->ev0, c->stream));
+    std::vector<int> host_codes((size_t)bb->codes_cap * G);
+    int active = B, total_frames = 0;
+    long long guard = ((long long)n_utt / B + 2) * ((long long)limit + 2 * QTC_Q_POLL);      /* frames this call can need at most */
+    while (active > 0) {
+        int poll = QTC_Q_POLL;
+        if (fixed > 0) {                                  /* the host knows when the next row's budget ends */
+            poll = limit;
+            for (int b = 0; b < B; b++) if (row_utt[b] >= 0 && row_end[b] - frame_now < poll) poll = row_end[b] - frame_now;
+            if (poll < 1) poll = 1;
+        }
+        for (int i = 0; i < poll; i++, frame_now++) {
+            QTC_CUDA(cudaGraphLaunch(bb->g_front, c->stream));
+            QTC_CUDA(cudaGraphLaunch(bb->g_talker, c->stream));
+            c->launches += bb->n_front + bb->n_talker;
+        }
+        if ((guard -= poll) < 0) { qtc_set_error("generate_queue: the frame loop ran past its bound"); return -1; }
+        if (b_pull_state(c, bb, B)) return -1;
+        std::vector<int> freed;
+        for (int b = 0; b < B; b++) {
+            const int u = row_utt[b];
+            if (u < 0 || !bb->state_host[b].done) continue;
+            /* retire: codes to the caller (and to the device-side stash for the decode at the end) */
+            const int n = bb->state_host[b].step;
+            nframes[u] = n; total_frames += n;
+            if (out_n_frames) out_n_frames[u] = n;
+            if (n > 0) {
+                QTC_CUDA(cudaMemcpy(host_codes.data(), bb->codes + (size_t)b * bb->codes_cap * G, (size_t)n * G * 4, cudaMemcpyDeviceToHost));
+                memcpy(out_codes + (size_t)u * max_tokens * G, host_codes.data(), (size_t)n * G * 4);
+                if (pcm_out) QTC_CUDA(cudaMemcpyAsync(bb->qcodes + (size_t)u * limit * G, bb->codes + (size_t)b * bb->codes_cap * G, (size_t)n * G * 4, cudaMemcpyDeviceToDevice, c->stream));
+            }
+            row_utt[b] = -1;
+            freed.push_back(b);
+        }
+        if (admit(freed)) return -1;
+        bool parked = false;
+        for (int b : freed) {
+            if (row_utt[b] >= 0) continue;               /* took a new utterance */
+            active--;
+            pos_host[b] = QTC_Q_PARKED;
+            QTC_CUDA(cudaMemcpyAsync(bb->pos + b, &pos_host[b], 4, cudaMemcpyHostToDevice, c->stream));
+            parked = true;
+        }
+        if (parked) QTC_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    QTC_CUDA(cudaEventRecord(c->ev1, c->stream));
+    QTC_CUDA(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->perf.talker_ms = ms; c->perf.codec_tokens = total_frames;
+    if (pcm_out) {
+        if (b_decode_all(c, bb, n_utt, bb->qcodes, (size_t)limit * G, nframes.data(), pcm_out, max_tokens)) return -1;
+        float dms = 0;
+        cudaEventElapsedTime(&dms, c->ev2, c->ev3);
+        c->perf.device_ms = dms;
+    } else {
+        float dms = 0;
+        cudaEventElapsedTime(&dms, c->ev2, c->ev1);
+        c->perf.device_ms = dms;
+    }
+    c->perf.queue_admitted = admitted;
     return 0;
 }
 

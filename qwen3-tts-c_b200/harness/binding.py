@@ -97,7 +97,7 @@ class Perf(C.Structure):
                 ("frame_ms_p50", C.c_double), ("frame_ms_p99", C.c_double),
                 ("device_mallocs", C.c_longlong), ("kv_page_allocs", C.c_longlong),
                 ("kv_pool_pages", C.c_int), ("kv_pages_in_use", C.c_int),
-                ("upload_ms", C.c_double), ("upload_bytes", C.c_double)]
+                ("upload_ms", C.c_double), ("upload_bytes", C.c_double), ("queue_admitted", C.c_int)]
 
 
 PcmCallback = C.CFUNCTYPE(None, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p)
@@ -158,6 +158,7 @@ def load_cuda():
     lib.qwen_tts_cuda_codec_stream_begin.argtypes = [vp, C.c_int]
     lib.qwen_tts_cuda_codec_stream_push.argtypes = [vp, i32p, C.c_int, f32p]
     lib.qwen_tts_cuda_generate_batch.argtypes = [vp, C.c_int, i32p, i32p, i32p, i32p, i32p, i32p, f32p, C.c_int]
+    lib.qwen_tts_cuda_generate_queue.argtypes = [vp, C.c_int, C.c_int, i32p, i32p, i32p, i32p, i32p, i32p, f32p, C.c_int]
     lib.qwen_tts_cuda_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_swiglu_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_rms_norm.argtypes = [f32p, f32p, f32p, C.c_int, C.c_float]

@@ -42,6 +42,7 @@ def _setup_batch_api(cuda):
     cuda.qwen_tts_cuda_batch_subtalker.argtypes = [C.c_void_p, C.c_int, B.f32p, B.i32p, B.i32p]
     cuda.qwen_tts_cuda_set_batch_pieces.argtypes = [C.c_void_p, C.c_int]
     cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+    cuda.qwen_tts_cuda_generate_queue.argtypes = [C.c_void_p, C.c_int, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
 
 
 @pytest.mark.parametrize("pieces,tol", [(3, 2e-4), (1, 1e-2)])
@@ -187,4 +188,102 @@ def test_generate_batch_mixed_eos_equals_per_utterance_oracle(cuda, orc):
         assert int(nfr[b]) == nf.value, (b, list(nfr), want_n)
         assert np.array_equal(codes[b][: nf.value], want[: nf.value]), b
     assert len(set(want_n)) > 2 and min(want_n) < cap, want_n       # the utterances really stop at different frames
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def _queue_prompts(n):
+    base = list(FIXTURE_TOKENS)
+    variants = [base, base[:4] + [2500, 31, 77] + base[4:], base[:9] + base[10:], base[:6] + [99] + base[6:],
+                base[:5] + [1234, 4321] + base[5:], base[:8] + base[9:], base[:7] + [555, 556, 557, 558] + base[7:],
+                base[:3] + [42] + base[3:], base[:10] + [7, 8] + base[10:]]
+    return [variants[i % len(variants)] + ([] if i < len(variants) else [100 + i]) for i in range(n)]
+
+
+def _oracle_solo(orc, desc, params, prompt, spk, lang, cap, G):
+    s = orc.orc_create(desc)
+    orc.orc_set_params(s, C.byref(params))
+    want = np.zeros((cap, G), dtype=np.int32)
+    ns, nf = C.c_int(0), C.c_int(0)
+    tk = np.array(prompt, dtype=np.int32)
+    ptr = orc.orc_generate(s, B.iptr(tk), len(tk), spk, lang, C.byref(ns), B.iptr(want), cap, C.byref(nf))
+    pcm = B.take_floats(orc.orc_free, ptr, ns.value) if ptr else np.zeros(0, dtype=np.float32)
+    orc.orc_destroy(s)
+    return nf.value, want, pcm
+
+
+def test_generate_queue_admits_into_freed_rows_eos(cuda, orc):
+    """Continuous batching (qwen_tts_cuda_generate_queue): 9 utterances queue for 3 lock-step rows, no frame budget, the EOS row
+    of the codec head boosted so that utterances end at different frames.  A row whose utterance has ended is retired at the next
+    poll, its KV pages go back to the free list and the next utterance is admitted into it (prefilled on its own while the other
+    rows are mid-utterance).  Every utterance's frame count and codes equal the oracle's solo run with seed 42 + u."""
+    _setup_batch_api(cuda)
+    spec = mg.PRESETS["tiny"]
+    main, cod = mg.build_tensors(spec, seed=0)
+    w = mg.bf16_to_f32(main["talker.codec_head.weight"]).copy()
+    w[mg.CODEC_IDS["codec_eos_token_id"]] *= 3.0
+    main["talker.codec_head.weight"] = mg.f32_to_bf16(w)
+    hm = B.HostModel(spec, main, cod)
+    G = spec["groups"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 4)
+    assert ctx
+    cap, n_utt, rows = 30, 9, 3
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.default_params(max_new_tokens=cap)))
+    prompts = _queue_prompts(n_utt)
+    spk = np.full(n_utt, mg.SPEAKERS["aiden"], dtype=np.int32)
+    lang = np.full(n_utt, mg.LANGUAGES["english"], dtype=np.int32)
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    codes = np.zeros((n_utt, cap, G), dtype=np.int32)
+    nfr = np.full(n_utt, -1, dtype=np.int32)
+    perf0 = B.Perf()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf0))
+    rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, rows, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), None, cap)
+    assert rc == 0, cuda.qwen_tts_cuda_last_error()
+    perf = B.Perf()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    assert perf.queue_admitted == n_utt
+    assert perf.kv_page_allocs - perf0.kv_page_allocs >= n_utt      # every admission took its pages from the free list again
+    want_n = []
+    for u in range(n_utt):
+        nf, want, _ = _oracle_solo(orc, hm.desc, B.default_params(max_new_tokens=cap, sample_seed=42 + u), prompts[u], int(spk[u]), int(lang[u]), cap, G)
+        want_n.append(nf)
+        assert int(nfr[u]) == nf, (u, list(nfr), want_n)
+        assert np.array_equal(codes[u][:nf], want[:nf]), u
+    assert len(set(want_n)) > 2 and min(want_n) < cap, want_n       # the utterances really stop at different frames
+    cuda.qwen_tts_cuda_release(ctx)
+
+
+def test_generate_queue_fixed_budget_with_pcm(cuda, orc, tiny):
+    """the same with a fixed frame budget (rows retire together, the next wave is prefilled as one ragged pass) and PCM:
+    5 utterances through 2 rows, 6 frames each; codes equal the oracle's, waveform >= 80 dB; then a plain generate_batch on the
+    same context still equals the oracle (the queue leaves rows parked, the batch call re-arms them)"""
+    _setup_batch_api(cuda)
+    G = tiny.spec["groups"]
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 2)
+    assert ctx
+    frames, n_utt, rows = 6, 5, 2
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.default_params(fixed_codec_tokens=frames)))
+    prompts = _queue_prompts(n_utt)
+    spk = np.array([mg.SPEAKERS["aiden"], -1, mg.SPEAKERS["vivian"], mg.SPEAKERS["aiden"], -1], dtype=np.int32)
+    lang = np.array([mg.LANGUAGES["english"], mg.LANGUAGES["chinese"], -1, -1, mg.LANGUAGES["english"]], dtype=np.int32)
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    codes = np.zeros((n_utt, frames, G), dtype=np.int32)
+    nfr = np.zeros(n_utt, dtype=np.int32)
+    pcm = np.zeros((n_utt, frames * 1920), dtype=np.float32)
+    rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, rows, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), B.fptr(pcm), frames)
+    assert rc == 0, cuda.qwen_tts_cuda_last_error()
+    assert list(nfr) == [frames] * n_utt
+    wants = []
+    for u in range(n_utt):
+        nf, want, want_pcm = _oracle_solo(orc, tiny.desc, B.default_params(fixed_codec_tokens=frames, sample_seed=42 + u), prompts[u], int(spk[u]), int(lang[u]), frames, G)
+        wants.append(want)
+        assert nf == frames and np.array_equal(codes[u], want), (u, codes[u], want)
+        err = ((pcm[u].astype(np.float64) - want_pcm) ** 2).sum()
+        snr = 10 * np.log10((want_pcm.astype(np.float64) ** 2).sum() / max(err, 1e-300))
+        assert snr >= 80.0, (u, snr)
+    codes2 = np.zeros((2, frames, G), dtype=np.int32)
+    rc = cuda.qwen_tts_cuda_generate_batch(ctx, 2, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes2), B.iptr(nfr), None, frames)
+    assert rc == 0, cuda.qwen_tts_cuda_last_error()
+    assert np.array_equal(codes2[0], wants[0]) and np.array_equal(codes2[1], wants[1])
     cuda.qwen_tts_cuda_release(ctx)
