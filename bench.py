@@ -323,6 +323,81 @@ def run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch):
             "gpu_launches": r["gpu_launches"], "roofline": r["roofline"], "clocks": r["clocks"]}))
 
 
+def run_queue(args, cuda, ctx, spec, rank, world, local, dist, torch):
+    """`--queue N`: N requests per GPU with RAGGED lengths (uniform in [frames / 5, frames], fixed per request) through 64 lock-step rows.
+    Two arms over the same requests: continuous batching (qwen_tts_cuda_generate_queue: a row whose request ended takes the next one)
+    and lock-step batches of 64 (qwen_tts_cuda_generate_batch runs every row of a batch to the call's frame limit; only the
+    requested frames count as audio).  Codes + codec decode to PCM in both."""
+    G, frames, n_utt = spec["groups"], args.frames, args.queue
+    cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+    cuda.qwen_tts_cuda_generate_queue.argtypes = [C.c_void_p, C.c_int, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+    cuda.qwen_tts_cuda_set_batch_pieces.argtypes = [C.c_void_p, C.c_int]
+    assert cuda.qwen_tts_cuda_set_batch_pieces(ctx, args.pieces) == 0
+    cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.default_params(fixed_codec_tokens=frames, sample_seed=1000 * rank + 42)))
+    rng = np.random.default_rng(rank)
+    prompts = []
+    for _ in range(n_utt):
+        extra = [int(x) for x in rng.integers(1000, 5000, size=int(rng.integers(0, 24)))]
+        prompts.append(TOKENS[:4] + extra + TOKENS[4:])
+    budgets = rng.integers(max(1, frames // 5), frames + 1, size=n_utt).astype(np.int32)
+    toks = np.array(sum(prompts, []), dtype=np.int32)
+    offs = np.array([0] + list(np.cumsum([len(q) for q in prompts])), dtype=np.int32)
+    spk, lang = np.full(n_utt, mg.SPEAKERS["aiden"], dtype=np.int32), np.full(n_utt, mg.LANGUAGES["english"], dtype=np.int32)
+    codes, nfr = np.zeros((n_utt, frames, G), dtype=np.int32), np.zeros(n_utt, dtype=np.int32)
+    pcm = np.zeros((n_utt, frames * 1920), dtype=np.float32)
+    perf = B.Perf()
+
+    def queue_arm():
+        rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, 64, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(budgets), B.iptr(codes), B.iptr(nfr), B.fptr(pcm), frames)
+        if rc != 0 or not np.array_equal(nfr, budgets):
+            raise RuntimeError("generate_queue failed: " + cuda.qwen_tts_cuda_last_error().decode())
+
+    def lockstep_arm():
+        for lo, hi in shard.micro_batches(0, n_utt, 64):
+            sub = np.ascontiguousarray(toks[offs[lo]:offs[hi]]); so = np.ascontiguousarray(offs[lo:hi + 1] - offs[lo])
+            rc = cuda.qwen_tts_cuda_generate_batch(ctx, hi - lo, B.iptr(sub), B.iptr(so), B.iptr(spk[lo:hi].copy()), B.iptr(lang[lo:hi].copy()), B.iptr(codes[lo:hi]),
+                                                   B.iptr(nfr[lo:hi]), B.fptr(pcm[lo:hi]), frames)
+            if rc != 0:
+                raise RuntimeError("generate_batch failed: " + cuda.qwen_tts_cuda_last_error().decode())
+
+    def timed(fn):
+        for _ in range(args.warmup):
+            fn()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            fn()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        return shard.reduce_times(dist, [time.perf_counter() - t0], device=None)[0]
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    l0 = perf.kernel_launches
+    t_queue = timed(queue_arm)
+    cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
+    launches, admitted = int(perf.kernel_launches - l0), int(perf.queue_admitted)
+    t_lock = timed(lockstep_arm)
+    sampler.stop_flag = True
+    useful = float(sum(shard.gather_counts(dist, int(budgets.sum()), device=None))) * FRAME_S * args.steps
+    if rank == 0:
+        print(json.dumps({
+            "metric": "audio-sec generated/sec, 1.7B-CustomVoice, queue of ragged-length requests through 64 lock-step rows", "value": useful / t_queue, "unit": "audio_s/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_queue / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16 x bf16 -> f32 (tcgen05), activations as %d bf16 piece(s)" % args.pieces, "data": "synthetic",
+            "config": {"workload": f"{args.model} CustomVoice shapes, {n_utt} requests per GPU, lengths uniform in [{max(1, frames // 5)}, {frames}] frames (mean {float(budgets.mean()):.1f}), "
+                                   "continuous batching over 64 rows, default sampling, ragged prompts, codes + codec decode to PCM; host wall clock",
+                       "requests": n_utt, "rows": 64, "pieces": args.pieces, "admitted": admitted},
+            "e2e": {"value": useful / t_queue, "unit": "audio_s/s", "h2d_bytes_per_step": int(toks.nbytes + offs.nbytes + budgets.nbytes), "d2h_bytes_per_step": int(codes.nbytes + pcm.nbytes)},
+            "lockstep_batches": {"value": useful / t_lock, "unit": "audio_s/s", "ms_per_step": t_lock / args.steps * 1e3,
+                                 "note": "the same requests as lock-step batches of 64, every row run to the frame limit; only the requested frames count"},
+            "gpu_launches": launches, "clocks": sampler.summary()}))
+
+
 def run_codec(args, cuda, ctx, spec, hm, rank, world, local, dist, torch):
     """BASELINE config 3: codec decoder only, 16 codebooks x T frames -> 24 kHz PCM (qwen_tts_codec_decode, c/qwen_tts_codec.c:581-749).
     value: audio-seconds per second, codes resident in HBM .. last codec kernel (CUDA events); e2e: host codes in, host PCM out."""
@@ -411,6 +486,7 @@ def main():
     ap.add_argument("--strict", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline sample")
     ap.add_argument("--batch", type=int, default=0, help="> 0: lock-step batched decode of this many utterances per GPU (configs 4-5), codes only")
+    ap.add_argument("--queue", type=int, default=0, help="> 0: this many ragged-length requests per GPU through 64 rows: continuous batching vs lock-step batches")
     ap.add_argument("--codes-only", action="store_true", help="with --batch: skip the codec decode (round-1 behaviour)")
     ap.add_argument("--no-batched", action="store_true", help="default line: skip the config 4 / 5 sub-measurement")
     ap.add_argument("--greedy", action="store_true", help="greedy decoding (BASELINE config 1: --model 0.6b --frames 74 --greedy)")
@@ -442,9 +518,9 @@ def main():
     if cuda.qwen_tts_cuda_init(local) != 0:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
     spec, main_t, cod, hm = build_model(args.model)
-    default_line = args.batch == 0 and args.codec_frames == 0
+    default_line = args.batch == 0 and args.codec_frames == 0 and args.queue == 0
     want_batched = default_line and not args.no_batched and args.model == "1.7b" and not args.greedy and args.frames == FRAMES
-    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 64 if (want_batched or args.batch > 0) else 1)     # max_batch sizes the paged KV pool
+    ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 64 if (want_batched or args.batch > 0 or args.queue > 0) else 1)     # max_batch sizes the paged KV pool
     if not ctx:
         raise RuntimeError(cuda.qwen_tts_cuda_last_error().decode())
     cuda.qwen_tts_cuda_set_mode(ctx, args.mode)
@@ -456,7 +532,9 @@ def main():
         if dist is not None:
             dist.destroy_process_group()
         return
-    if args.batch > 0:
+    if args.queue > 0:
+        run_queue(args, cuda, ctx, spec, rank, world, local, dist, torch)
+    elif args.batch > 0:
         run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch)
         cuda.qwen_tts_cuda_release(ctx)
         if dist is not None:

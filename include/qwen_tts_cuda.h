@@ -287,10 +287,12 @@ int  qwen_tts_cuda_generate_batch(qtc_ctx_t *ctx, int batch,
  * next queued utterance is admitted into the row (pages reserved again, prompt built and prefilled on its own, per-row
  * state / RNG / repetition history reset) while the other rows are mid-utterance.  Utterance u uses seed
  * params.sample_seed + u and produces what it produces alone.  Buffers as for generate_batch with n_utt in place of batch.
+ * frame_budgets (optional, [n_utt]): per-utterance frame limit (the reference's max_new_tokens / fixed_codec_tokens are per
+ * context, c/qwen_tts.h:420-430; a queue of requests has one each), capped by the call's own limit.
  * Needs fast arithmetic (the default). */
 int  qwen_tts_cuda_generate_queue(qtc_ctx_t *ctx, int n_utt, int rows,
                                   const int *token_ids, const int *offsets,
-                                  const int *speaker_ids, const int *language_ids,
+                                  const int *speaker_ids, const int *language_ids, const int *frame_budgets,
                                   int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens);
 
 /* activations of the batched GEMMs: 3 = exact split of every fp32 value into three bf16 pieces (default: results differ

@@ -182,6 +182,111 @@ __global__ void __launch_bounds__(128) k_b_attn(const BAttnArgs a) {
     }
 }
 
+/* The same for head_dim 128 and two query heads per KV head (every shipped talker), one CTA of 8 warps per (KV head, utterance):
+ * a warp takes positions w, w + 8, ..., lane i owns dims 4i..4i+3, and each K / V row it loads (one 512-byte request per row
+ * instead of 128 scalar-strided ones) serves BOTH query heads of the group - k_b_attn reads every row once per query head and
+ * walks the V rows one position per dependent FMA.  Scores, running maximum, sum and output are kept per warp (online softmax)
+ * and folded over the 8 warps at the end.  Differs from k_b_attn by summation order only. */
+#define BA2_WARPS 8
+#define BA2_REC 132
+__device__ __forceinline__ float4 ba2_norm_rope(const float *src, const float *nw, const float *cs, const float *sn, float eps, int lane) {
+    const float4 v = reinterpret_cast<const float4 *>(src)[lane], n4 = reinterpret_cast<const float4 *>(nw)[lane];
+    const float4 c4 = reinterpret_cast<const float4 *>(cs)[lane], s4 = reinterpret_cast<const float4 *>(sn)[lane];
+    float ss = v.x * v.x;
+    ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
+    ss = warp_sum(ss);
+    const float inv = 1.0f / sqrtf(ss / 128.0f + eps);
+    const float4 y = make_float4(v.x * inv * n4.x, v.y * inv * n4.y, v.z * inv * n4.z, v.w * inv * n4.w);
+    const float px = __shfl_xor_sync(0xffffffffu, y.x, 16), py = __shfl_xor_sync(0xffffffffu, y.y, 16);
+    const float pz = __shfl_xor_sync(0xffffffffu, y.z, 16), pw = __shfl_xor_sync(0xffffffffu, y.w, 16);
+    /* rotate-half: dims < 64 (lanes < 16): y cos - partner sin; dims >= 64: y cos + partner sin */
+    return lane < 16 ? make_float4(y.x * c4.x - px * s4.x, y.y * c4.y - py * s4.y, y.z * c4.z - pz * s4.z, y.w * c4.w - pw * s4.w)
+                     : make_float4(y.x * c4.x + px * s4.x, y.y * c4.y + py * s4.y, y.z * c4.z + pz * s4.z, y.w * c4.w + pw * s4.w);
+}
+__global__ void __launch_bounds__(BA2_WARPS * 32) k_b_attn_gqa2(const BAttnArgs a) {
+    pdl_enter();
+    __shared__ __align__(16) float wpart[BA2_WARPS][2][BA2_REC];
+    const int g = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int kvd = a.kv_heads * 128, qd = a.heads * 128;
+    const int pos = (a.pos ? a.pos[b] : 0) + a.pos_add;
+    if (pos < 0) { store_pieces(a.xb, b, g * 256 + tid, qd, a.pieces, 0.0f); return; }
+    const float *row = a.qkv + (size_t)b * (qd + 2 * kvd), *cs = a.cos + (size_t)pos * 128, *sn = a.sin + (size_t)pos * 128;
+    const int *tab = a.tables ? a.tables + (size_t)b * a.table_stride : NULL;
+    float *kc = a.kc + (tab ? 0 : (size_t)b * a.kv_stride) + g * 128, *vc = a.vc + (tab ? 0 : (size_t)b * a.kv_stride) + g * 128;
+    const int n = pos + 1;
+    float m0 = -3.402823466e+38f, m1 = m0, l0 = 0.0f, l1 = 0.0f;
+    float4 o0 = make_float4(0, 0, 0, 0), o1 = o0;
+    if (warp < n) {
+        const float4 q0 = ba2_norm_rope(row + (2 * g) * 128, a.q_norm, cs, sn, a.eps, lane), q1 = ba2_norm_rope(row + (2 * g + 1) * 128, a.q_norm, cs, sn, a.eps, lane);
+        float4 k_new = make_float4(0, 0, 0, 0), v_new = k_new;
+        if (((n - 1) % BA2_WARPS) == warp) {             /* the warp that takes the new position also appends it to the cache */
+            k_new = ba2_norm_rope(row + qd + g * 128, a.k_norm, cs, sn, a.eps, lane);
+            v_new = reinterpret_cast<const float4 *>(row + qd + kvd + g * 128)[lane];
+            const size_t off = kv_off(tab, pos, kvd);
+            *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
+            *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
+        }
+        for (int tb = warp; tb < n; tb += 4 * BA2_WARPS) {
+            float d0[4], d1[4];
+            float4 vr[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int t = tb + BA2_WARPS * j;
+                float4 kr = make_float4(0, 0, 0, 0);
+                vr[j] = kr;
+                if (t < pos) {
+                    const size_t off = kv_off(tab, t, kvd);
+                    kr = *reinterpret_cast<const float4 *>(kc + off + lane * 4);
+                    vr[j] = *reinterpret_cast<const float4 *>(vc + off + lane * 4);
+                } else if (t == pos) { kr = k_new; vr[j] = v_new; }
+                d0[j] = fmaf(q0.w, kr.w, fmaf(q0.z, kr.z, fmaf(q0.y, kr.y, q0.x * kr.x)));
+                d1[j] = fmaf(q1.w, kr.w, fmaf(q1.z, kr.z, fmaf(q1.y, kr.y, q1.x * kr.x)));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                float u0[4], u1[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { u0[j] = __shfl_xor_sync(0xffffffffu, d0[j], o); u1[j] = __shfl_xor_sync(0xffffffffu, d1[j], o); }
+#pragma unroll
+                for (int j = 0; j < 4; j++) { d0[j] += u0[j]; d1[j] += u1[j]; }
+            }
+            float b0 = m0, b1 = m1;
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (tb + BA2_WARPS * j < n) { d0[j] *= a.scale; d1[j] *= a.scale; b0 = fmaxf(b0, d0[j]); b1 = fmaxf(b1, d1[j]); }
+            const float f0 = __expf(m0 - b0), f1 = __expf(m1 - b1);      /* first batch: exp(-huge) = 0 on zeros */
+            l0 *= f0; o0.x *= f0; o0.y *= f0; o0.z *= f0; o0.w *= f0;
+            l1 *= f1; o1.x *= f1; o1.y *= f1; o1.z *= f1; o1.w *= f1;
+            m0 = b0; m1 = b1;
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (tb + BA2_WARPS * j < n) {
+                    const float e0 = __expf(d0[j] - m0), e1 = __expf(d1[j] - m1);
+                    l0 += e0; l1 += e1;
+                    o0.x = fmaf(e0, vr[j].x, o0.x); o0.y = fmaf(e0, vr[j].y, o0.y); o0.z = fmaf(e0, vr[j].z, o0.z); o0.w = fmaf(e0, vr[j].w, o0.w);
+                    o1.x = fmaf(e1, vr[j].x, o1.x); o1.y = fmaf(e1, vr[j].y, o1.y); o1.z = fmaf(e1, vr[j].z, o1.z); o1.w = fmaf(e1, vr[j].w, o1.w);
+                }
+        }
+    }
+    if (lane == 0) { wpart[warp][0][0] = m0; wpart[warp][0][1] = l0; wpart[warp][1][0] = m1; wpart[warp][1][1] = l1; }
+    *reinterpret_cast<float4 *>(&wpart[warp][0][4 + lane * 4]) = o0;
+    *reinterpret_cast<float4 *>(&wpart[warp][1][4 + lane * 4]) = o1;
+    __syncthreads();
+    {
+        const int hh = tid >> 7, d = tid & 127;              /* 256 threads: (query head of the group, dim) */
+        float M = -3.402823466e+38f;
+#pragma unroll
+        for (int k = 0; k < BA2_WARPS; k++) M = fmaxf(M, wpart[k][hh][0]);
+        float L = 0.0f, o = 0.0f;
+#pragma unroll
+        for (int k = 0; k < BA2_WARPS; k++) {
+            const float lw = wpart[k][hh][1], f = lw > 0.0f ? __expf(wpart[k][hh][0] - M) : 0.0f;
+            L = fmaf(lw, f, L);
+            o = fmaf(wpart[k][hh][4 + d], f, o);
+        }
+        store_pieces(a.xb, b, (2 * g + hh) * 128 + d, qd, a.pieces, o / L);
+    }
+}
+
 /* the same for short contexts (n = pos + 1 <= 32, head_dim <= 128: every sub-talker step): a warp per (utterance, head),
  * lane i owns dims 4i..4i+3, eight K/V rows in flight per lane, no block barrier.  grid (ceil(heads / 4), B), 128 threads */
 __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
@@ -459,6 +564,11 @@ static int batch_ensure(qtc_ctx *c, int B, int kv_need, int frames, int pre_rows
     return 0;
 }
 
+static bool b_attn_gqa_on() {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("QTC_BATCH_ATTN_GQA"); on = e ? atoi(e) : 1; }
+    return on != 0;
+}
 /* ---- one decoder-stack step for the whole batch ------------------------------------------------------------
  * s->x [B,H] holds the inputs on entry.  pos (device, per utterance, may be NULL) + pos_add = KV position.
  * hidden_out (optional) receives the post-final-norm hidden rows; head_w (optional) -> s->logits [B, head_rows]. */
@@ -479,6 +589,7 @@ static int b_lm_step(qtc_ctx *c, BatchBuf *bb, const LmDev *lm, BStack *s, const
         a.xb = bb->xb; a.pos = pos; a.pos_add = pos_add; a.heads = lm->heads; a.kv_heads = lm->kv_heads; a.hd = hd; a.pieces = np;
         a.eps = lm->eps; a.scale = 1.0f / sqrtf((float)hd);
         if (!pos && pos_add + 1 <= 32 && hd <= 128 && hd % 4 == 0) qtc_launch_pdl(c->stream, k_b_attn_small, dim3(dim3((lm->heads + 3) / 4, B)), dim3(128), 0, a);
+        else if (hd == 128 && lm->heads == 2 * lm->kv_heads && b_attn_gqa_on()) qtc_launch_pdl(c->stream, k_b_attn_gqa2, dim3(dim3(lm->kv_heads, B)), dim3(BA2_WARPS * 32), 0, a);
         else qtc_launch_pdl(c->stream, k_b_attn, dim3(dim3(lm->heads, B)), dim3(128), (size_t)(2 * hd + (s->kv_max > 0 ? s->kv_max : c->kv.used[0] * QTC_KV_PAGE_POS) + 32) * 4, a);
         BLAUNCH(c);
         if (qtc_gemm_tc(c, s->x, H, bb->xb, w->wo, B, H, qd, np)) return -1;                      /* x += Wo . att */
@@ -800,7 +911,9 @@ extern "C" int qwen_tts_cuda_generate_batch(qtc_ctx_t *c, int batch, const int *
  * first row's budget ends): its codes are saved, its KV pages go back to the pool's free list, and the next utterance of the
  * queue is ADMITTED into the row - pages reserved, prompt built, prefilled on its own (qtc_prefill.cuh, KV rows straight into
  * the row's pages), frame-0 logits from the codec head, per-row state / RNG / repetition history reset - while the other rows
- * are mid-utterance.  Rows never see each other, so utterance u (seed sample_seed + u) produces what it produces alone. */
+ * are mid-utterance.  Rows never see each other, so utterance u (seed sample_seed + u) produces what it produces alone.
+ * frame_budgets (optional, [n_utt]): utterance u stops after min(budget, the call's limit) frames - requests of different
+ * lengths are where a freed row pays: lock-step batches run every row to the longest request. */
 __global__ void k_pf_fill_rows_imm(int *slot, int *pos, int R, int s, int base) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < R) { slot[r] = s; pos[r] = base + r; }
@@ -808,7 +921,7 @@ __global__ void k_pf_fill_rows_imm(int *slot, int *pos, int R, int s, int base) 
 #define QTC_Q_POLL 8
 #define QTC_Q_PARKED (-(1 << 30))         /* position of a row with no utterance: negative = every kernel skips it, and 2^30 steps stay negative */
 extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, const int *token_ids, const int *offsets, const int *speaker_ids,
-                                            const int *language_ids, int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens) {
+                                            const int *language_ids, const int *frame_budgets, int *out_codes, int *out_n_frames, float *pcm_out, int max_tokens) {
     if (!c || c->talker.layers <= 0) { qtc_set_error("generate_queue: context has no talker weights"); return -1; }
     if (n_utt < 1 || rows < 1 || rows > BROWS || !token_ids || !offsets || !out_codes || max_tokens < 1) { qtc_set_error("generate_queue: rows must be 1..64 and buffers non-null"); return -1; }
     if (c->talker.hidden % 64 || c->talker.inter % 64 || (c->talker.heads * c->talker.head_dim) % 64 || c->sub.hidden % 64 || c->sub.inter % 64 ||
@@ -838,7 +951,7 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
         c->dev_mallocs++;
     }
     cudaEventRecord(c->ev2, c->stream);
-    std::vector<int> row_utt(B, -1), row_end(B, 0), pos_host(B, QTC_Q_PARKED), nframes(n_utt, 0);
+    std::vector<int> row_utt(B, -1), row_end(B, 0), row_lim(B, 0), pos_host(B, QTC_Q_PARKED), nframes(n_utt, 0);
     std::vector<uint32_t> seed_host(B, 0);
     int frame_now = 0, next_u = 0, admitted = 0;
     /* the next utterances of the queue -> the rows in `free_rows` (as many as there are of both); their prompts are prefilled
@@ -856,7 +969,8 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
             const int spk = speaker_ids ? speaker_ids[u] : -1, lang = language_ids ? language_ids[u] : -1;
             if (qtc_build_prompt_dev(c, token_ids + offsets[u], offsets[u + 1] - offsets[u], spk, lang, bb->prefill + (size_t)b * bb->prefill_cap * H, &plen[b],
                                      bb->trailing + (size_t)b * bb->trailing_cap * H, &ntr[b], c->tts_pad)) return -1;
-            row_utt[b] = u; row_end[b] = frame_now + limit; admitted++;
+            row_utt[b] = u; row_lim[b] = frame_budgets && frame_budgets[u] < limit ? (frame_budgets[u] > 1 ? frame_budgets[u] : 1) : limit;
+            row_end[b] = frame_now + row_lim[b]; admitted++;
             rows_in.push_back(b);
         }
         if (rows_in.empty()) return 0;
@@ -881,7 +995,7 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
             memset(&s, 0, sizeof(s));
             const float f = (float)(c->params.sample_seed + row_utt[b]);
             memcpy(&s.rng, &f, 4); memcpy(&seed_host[b], &f, 4);
-            s.limit = limit; s.fixed = fixed > 0; s.n_trailing = ntr[b]; s.stop_step = limit;
+            s.limit = row_lim[b]; s.fixed = fixed > 0; s.n_trailing = ntr[b]; s.stop_step = row_lim[b];
             bb->state_host[b] = s;
             pos_host[b] = plen[b];
             QTC_CUDA(cudaMemcpyAsync(bb->state + b, bb->state_host + b, sizeof(GenState), cudaMemcpyHostToDevice, c->stream));

@@ -158,7 +158,7 @@ def load_cuda():
     lib.qwen_tts_cuda_codec_stream_begin.argtypes = [vp, C.c_int]
     lib.qwen_tts_cuda_codec_stream_push.argtypes = [vp, i32p, C.c_int, f32p]
     lib.qwen_tts_cuda_generate_batch.argtypes = [vp, C.c_int, i32p, i32p, i32p, i32p, i32p, i32p, f32p, C.c_int]
-    lib.qwen_tts_cuda_generate_queue.argtypes = [vp, C.c_int, C.c_int, i32p, i32p, i32p, i32p, i32p, i32p, f32p, C.c_int]
+    lib.qwen_tts_cuda_generate_queue.argtypes = [vp, C.c_int, C.c_int, i32p, i32p, i32p, i32p, i32p, i32p, i32p, f32p, C.c_int]
     lib.qwen_tts_cuda_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_swiglu_matvec_bf16.argtypes = [f32p, u16p, f32p, C.c_int, C.c_int]
     lib.qwen_tts_cuda_rms_norm.argtypes = [f32p, f32p, f32p, C.c_int, C.c_float]

@@ -42,7 +42,7 @@ def _setup_batch_api(cuda):
     cuda.qwen_tts_cuda_batch_subtalker.argtypes = [C.c_void_p, C.c_int, B.f32p, B.i32p, B.i32p]
     cuda.qwen_tts_cuda_set_batch_pieces.argtypes = [C.c_void_p, C.c_int]
     cuda.qwen_tts_cuda_generate_batch.argtypes = [C.c_void_p, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
-    cuda.qwen_tts_cuda_generate_queue.argtypes = [C.c_void_p, C.c_int, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
+    cuda.qwen_tts_cuda_generate_queue.argtypes = [C.c_void_p, C.c_int, C.c_int, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.i32p, B.f32p, C.c_int]
 
 
 @pytest.mark.parametrize("pieces,tol", [(3, 2e-4), (1, 1e-2)])
@@ -237,7 +237,7 @@ def test_generate_queue_admits_into_freed_rows_eos(cuda, orc):
     nfr = np.full(n_utt, -1, dtype=np.int32)
     perf0 = B.Perf()
     cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf0))
-    rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, rows, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), None, cap)
+    rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, rows, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), None, B.iptr(codes), B.iptr(nfr), None, cap)
     assert rc == 0, cuda.qwen_tts_cuda_last_error()
     perf = B.Perf()
     cuda.qwen_tts_cuda_get_perf(ctx, C.byref(perf))
@@ -254,14 +254,15 @@ def test_generate_queue_admits_into_freed_rows_eos(cuda, orc):
 
 
 def test_generate_queue_fixed_budget_with_pcm(cuda, orc, tiny):
-    """the same with a fixed frame budget (rows retire together, the next wave is prefilled as one ragged pass) and PCM:
-    5 utterances through 2 rows, 6 frames each; codes equal the oracle's, waveform >= 80 dB; then a plain generate_batch on the
-    same context still equals the oracle (the queue leaves rows parked, the batch call re-arms them)"""
+    """the same with fixed frame budgets - one per utterance (6, 3, 5, 6, 2 frames: rows retire at different frames, exactly at
+    their budget) - and PCM: 5 utterances through 2 rows; codes equal the oracle's, waveform >= 80 dB; then a plain
+    generate_batch on the same context still equals the oracle (the queue leaves rows parked, the batch call re-arms them)"""
     _setup_batch_api(cuda)
     G = tiny.spec["groups"]
     ctx = cuda.qwen_tts_cuda_upload(C.byref(tiny.desc), 2)
     assert ctx
     frames, n_utt, rows = 6, 5, 2
+    budgets = np.array([6, 3, 5, 6, 2], dtype=np.int32)
     cuda.qwen_tts_cuda_set_params(ctx, C.byref(B.default_params(fixed_codec_tokens=frames)))
     prompts = _queue_prompts(n_utt)
     spk = np.array([mg.SPEAKERS["aiden"], -1, mg.SPEAKERS["vivian"], mg.SPEAKERS["aiden"], -1], dtype=np.int32)
@@ -271,19 +272,21 @@ def test_generate_queue_fixed_budget_with_pcm(cuda, orc, tiny):
     codes = np.zeros((n_utt, frames, G), dtype=np.int32)
     nfr = np.zeros(n_utt, dtype=np.int32)
     pcm = np.zeros((n_utt, frames * 1920), dtype=np.float32)
-    rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, rows, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes), B.iptr(nfr), B.fptr(pcm), frames)
+    rc = cuda.qwen_tts_cuda_generate_queue(ctx, n_utt, rows, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(budgets), B.iptr(codes), B.iptr(nfr), B.fptr(pcm), frames)
     assert rc == 0, cuda.qwen_tts_cuda_last_error()
-    assert list(nfr) == [frames] * n_utt
-    wants = []
+    assert list(nfr) == list(budgets)
     for u in range(n_utt):
-        nf, want, want_pcm = _oracle_solo(orc, tiny.desc, B.default_params(fixed_codec_tokens=frames, sample_seed=42 + u), prompts[u], int(spk[u]), int(lang[u]), frames, G)
-        wants.append(want)
-        assert nf == frames and np.array_equal(codes[u], want), (u, codes[u], want)
-        err = ((pcm[u].astype(np.float64) - want_pcm) ** 2).sum()
+        k = int(budgets[u])
+        nf, want, want_pcm = _oracle_solo(orc, tiny.desc, B.default_params(fixed_codec_tokens=k, sample_seed=42 + u), prompts[u], int(spk[u]), int(lang[u]), frames, G)
+        assert nf == k and np.array_equal(codes[u][:k], want[:k]), (u, codes[u], want)
+        got_pcm = pcm[u][: len(want_pcm)]
+        err = ((got_pcm.astype(np.float64) - want_pcm) ** 2).sum()
         snr = 10 * np.log10((want_pcm.astype(np.float64) ** 2).sum() / max(err, 1e-300))
-        assert snr >= 80.0, (u, snr)
+        assert len(want_pcm) == k * 1920 and snr >= 80.0, (u, snr)
     codes2 = np.zeros((2, frames, G), dtype=np.int32)
     rc = cuda.qwen_tts_cuda_generate_batch(ctx, 2, B.iptr(toks), B.iptr(offs), B.iptr(spk), B.iptr(lang), B.iptr(codes2), B.iptr(nfr), None, frames)
     assert rc == 0, cuda.qwen_tts_cuda_last_error()
-    assert np.array_equal(codes2[0], wants[0]) and np.array_equal(codes2[1], wants[1])
+    for b in range(2):
+        nf, want, _ = _oracle_solo(orc, tiny.desc, B.default_params(fixed_codec_tokens=frames, sample_seed=42 + b), prompts[b], int(spk[b]), int(lang[b]), frames, G)
+        assert np.array_equal(codes2[b], want), b
     cuda.qwen_tts_cuda_release(ctx)
