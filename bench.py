@@ -532,10 +532,8 @@ def main():
         if dist is not None:
             dist.destroy_process_group()
         return
-    if args.queue > 0:
-        run_queue(args, cuda, ctx, spec, rank, world, local, dist, torch)
-    elif args.batch > 0:
-        run_batch(args, cuda, ctx, spec, rank, world, local, dist, torch)
+    if args.queue > 0 or args.batch > 0:
+        (run_queue if args.queue > 0 else run_batch)(args, cuda, ctx, spec, rank, world, local, dist, torch)
         cuda.qwen_tts_cuda_release(ctx)
         if dist is not None:
             dist.destroy_process_group()

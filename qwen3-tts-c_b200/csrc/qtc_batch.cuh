@@ -303,6 +303,19 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
     const float *cs = a.cos + (size_t)pos * hd, *sn = a.sin + (size_t)pos * hd;
     const int *tab = a.tables ? a.tables + (size_t)b * a.table_stride : NULL;
     float *kc = a.kc + (tab ? 0 : (size_t)b * a.kv_stride), *vc = a.vc + (tab ? 0 : (size_t)b * a.kv_stride);
+    /* The cached rows do not depend on this step's q: the first 16 K and V rows (every sub-talker context: <= 17 positions, the last
+     * one being the new token) are requested before anything else, together with q, k, v and the norm / RoPE vectors - one round
+     * trip to L2 instead of five dependent ones (a 10 us kernel, 80 launches per batched frame, was almost all load latency). */
+    float4 kpre[16], vpre[16];
+#pragma unroll
+    for (int t = 0; t < 16; t++) {
+        kpre[t] = make_float4(0, 0, 0, 0); vpre[t] = kpre[t];
+        if (t < pos && act) {
+            const size_t off = kv_off(tab, t, kvd) + g * hd + lane * 4;
+            kpre[t] = *reinterpret_cast<const float4 *>(kc + off);
+            vpre[t] = *reinterpret_cast<const float4 *>(vc + off);
+        }
+    }
     float sq = 0.0f, sk = 0.0f;
     for (int i = lane; i < hd; i += 32) { const float vq = qr[i], vk = kr[i]; qs[i] = vq; ks[i] = vk; sq = fmaf(vq, vq, sq); sk = fmaf(vk, vk, sk); }
     const float4 v_new = act ? *reinterpret_cast<const float4 *>(vr + lane * 4) : make_float4(0, 0, 0, 0);
@@ -324,44 +337,54 @@ __global__ void __launch_bounds__(128) k_b_attn_small(const BAttnArgs a) {
         *reinterpret_cast<float4 *>(vc + kv_off(tab, pos, kvd) + g * hd + lane * 4) = v_new;
     }
     float sc = -3.402823466e+38f;
-    for (int t0 = 0; t0 < n; t0 += 8) {
-        float d[8];
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const int t = t0 + u;
-            float4 kv = make_float4(0, 0, 0, 0);
-            if (t < pos) { if (act) kv = *reinterpret_cast<const float4 *>(kc + kv_off(tab, t, kvd) + g * hd + lane * 4); }
-            else if (t == pos) kv = k_new;
-            d[u] = fmaf(q4.w, kv.w, fmaf(q4.z, kv.z, fmaf(q4.y, kv.y, q4.x * kv.x)));
+    for (int t0 = 0; t0 < 32; t0 += 8) {
+        if (t0 < n) {
+            float d[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int t = t0 + u;
+                float4 kv = make_float4(0, 0, 0, 0);
+                if (t < pos) {
+                    if (t0 < 16) kv = kpre[t0 < 16 ? t : 0];
+                    else if (act) kv = *reinterpret_cast<const float4 *>(kc + kv_off(tab, t, kvd) + g * hd + lane * 4);
+                } else if (t == pos) kv = k_new;
+                d[u] = fmaf(q4.w, kv.w, fmaf(q4.z, kv.z, fmaf(q4.y, kv.y, q4.x * kv.x)));
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                float t8[8];
+#pragma unroll
+                for (int u = 0; u < 8; u++) t8[u] = __shfl_xor_sync(0xffffffffu, d[u], o);
+#pragma unroll
+                for (int u = 0; u < 8; u++) d[u] += t8[u];
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) if (lane == t0 + u && t0 + u < n) sc = d[u] * a.scale;
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            float t8[8];
-#pragma unroll
-            for (int u = 0; u < 8; u++) t8[u] = __shfl_xor_sync(0xffffffffu, d[u], o);
-#pragma unroll
-            for (int u = 0; u < 8; u++) d[u] += t8[u];
-        }
-#pragma unroll
-        for (int u = 0; u < 8; u++) if (lane == t0 + u && t0 + u < n) sc = d[u] * a.scale;
     }
     const float mx = warp_max(sc);
     const float e = lane < n ? __expf(sc - mx) : 0.0f;
     const float tot = warp_sum(e);
     float4 o4 = make_float4(0, 0, 0, 0);
-    for (int t0 = 0; t0 < n; t0 += 8) {
-        float4 vv[8];
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const int t = t0 + u;
-            vv[u] = make_float4(0, 0, 0, 0);
-            if (t < pos) { if (act) vv[u] = *reinterpret_cast<const float4 *>(vc + kv_off(tab, t, kvd) + g * hd + lane * 4); }
-            else if (t == pos) vv[u] = v_new;
-        }
+    for (int t0 = 0; t0 < 32; t0 += 8) {
+        if (t0 < n) {
+            float4 vv[8];
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
-            const float p = __shfl_sync(0xffffffffu, e, (t0 + u) & 31);
-            if (t0 + u < n) { o4.x = fmaf(p, vv[u].x, o4.x); o4.y = fmaf(p, vv[u].y, o4.y); o4.z = fmaf(p, vv[u].z, o4.z); o4.w = fmaf(p, vv[u].w, o4.w); }
+            for (int u = 0; u < 8; u++) {
+                const int t = t0 + u;
+                vv[u] = make_float4(0, 0, 0, 0);
+                if (t < pos) {
+                    if (t0 < 16) vv[u] = vpre[t0 < 16 ? t : 0];
+                    else if (act) vv[u] = *reinterpret_cast<const float4 *>(vc + kv_off(tab, t, kvd) + g * hd + lane * 4);
+                } else if (t == pos) vv[u] = v_new;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const float p = __shfl_sync(0xffffffffu, e, (t0 + u) & 31);
+                if (t0 + u < n) { o4.x = fmaf(p, vv[u].x, o4.x); o4.y = fmaf(p, vv[u].y, o4.y); o4.z = fmaf(p, vv[u].z, o4.z); o4.w = fmaf(p, vv[u].w, o4.w); }
+            }
         }
     }
     if (act) {

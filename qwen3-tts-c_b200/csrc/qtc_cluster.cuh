@@ -334,18 +334,20 @@ __device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const Cluste
 }
 #undef APROF
 
-/* Contexts of at most 32 positions (every sub-talker step): the whole head in ONE warp of CTA rank hh (0 / 1), and the 128 outputs
- * go straight into every peer's att[]: no partial records, no fold, no block barrier.  The warp's latency chain is kept short:
+/* Contexts of at most 32 positions (every sub-talker step): the whole head in ONE warp, no partial records, no fold.  EVERY CTA of
+ * the cluster runs both heads for itself (warps 0 and 1; it holds the cluster's 512 projection outputs anyway and stages the <= 31
+ * cached K/V rows across the grid barrier like the two CTAs that used to do the work and push the 256 outputs to their peers):
+ * the cluster barrier between attention and O projection - 0.7 us of a 17 us layer - becomes a block barrier.  Rank 0 appends the
+ * new K/V row to the cache.  The warp's latency chain is kept short:
  * the q and k norms run as one interleaved butterfly, scores are position-parallel (lane t takes the whole 128-wide dot product of
  * position t against q in shared memory - K rows are staged with a 132-float stride so that the lanes' rows fall into different
  * banks - instead of 40 shuffles per eight positions), V rows are weighted with lane-owns-4-dims.  kvs: rows [0, pos) of K, then V. */
 #define CL_KST_SMALL 132
-__device__ __forceinline__ void cl_attention_small(cg::cluster_group &cl, const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int hh,
+__device__ __forceinline__ void cl_attention_small(const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int hh, bool append,
                                                    const float *qkv, float *att, const float *kvs, const float *aux, float *scr) {
-    if (threadIdx.x >= 32) return;
 #define SPROF(i) do { if (a.prof && threadIdx.x == 0 && l == a.prof_layer) a.prof[blockIdx.x * 32 + (i)] = clock64(); } while (0)
     SPROF(24);
-    const int lane = threadIdx.x, kvd = lm.kv_heads * 128, n = pos + 1, cap = a.att_cap;
+    const int lane = threadIdx.x & 31, kvd = lm.kv_heads * 128, n = pos + 1, cap = a.att_cap;
     float *qs = scr, *ks = scr + 128;
     const float4 c4 = reinterpret_cast<const float4 *>(aux)[lane], s4 = reinterpret_cast<const float4 *>(aux + 128)[lane];
     const float4 qv = reinterpret_cast<const float4 *>(qkv + hh * 128)[lane], kv = reinterpret_cast<const float4 *>(qkv + 256)[lane];
@@ -368,7 +370,7 @@ __device__ __forceinline__ void cl_attention_small(cg::cluster_group &cl, const 
     }
     reinterpret_cast<float4 *>(qs)[lane] = q4;
     reinterpret_cast<float4 *>(ks)[lane] = k_new;
-    if (hh == 0) {
+    if (append) {
         float *kc = a.kc + (size_t)l * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)l * a.kv_max * kvd + g * 128;
         const size_t off = kv_off(a.table, pos, kvd);
         *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
@@ -410,8 +412,7 @@ __device__ __forceinline__ void cl_attention_small(cg::cluster_group &cl, const 
     SPROF(28);
     const float inv = __fdividef(1.0f, tot);
     const float4 r4 = make_float4(o4.x * inv, o4.y * inv, o4.z * inv, o4.w * inv);
-#pragma unroll
-    for (int k = 0; k < CL_SIZE; k++) *reinterpret_cast<float4 *>(cl.map_shared_rank(att, k) + hh * 128 + lane * 4) = r4;
+    *reinterpret_cast<float4 *>(att + hh * 128 + lane * 4) = r4;
     SPROF(29);
 }
 #undef SPROF
@@ -550,10 +551,10 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     for (int gstep = 0; gstep < nsteps; gstep++) {
         const int pos = pos_base + gstep;
         const int n = pos + 1;
-        const bool small_att = n <= 32 && (n - 1) * CL_KST_SMALL <= a.att_cap * 128;      /* ranks 0 / 1 take a whole head each, one warp */
+        const bool small_att = n <= 32 && (n - 1) * CL_KST_SMALL <= a.att_cap * 128;      /* every CTA takes both heads, one warp each */
         const int kst = small_att ? CL_KST_SMALL : 128;    /* K row stride in the stage */
         const int chunk = small_att ? n : (n + CL_SIZE - 1) / CL_SIZE;
-        int t0 = small_att ? 0 : rank * chunk, t1 = small_att ? (rank < 2 ? n : 0) : (t0 + chunk < n ? t0 + chunk : n);
+        int t0 = small_att ? 0 : rank * chunk, t1 = small_att ? n : (t0 + chunk < n ? t0 + chunk : n);
         if (t0 > n) t0 = n;
         if (t1 < t0) t1 = t0;
         const bool staged = small_att || chunk <= a.att_cap;
@@ -620,7 +621,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 cl.sync();
                 PROF(3);
-                if (small_att) { if (rank < 2) { cl_attention_small(cl, a, lm, l, g, pos, rank, qkv, att, kvs, aux, wpart); __syncthreads(); } }   /* the other 15 warps park at bar.sync, not in the cluster barrier's wait */
+                if (small_att) { if (warp < 2) cl_attention_small(a, lm, l, g, pos, warp, warp == 0 && rank == 0, qkv, att, kvs, aux, wpart + warp * 256); }
                 else cl_attention(cl, a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
                 /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
                 const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
@@ -628,7 +629,8 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
 #pragma unroll
                 for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(warp * 8 + i) * 256) + lane);
                 PROF(4);
-                cl.sync();
+                if (small_att) __syncthreads();                         /* att[] is this CTA's own: no cluster barrier */
+                else cl.sync();
                 PROF(5);
                 if (!small_att) cl_attention_combine(cpart, att);
                 if (a.flags & 8) cl.sync();                             /* experiment: the third cluster barrier of the push variant */
@@ -730,6 +732,17 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                     }
                 };
                 float sa = 0.0f, sb = 0.0f;
+                /* flags & 256: every CTA adds its partial of every row straight into the fixed-point accumulator (8 x the atomics,
+                 * all exact integer adds) instead of folding the cluster's 8 partials through DSMEM first: no cluster barrier, no fold */
+                const bool direct = (a.flags & 256) != 0;
+                long long res0 = 0, res1 = 0, res2 = 0, res3 = 0;       /* the residual rows this CTA contributes (cluster 0: rank r owns rows [r RPC, (r+1) RPC)) */
+                if (direct && g == 0) {
+                    const int r0 = tid, r1 = tid + CL_THREADS, r2 = tid + 2 * CL_THREADS, r3 = tid + 3 * CL_THREADS;
+                    if (r0 / RPC == rank) res0 = __ldcg(xmid + r0);
+                    if (r1 / RPC == rank) res1 = __ldcg(xmid + r1);
+                    if (r2 < H && r2 / RPC == rank) res2 = __ldcg(xmid + r2);
+                    if (r3 < H && r3 / RPC == rank) res3 = __ldcg(xmid + r3);
+                }
                 auto d_consume = [&](const Stage &st, int bi) {
                     const int r = tid + 2 * CL_THREADS * (bi / CB), cb = 4 * (bi % CB);
 #pragma unroll
@@ -738,7 +751,13 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                         sa = dot8f(st.a[c], g0, g1, sa);
                         sb = dot8f(st.b[c], g0, g1, sb);
                     }
-                    if (bi % CB == CB - 1) { dp[r] = sa; dp[r + CL_THREADS] = sb; sa = 0.0f; sb = 0.0f; }
+                    if (bi % CB == CB - 1) {
+                        if (direct) {
+                            red_add_s64(xout + r, to_fx(sa) + (bi / CB == 0 ? res0 : res2));
+                            red_add_s64(xout + r + CL_THREADS, to_fx(sb) + (bi / CB == 0 ? res1 : res3));
+                        } else { dp[r] = sa; dp[r + CL_THREADS] = sb; }
+                        sa = 0.0f; sb = 0.0f;
+                    }
                 };
                 d_issue(s0, 0);
                 if (nb > 1) d_issue(s1, 1); else st_zero(s1);
@@ -751,9 +770,9 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 }
             }
             PROF(11);
-            cl.sync();
+            if (!(a.flags & 256)) cl.sync();
             PROF(12);
-            {
+            if (!(a.flags & 256)) {
                 /* rank r folds rows [r RPC, (r+1) RPC) over the 8 peers: lane group of 8 = the peers, fixed butterfly order */
                 const int peer = tid & 7, grp = tid >> 3;
                 if (grp < RPC / 4) {

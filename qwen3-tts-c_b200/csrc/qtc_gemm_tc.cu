@@ -28,11 +28,15 @@
 #define TC_THREADS 192
 /* NP = activation pieces: 1 = activations rounded to bf16; 3 = exact split x = hi + mid + lo (three bf16 pieces stacked
  * as 192 B-operand rows), which makes every product exact and leaves only fp32 summation-order differences */
-template <int NP> struct TcCfg {
+/* ST = pipeline stages; 0 = as many as one CTA per SM holds (6 / 5).  ST = 2 (81 KB at three pieces) lets TWO CTAs share an SM: the
+ * CTAs of the next launch become resident - barrier init, TMEM allocation, first weight tiles under way - while this one's are still
+ * streaming or draining their epilogue, which a 206 KB CTA that owns the SM rules out.  The split-K accumulate path uses ST = 2
+ * (QTC_GEMM_STAGES=5 brings the deep pipeline back for A/B); K splits are then sized for two CTAs per SM. */
+template <int NP, int ST = 0> struct TcCfg {
     static constexpr int N = TC_BN * NP;                       /* UMMA N */
     static constexpr int B_BYTES = N * TC_BK * 2;
     static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
-    static constexpr int STAGES = NP == 1 ? 6 : 5;
+    static constexpr int STAGES = ST > 0 ? ST : (NP == 1 ? 6 : 5);
     static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
     static constexpr int TMEM_COLS = NP == 1 ? 64 : 256;       /* power of two >= N */
 };
@@ -44,11 +48,11 @@ template <int NP> struct TcCfg {
  *        xo[(p*64 + b) * (N/2) + u]: SwiGLU costs no kernel and no fp32 round trip.
  * EPI 2: K split s STORES its partial sums at Y + s * split_stride (plain stores, no pre-initialised Y): the consumer adds the
  *        splits in a fixed order, so the result is bit-reproducible run to run (the batch-1 prefill, qtc_prefill.cuh). */
-template <int NP, int EPI>
-__global__ void __launch_bounds__(TC_THREADS, 1) k_gemm_tc(const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapX,
+template <int NP, int EPI, int ST = 0>
+__global__ void __launch_bounds__(TC_THREADS, ST == 2 ? 2 : 1) k_gemm_tc(const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapX,
                                                             float *Y, int N, int ldy, int kb_per_split, int nbatch, uint16_t *xo, int xo_pieces, int split_stride) {
     extern __shared__ __align__(1024) unsigned char tc_smem_raw[];
-    typedef TcCfg<NP> Cfg;
+    typedef TcCfg<NP, ST> Cfg;
     constexpr int TC_STAGES = Cfg::STAGES, TC_STAGE_BYTES = Cfg::STAGE_BYTES;
     __shared__ __align__(8) uint64_t full[TC_STAGES], empty[TC_STAGES], acc_full;
     __shared__ uint32_t tmem_base_s;
@@ -250,10 +254,22 @@ int qtc_gemm_tc_ex(qtc_ctx *c, float *Y, int ldy, const uint16_t *X, const uint1
     }
     const CUtensorMap *mw = qtc_tmap_bf16(W, N, K, TC_BM), *mx = qtc_tmap_bf16(X, TC_BN * pieces, K, TC_BN * pieces);
     if (!mw || !mx) return -1;
-    const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = swiglu_out ? 1 : pick_splits(tiles, kblocks, c->num_sms);
+    static int st2 = -1;
+    if (st2 < 0) {
+        const char *e = getenv("QTC_GEMM_STAGES");
+        st2 = !(e && atoi(e) != 2);                                   /* default since the A/B on config 4: 5.89 -> 5.64 ms per 64-utterance frame */
+        if (st2) {
+            QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<1, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1, 2>::SMEM));
+            QTC_CUDA(cudaFuncSetAttribute(k_gemm_tc<3, 0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<3, 2>::SMEM));
+        }
+    }
+    const int tiles = (N + TC_BM - 1) / TC_BM, kblocks = K / TC_BK, splits = swiglu_out ? 1 : pick_splits(tiles, kblocks, st2 ? 2 * c->num_sms : c->num_sms);
     if (swiglu_out && (N & 1)) { qtc_set_error("gemm_tc: interleaved gate/up needs an even row count"); return -1; }
     const dim3 grid(tiles, splits);
-    if (swiglu_out) {
+    if (st2 && !swiglu_out) {
+        if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 0, 2>, grid, dim3(TC_THREADS), (size_t)TcCfg<1, 2>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0, 0);
+        else qtc_launch_pdl(c->stream, k_gemm_tc<3, 0, 2>, grid, dim3(TC_THREADS), (size_t)TcCfg<3, 2>::SMEM, *mw, *mx, Y, N, ldy, kblocks / splits, nbatch, (uint16_t *)NULL, 0, 0);
+    } else if (swiglu_out) {
         if (pieces == 1) qtc_launch_pdl(c->stream, k_gemm_tc<1, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<1>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces, 0);
         else qtc_launch_pdl(c->stream, k_gemm_tc<3, 1>, grid, dim3(TC_THREADS), (size_t)TcCfg<3>::SMEM, *mw, *mx, Y, N, ldy, kblocks, nbatch, swiglu_out, pieces, 0);
     } else {
