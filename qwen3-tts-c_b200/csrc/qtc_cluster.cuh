@@ -17,7 +17,8 @@
  *     slice is contiguous) = a PARTIAL sum for every row of x.
  *   Phase B (every CTA owns a run of 8-column chunks of the MLP's inner dimension): RMSNorm -> gate/up -> SwiGLU in
  *     shared memory -> the down projection restricted to those input columns (re-laid out [I/8][H][8]) = a partial
- *     for every row of x, reduced over the 8 CTAs of the cluster through DSMEM in a fixed order.
+ *     for every row of x, which every CTA adds straight into the accumulator (folding the cluster's 8 partials through DSMEM
+ *     first saved 7/8 of the atomics but cost a cluster barrier and a fold: 1.4 us of a 17 us sub-talker layer).
  *   The partial sums of both phases meet in HBM/L2 as 64-bit FIXED-POINT atomic adds (scale 2^32): integer addition
  *   is associative, so the result does not depend on arrival order - the step stays bit-reproducible - and the
  *   residual stream is carried exactly.  Three accumulators rotate: phase p reads buf[p % 3], adds into
@@ -468,7 +469,7 @@ __device__ __forceinline__ void cl_prefetch_paced(const void *base, size_t bytes
     }
 }
 
-/* dynamic shared memory (floats): [ xs (= dp in the second half of phase B) | qkv 512 | att 256 | cpart 8 x 2 x 132 | wpart 16 x 2 x 132 | fold factors 64 | g 64 |
+/* dynamic shared memory (floats): [ xs | qkv 512 | att 256 | cpart 8 x 2 x 132 | wpart 16 x 2 x 132 | fold factors 64 | g 64 |
  * aux 512 | in_norm H | post_norm H | kv stage 2 x att_cap x 128 ]; the in-kernel sampler's workspace overlays aux.. (sampling happens
  * between steps; only this CTA writes there).  Kept small on purpose: shared memory is carved out of the SM's 228 KB and what is left is L1, whose size bounds
  * the loads an SM keeps in flight - measured: +17 KB of shared memory (a 132 -> 164 KB carve-out) cost the talker step 12 %. */
@@ -498,7 +499,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
     const int H = lm.hidden, I = lm.inter, L = lm.layers;
     const bool att_cluster = g < lm.kv_heads;           /* this cluster owns a KV head in phase A */
     float *sm = cl_smem, *qkv = sm + a.xs_floats, *att = qkv + 512, *cpart = att + 256, *wpart = cpart + CL_SIZE * 2 * CL_REC;
-    float *gs = wpart + CL_WARPS * 2 * CL_REC + 64, *dp = sm, *aux = gs + 64, *nin = aux + 512, *npost = nin + H, *kvs = npost + H;
+    float *gs = wpart + CL_WARPS * 2 * CL_REC + 64, *aux = gs + 64, *nin = aux + 512, *npost = nin + H, *kvs = npost + H;
     SampleSmem &S_samp = *reinterpret_cast<SampleSmem *>(aux);      /* 17.2 KB over aux | in_norm | post_norm | kv stage: regions only this CTA writes (peers push into qkv) */
     const int pos_base = *a.pos_ptr + a.pos_add;
     int p = *a.phase;                                   /* phase counter mod 3 */
@@ -718,7 +719,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 if (lane == 0) gs[warp + CL_WARPS * k] = swiglu_act<QTC_FAST>(va, vb);
             });
             {
-                /* down partial: dp[r] = sum over this CTA's columns of W_down[r][.] g[.]; pieces (chunk c, row r) are 16 bytes at
+                /* down partial of row r = sum over this CTA's columns of W_down[r][.] g[.]; pieces (chunk c, row r) are 16 bytes at
                  * (c H + r).  A batch = rows (r, r + 512) x 4 chunks = 8 loads in a Stage; batches: row pairs x chunk groups, two in flight;
                  * the first two are requested before the SwiGLU values are complete (they do not depend on them). */
                 const uint4 *dw = reinterpret_cast<const uint4 *>(w.down_t) + (size_t)c0 * H;
@@ -732,11 +733,10 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                     }
                 };
                 float sa = 0.0f, sb = 0.0f;
-                /* flags & 256: every CTA adds its partial of every row straight into the fixed-point accumulator (8 x the atomics,
-                 * all exact integer adds) instead of folding the cluster's 8 partials through DSMEM first: no cluster barrier, no fold */
-                const bool direct = (a.flags & 256) != 0;
+                /* every CTA adds its partial of every row straight into the fixed-point accumulator: exact integer adds, so the sum does
+                 * not depend on the order in which the 120 CTAs arrive */
                 long long res0 = 0, res1 = 0, res2 = 0, res3 = 0;       /* the residual rows this CTA contributes (cluster 0: rank r owns rows [r RPC, (r+1) RPC)) */
-                if (direct && g == 0) {
+                if (g == 0) {
                     const int r0 = tid, r1 = tid + CL_THREADS, r2 = tid + 2 * CL_THREADS, r3 = tid + 3 * CL_THREADS;
                     if (r0 / RPC == rank) res0 = __ldcg(xmid + r0);
                     if (r1 / RPC == rank) res1 = __ldcg(xmid + r1);
@@ -752,16 +752,14 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                         sb = dot8f(st.b[c], g0, g1, sb);
                     }
                     if (bi % CB == CB - 1) {
-                        if (direct) {
-                            red_add_s64(xout + r, to_fx(sa) + (bi / CB == 0 ? res0 : res2));
-                            red_add_s64(xout + r + CL_THREADS, to_fx(sb) + (bi / CB == 0 ? res1 : res3));
-                        } else { dp[r] = sa; dp[r + CL_THREADS] = sb; }
+                        red_add_s64(xout + r, to_fx(sa) + (bi / CB == 0 ? res0 : res2));
+                        red_add_s64(xout + r + CL_THREADS, to_fx(sb) + (bi / CB == 0 ? res1 : res3));
                         sa = 0.0f; sb = 0.0f;
                     }
                 };
                 d_issue(s0, 0);
                 if (nb > 1) d_issue(s1, 1); else st_zero(s1);
-                __syncthreads();                                        /* gs complete; xs (= dp) no longer read */
+                __syncthreads();                                        /* gs complete */
                 PROF(10);
                 for (int bi = 0; bi < nb; bi += 2) {
                     d_consume(s0, bi);
@@ -770,27 +768,6 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 }
             }
             PROF(11);
-            if (!(a.flags & 256)) cl.sync();
-            PROF(12);
-            if (!(a.flags & 256)) {
-                /* rank r folds rows [r RPC, (r+1) RPC) over the 8 peers: lane group of 8 = the peers, fixed butterfly order */
-                const int peer = tid & 7, grp = tid >> 3;
-                if (grp < RPC / 4) {
-                    const int row = rank * RPC + 4 * grp;
-                    float4 v = *reinterpret_cast<const float4 *>(cl.map_shared_rank(dp, peer) + row);
-#pragma unroll
-                    for (int o = 4; o > 0; o >>= 1) {
-                        v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
-                        v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
-                    }
-                    if (peer < 4) {
-                        const float mine = peer == 0 ? v.x : peer == 1 ? v.y : peer == 2 ? v.z : v.w;
-                        long long fx = to_fx(mine);
-                        if (g == 0) fx += __ldcg(xmid + row + peer);
-                        red_add_s64(xout + row + peer, fx);
-                    }
-                }
-            }
             PROF(13);
             cl_barrier_arrive(a.bar, target, ncta);
             if (l + 1 < L && att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[l + 1]));
