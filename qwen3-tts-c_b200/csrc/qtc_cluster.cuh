@@ -47,6 +47,7 @@ namespace cg = cooperative_groups;
 #define CL_WARPS 16
 #define CL_ATT_CAP 64                 /* most positions per CTA the shared-memory K/V stage is sized for (contexts up to 8 x 64 = 512; longer ones read K/V through L2) */
 #define CL_REC 132                    /* partial record: max, sum, -, -, out[128] */
+#define CL_FULL_MAX 512               /* contexts up to this many positions: every CTA of a cluster walks the whole context (no partial records across CTAs) */
 #define CL_FX 4294967296.0f           /* 2^32 */
 #define CL_FX_INV 2.3283064365386963e-10f
 
@@ -216,10 +217,12 @@ __device__ __forceinline__ float dot4(const float4 a, const float4 b) {
     return d;
 }
 
-/* Attention of cluster g at position pos: positions [t0, t1) of this CTA, both query heads per K/V row.
- * qkv: this CTA's copy of the cluster's 512 projection outputs.  Leaves the CTA's partial records in cpart[2][CL_REC]. */
-__device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int t0, int t1, bool staged,
-                                             const float *qkv, float *wpart, float *cpart, const float *kvs, const float *aux) {
+/* Attention of cluster g at position pos: positions [t0, t1) of this CTA, both query heads per K/V row; the first nst of them sit in
+ * the shared-memory stage, the others are read through L2.  qkv: this CTA's copy of the cluster's 512 projection outputs.
+ * att == NULL (contexts split over the cluster's CTAs): the CTA's partial record goes into every peer's table cpart[rank][head];
+ * att != NULL (the CTA took the WHOLE context, t0 = 0, t1 = pos + 1): the finished 256 outputs are written there. */
+__device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const ClusterArgs &a, const LmDev &lm, int l, int g, int pos, int t0, int t1, int nst, bool append,
+                                             const float *qkv, float *wpart, float *cpart, float *att, const float *kvs, const float *aux) {
     const int cap = a.att_cap;
 #define APROF(i) do { if (a.prof && threadIdx.x == 0 && l == a.prof_layer) a.prof[blockIdx.x * 32 + (i)] = clock64(); } while (0)
     /* aux (staged with the K/V rows): [cos row | sin row | q_norm | k_norm], 128 floats each */
@@ -237,9 +240,11 @@ __device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const Cluste
         if (has_new) {
             k_new = cl_norm_rope(qkv + 256, k_norm, c4, s4, lm.eps);
             v_new = reinterpret_cast<const float4 *>(qkv + 384)[lane];
-            const size_t off = kv_off(a.table, pos, kvd);
-            *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
-            *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
+            if (append) {
+                const size_t off = kv_off(a.table, pos, kvd);
+                *reinterpret_cast<float4 *>(kc + off + lane * 4) = k_new;
+                *reinterpret_cast<float4 *>(vc + off + lane * 4) = v_new;
+            }
         }
         APROF(16);
         const float *Ks = kvs, *Vs = kvs + cap * 128;
@@ -254,7 +259,7 @@ __device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const Cluste
                 vr[j] = kr;
                 if (t < t1) {
                     if (t < pos) {
-                        if (staged) {
+                        if (t - t0 < nst) {
                             kr = *reinterpret_cast<const float4 *>(Ks + (size_t)(t - t0) * 128 + lane * 4);
                             vr[j] = *reinterpret_cast<const float4 *>(Vs + (size_t)(t - t0) * 128 + lane * 4);
                         } else {
@@ -322,13 +327,16 @@ __device__ __forceinline__ void cl_attention(cg::cluster_group &cl, const Cluste
             L = fmaf(lw, f, L);
             o = fmaf(ov, f, o);
         }
-        /* the CTA's record goes into every peer's table: after the cluster barrier each CTA folds the 8 records locally */
-        float *mine = cpart + (size_t)(cl.block_rank() * 2 + hh) * CL_REC;
+        if (att) att[hh * 128 + d] = __fdividef(o, L);      /* the whole context was this CTA's */
+        else {
+            /* the CTA's record goes into every peer's table: after the cluster barrier each CTA folds the 8 records locally */
+            float *mine = cpart + (size_t)(cl.block_rank() * 2 + hh) * CL_REC;
 #pragma unroll
-        for (int k = 0; k < CL_SIZE; k++) {
-            float *dst = cl.map_shared_rank(mine, k);
-            dst[4 + d] = o;
-            if (d == 0) { dst[0] = M; dst[1] = L; }
+            for (int k = 0; k < CL_SIZE; k++) {
+                float *dst = cl.map_shared_rank(mine, k);
+                dst[4 + d] = o;
+                if (d == 0) { dst[0] = M; dst[1] = L; }
+            }
         }
     }
     APROF(19);
@@ -523,16 +531,24 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
      * the CTA waits at the grid barrier before it: the K/V rows of this CTA's position range, the RoPE row, the head norms and the
      * input norm's weights.  (Read on demand, each of these was a DRAM round trip on the critical path: the 2.8 GB streamed per
      * step evict them from L2 every time.) */
-    auto stage_phase_a = [&](int ll, int pos, int t0, int t1, bool staged, int kst) {
+    auto stage_phase_a = [&](int ll, int pos, int t0, int t1, int rows, int kst) {
         const LmLayerDev &wl = lm.layer[ll];
         if (att_cluster) {
-            if (staged && t1 > t0) {
-                const int kvd = lm.kv_heads * 128;
-                const float *kc = a.kc + (size_t)ll * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)ll * a.kv_max * kvd + g * 128;
-                const int rows = (t1 < pos ? t1 : pos) - t0;
+            const int kvd = lm.kv_heads * 128;
+            const float *kc = a.kc + (size_t)ll * a.kv_max * kvd + g * 128, *vc = a.vc + (size_t)ll * a.kv_max * kvd + g * 128;
+            if (rows > 0) {
                 for (int i = tid; i < rows * 64; i += CL_THREADS) {
                     const int which = i >= rows * 32, j = which ? i - rows * 32 : i, r = j >> 5, c = j & 31;
                     cl_cp16(kvs + (size_t)which * a.att_cap * 128 + r * (which ? 128 : kst) + c * 4, (which ? vc : kc) + kv_off(a.table, t0 + r, kvd) + c * 4);
+                }
+            }
+            /* whole-context attention: the rows past the stage -> L2, every CTA of the cluster an eighth of them (128-byte lines: 4 per row and matrix) */
+            const int past = (t1 < pos ? t1 : pos) - t0 - rows;
+            if (rows > 0 && past > 0 && t0 == 0 && t1 == pos + 1) {
+                for (int i = tid; i < past * 8; i += CL_THREADS) {
+                    const int r = rows + (i >> 3), which = (i >> 2) & 1, c = i & 3;
+                    if ((r & (CL_SIZE - 1)) != rank) continue;
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"((which ? vc : kc) + kv_off(a.table, r, kvd) + c * 32));
                 }
             }
 #if CL_STAGE_AUX
@@ -554,12 +570,20 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
         const int n = pos + 1;
         const bool small_att = n <= 32 && (n - 1) * CL_KST_SMALL <= a.att_cap * 128;      /* every CTA takes both heads, one warp each */
         const int kst = small_att ? CL_KST_SMALL : 128;    /* K row stride in the stage */
-        const int chunk = small_att ? n : (n + CL_SIZE - 1) / CL_SIZE;
-        int t0 = small_att ? 0 : rank * chunk, t1 = small_att ? n : (t0 + chunk < n ? t0 + chunk : n);
+        /* Experiment (QTC_FUSED_FLAGS & 512; off): contexts up to CL_FULL_MAX positions walked WHOLE by every CTA of the cluster (a warp
+         * per position, the first att_cap rows from the stage, the others prefetched into L2 and read from there) instead of an eighth
+         * each - no partial records, no push into the peers, no cluster barrier, no fold of 8 records.  Parity green, but measured
+         * SLOWER at 190 positions (talker step 1.019 vs 0.899 ms on one box): 12 positions per warp, two thirds of them through L2,
+         * cost more than the exchange they save. */
+        const bool full_att = !small_att && n <= CL_FULL_MAX && (a.flags & 512);
+        const int chunk = small_att || full_att ? n : (n + CL_SIZE - 1) / CL_SIZE;
+        int t0 = small_att || full_att ? 0 : rank * chunk, t1 = small_att || full_att ? n : (t0 + chunk < n ? t0 + chunk : n);
         if (t0 > n) t0 = n;
         if (t1 < t0) t1 = t0;
-        const bool staged = small_att || chunk <= a.att_cap;
-        if (sp.G == 0) stage_phase_a(0, pos, t0, t1, staged, kst);
+        const bool staged = small_att || full_att || chunk <= a.att_cap;
+        const int cached = (t1 < pos ? t1 : pos) - t0;     /* rows of [t0, t1) that are in the cache (the last position is the new token) */
+        const int nst = !staged ? 0 : (small_att || cached < a.att_cap) ? cached : a.att_cap;       /* ... and how many of them wait in the stage */
+        if (sp.G == 0) stage_phase_a(0, pos, t0, t1, nst, kst);
         const float *x_in = a.x;                        /* fp32 input of layer 0 */
         if (sp.G > 0 && gstep >= 1 && sp.ptab[gstep - 1]) {
             /* ST_PROJECT_INPUT by table: the projected embedding of every code was computed at upload, and every CTA knows the code it
@@ -568,7 +592,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             x_in = sp.ptab[gstep - 1] + (size_t)s_codes[gstep - 1] * H;
             head_w = sp.heads[gstep - 1];
             if (att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
-            stage_phase_a(0, pos, t0, t1, staged, kst);
+            stage_phase_a(0, pos, t0, t1, nst, kst);
         } else if (sp.G > 0) {
             /* ST_PROJECT_INPUT: gather (every CTA for itself) -> input projection rows -> x (fp32, like the step's input) */
             __syncthreads();
@@ -587,7 +611,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             head_w = gstep >= 1 ? sp.heads[gstep - 1] : NULL;
             cl_barrier_arrive(a.bar, target, ncta);
             if (att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[0]));
-            stage_phase_a(0, pos, t0, t1, staged, kst);
+            stage_phase_a(0, pos, t0, t1, nst, kst);
             cl_barrier_wait(a.bar, target, a.err);
         }
         for (int l = 0; l < L; l++) {
@@ -623,17 +647,17 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
                 cl.sync();
                 PROF(3);
                 if (small_att) { if (warp < 2) cl_attention_small(a, lm, l, g, pos, warp, warp == 0 && rank == 0, qkv, att, kvs, aux, wpart + warp * 256); }
-                else cl_attention(cl, a, lm, l, g, pos, t0, t1, staged, qkv, wpart, cpart, kvs, aux);
+                else cl_attention(cl, a, lm, l, g, pos, t0, t1, nst, !full_att || rank == 0, qkv, wpart, cpart, full_att ? att : NULL, kvs, aux);
                 /* this CTA's rows of the O partial: RPC rows x 256 bf16; the first eight per warp are requested before the combine */
                 const uint16_t *wo = w.wo_t + ((size_t)g * H + (size_t)rank * RPC) * 256;
                 uint4 ow[8];
 #pragma unroll
                 for (int i = 0; i < 8; i++) ow[i] = ldg_stream(reinterpret_cast<const uint4 *>(wo + (size_t)(warp * 8 + i) * 256) + lane);
                 PROF(4);
-                if (small_att) __syncthreads();                         /* att[] is this CTA's own: no cluster barrier */
+                if (small_att || full_att) __syncthreads();             /* att[] is this CTA's own: no cluster barrier */
                 else cl.sync();
                 PROF(5);
-                if (!small_att) cl_attention_combine(cpart, att);
+                if (!small_att && !full_att) cl_attention_combine(cpart, att);
                 if (a.flags & 8) cl.sync();                             /* experiment: the third cluster barrier of the push variant */
                 PROF(6);
                 const float4 a0v = reinterpret_cast<const float4 *>(att)[2 * lane], a1v = reinterpret_cast<const float4 *>(att)[2 * lane + 1];
@@ -771,7 +795,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) k_lm_cluster(const ClusterArgs 
             PROF(13);
             cl_barrier_arrive(a.bar, target, ncta);
             if (l + 1 < L && att_cluster) cl_stream_prefetch(s0, s1, 2, HS, qkv_rows(lm.layer[l + 1]));
-            if (l + 1 < L) stage_phase_a(l + 1, pos, t0, t1, staged, kst);
+            if (l + 1 < L) stage_phase_a(l + 1, pos, t0, t1, nst, kst);
             cl_barrier_wait(a.bar, target, a.err);
             p++;
             PROF(14);

@@ -42,17 +42,18 @@ def test_fused_generate(cuda, fused_ctx, name, params, spk, lang):
     assert snr_db(want_pcm, pcm) >= 80.0
 
 
-@pytest.mark.parametrize("mode", [1, 2], ids=["fused", "cluster"])
-def test_fused_long_context_splits(cuda, orc, mode):
+@pytest.mark.parametrize("mode,n_pre,n_steps", [(1, 60, 150), (2, 60, 150), (2, 490, 40)], ids=["fused", "cluster", "cluster-past-512"])
+def test_fused_long_context_splits(cuda, orc, mode, n_pre, n_steps):
     """KV length past 64 / 128 / ... positions exercises the split-KV attention and its combine step:
-    teacher-forced talker steps on the `small` preset (16 Q / 8 KV heads of 128) against the oracle"""
+    teacher-forced talker steps on the `small` preset (16 Q / 8 KV heads of 128) against the oracle.  The cluster kernel stages a
+    CTA's eighth of the context in shared memory up to 8 x 64 = 512 positions and reads longer contexts through L2: the third
+    case crosses that boundary at step 22."""
     hm = get_model(orc, "small")
     H, V = hm.spec["talker"]["hidden"], hm.spec["talker"]["vocab"]
     ctx = cuda.qwen_tts_cuda_upload(C.byref(hm.desc), 1)
     assert ctx and cuda.qwen_tts_cuda_set_mode(ctx, mode) == 0
     s = orc.orc_create(hm.desc)
     rng = np.random.default_rng(0)
-    n_pre, n_steps = 60, 150
     emb = (rng.standard_normal((n_pre + n_steps, H)) * 0.5).astype(np.float32)
     orc.orc_reset(s)
     orc.orc_talker_prefill(s, B.fptr(emb), n_pre)
