@@ -299,7 +299,7 @@ __device__ int block_sample_thr(const float *lg, float *vv, int V, int top_k, fl
     for (int i = tid; i < V; i += NT) {
         const float v = __fdiv_rn(lg[i], temperature);
         vv[i] = v;
-        if (v > -1e30f && v < 1e30f) { s1 += v; s2 = fmaf(v, v, s2); cnt += 1.0f; }
+        if (v > -1e8f && v < 1e30f) { s1 += v; s2 = fmaf(v, v, s2); cnt += 1.0f; }      /* suppressed logits (-1e9) stay out of the moments: they only bracket the k-th value */
     }
     s1 = warp_sum(s1); s2 = warp_sum(s2); cnt = warp_sum(cnt);
     if (lane == 0) { S.ord_v[warp] = s1; S.ord_v[32 + warp] = s2; S.ord_v[64 + warp] = cnt; }
@@ -419,7 +419,8 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample(const SampleArgs a0) 
         lg[i] = l;
     }
     __syncthreads();
-    int tok = block_sample(lg, vv, V, a.cfg.top_k, a.cfg.top_p, a.cfg.temperature, a.rng, S, a.scratch_f, a.scratch_i);
+    /* the bracketing select (a third of the radix select's block barriers; falls back to it when its conditions do not hold) */
+    int tok = block_sample_thr(lg, vv, V, a.cfg.top_k, a.cfg.top_p, a.cfg.temperature, a.rng, S, a.scratch_f, a.scratch_i);
     if (a.role == 0) {
         const int eos = a.cfg.eos_id;
         if (a.st->fixed && tok == eos) {                       /* c/qwen_tts.c:1315-1321: second draw */
