@@ -335,11 +335,14 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
     {   /* idle-cluster L2 prefetch of the MLP weights (measured on B200, scripts/probe/pf_sweep.sh): the sub-talker takes all of it
          * unpaced (1837 -> 1784 us per frame); the talker's 75 MB per layer must not crowd out the attention block's own loads:
          * half of every slice, 2 us between a warp's requests (1030 -> 982 us per step; all of it unpaced: 1043) */
-        static int fr = -2, gp = -1;
-        if (fr == -2) { const char *e = getenv("QTC_PF_FRAC"); fr = e ? atoi(e) : -1; e = getenv("QTC_PF_GAP"); gp = e ? atoi(e) : -1; }
+        static int fr = -2, gp = -1, tfr = -1, tgp = -1;
+        if (fr == -2) {
+            const char *e = getenv("QTC_PF_FRAC"); fr = e ? atoi(e) : -1; e = getenv("QTC_PF_GAP"); gp = e ? atoi(e) : -1;
+            e = getenv("QTC_PF_TK_FRAC"); tfr = e ? atoi(e) : -1; e = getenv("QTC_PF_TK_GAP"); tgp = e ? atoi(e) : -1;     /* the talker's alone */
+        }
         const bool tk = lm == &c->talker;
-        a.pf_frac = fr >= 0 ? fr : (tk ? 50 : 100);
-        a.pf_gap = gp >= 0 ? gp : (tk ? 2000 : 0);
+        a.pf_frac = tk && tfr >= 0 ? tfr : fr >= 0 ? fr : (tk ? 50 : 100);
+        a.pf_gap = tk && tgp >= 0 ? tgp : gp >= 0 ? gp : (tk ? 2000 : 0);
     }
     int vec = lm->hidden;
     SubProg sp;
