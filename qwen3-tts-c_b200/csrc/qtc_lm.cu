@@ -336,14 +336,15 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
          * unpaced (1837 -> 1784 us per frame); the talker's 75 MB per layer must not crowd out the attention block's own loads:
          * three quarters of every slice, 2 us between a warp's requests (re-swept on the closing kernel, scripts/gpu_r2_pftk.sh, us per step:
          * 40 % 924, 50 % 900, 60 % 886, 70 % 882, 80 % 880, 90 % 900, 100 % 953; 80 % at 3 us: 1174; round 2's first sweep had 50 % ahead) */
-        static int fr = -2, gp = -1, tfr = -1, tgp = -1;
+        static int fr = -2, gp = -1, tfr = -1, tgp = -1, sfr = -1, sgp = -1;
         if (fr == -2) {
             const char *e = getenv("QTC_PF_FRAC"); fr = e ? atoi(e) : -1; e = getenv("QTC_PF_GAP"); gp = e ? atoi(e) : -1;
             e = getenv("QTC_PF_TK_FRAC"); tfr = e ? atoi(e) : -1; e = getenv("QTC_PF_TK_GAP"); tgp = e ? atoi(e) : -1;     /* the talker's alone */
+            e = getenv("QTC_PF_ST_FRAC"); sfr = e ? atoi(e) : -1; e = getenv("QTC_PF_ST_GAP"); sgp = e ? atoi(e) : -1;     /* the sub-talker's alone */
         }
         const bool tk = lm == &c->talker;
-        a.pf_frac = tk && tfr >= 0 ? tfr : fr >= 0 ? fr : (tk ? 75 : 100);
-        a.pf_gap = tk && tgp >= 0 ? tgp : gp >= 0 ? gp : (tk ? 2000 : 0);
+        a.pf_frac = tk && tfr >= 0 ? tfr : !tk && sfr >= 0 ? sfr : fr >= 0 ? fr : (tk ? 75 : 100);
+        a.pf_gap = tk && tgp >= 0 ? tgp : !tk && sgp >= 0 ? sgp : gp >= 0 ? gp : (tk ? 2000 : 0);
     }
     int vec = lm->hidden;
     SubProg sp;
