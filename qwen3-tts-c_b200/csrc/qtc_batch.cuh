@@ -972,6 +972,7 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
         bb->qcodes = (int *)balloc(bb, bb->qcodes_cap * 4);
         if (!bb->qcodes) return -1;
         c->dev_mallocs++;
+        QTC_CUDA(cudaDeviceSynchronize());               /* balloc clears on the NULL stream; the copies into the stash run on c->stream */
     }
     cudaEventRecord(c->ev2, c->stream);
     std::vector<int> row_utt(B, -1), row_end(B, 0), row_lim(B, 0), pos_host(B, QTC_Q_PARKED), nframes(n_utt, 0);
