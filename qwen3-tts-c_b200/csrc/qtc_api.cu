@@ -183,6 +183,7 @@ extern "C" void qwen_tts_cuda_release(qtc_ctx_t *c) {
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->g_front) cudaGraphExecDestroy(c->g_front);
     if (c->g_talker) cudaGraphExecDestroy(c->g_talker);
+    for (int i = 0; i < 4; i++) if (c->g_talker_b[i]) cudaGraphExecDestroy(c->g_talker_b[i]);
     qtc_batch_release(c);
     qtc_prefill_release(c);
     qtc_codec_release(c->codec);
@@ -211,6 +212,8 @@ extern "C" qtc_ctx_t *qwen_tts_cuda_upload(const qtc_model_desc_t *desc, int max
     c->bb = NULL; c->pf = NULL; c->batch_pieces = 3; c->dev_mallocs = 0;
     c->mode = 2; c->arith = 0;
     { const char *e = getenv("QTC_MODE"); if (e) c->mode = atoi(e) < 0 ? 0 : atoi(e) > 2 ? 2 : atoi(e); } c->graph_key = -1; c->g_front = NULL; c->g_talker = NULL; c->launches = 0;
+    for (int i = 0; i < 4; i++) c->g_talker_b[i] = NULL;
+    c->tk_reach_hint = 0;
     c->codec = NULL; c->codes = NULL; c->trailing = NULL; c->prefill = NULL; c->codes_cap = c->trailing_cap = c->prefill_cap = 0;
     memset(&c->tk, 0, sizeof(c->tk)); memset(&c->st, 0, sizeof(c->st)); memset(&c->perf, 0, sizeof(c->perf));
     memset(&c->talker, 0, sizeof(c->talker)); memset(&c->sub, 0, sizeof(c->sub));

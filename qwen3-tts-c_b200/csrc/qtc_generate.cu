@@ -100,7 +100,10 @@ extern "C" int qwen_tts_cuda_talker_forward(qtc_ctx_t *c, const float *input_emb
     if (pull_state(c)) return -1;
     if (qtc_ensure_kv(c, &c->tk, &c->talker, c->state_host->pos + 2)) return -1;
     QTC_CUDA(cudaMemcpyAsync(c->next_embed, input_embed, (size_t)c->H * 4, cudaMemcpyHostToDevice, c->stream));
-    if (qtc_talker_forward_dev(c, c->next_embed)) return -1;
+    c->tk_reach_hint = ((c->state_host->pos + 1 + 127) / 128) * 128;       /* the stage sized as the frame loop sizes it at this position */
+    const int frc = qtc_talker_forward_dev(c, c->next_embed);
+    c->tk_reach_hint = 0;
+    if (frc) return -1;
     if (logits) QTC_CUDA(cudaMemcpyAsync(logits, c->tk.logits, (size_t)c->talker.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
     QTC_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
@@ -179,8 +182,22 @@ static int ensure_graphs(qtc_ctx *c) {
     if (c->graph_key == key && c->g_front && c->g_talker) return 0;
     if (capture(c, &c->g_front, body_front)) return -1;
     if (capture(c, &c->g_talker, body_talker)) return -1;
+    for (int i = 0; i < 4; i++) if (c->g_talker_b[i]) { cudaGraphExecDestroy(c->g_talker_b[i]); c->g_talker_b[i] = NULL; }   /* captured under the old key */
     c->graph_key = key;
     return 0;
+}
+/* mode 2: the talker graph for steps that see at most 128 (bk + 1) positions (stage of 16 (bk + 1) positions per CTA); other modes
+ * and longer contexts: the one graph sized by the pages the utterance holds */
+static cudaGraphExec_t talker_graph_for(qtc_ctx *c, int positions) {
+    const int bk = (positions - 1) / 128;
+    if (c->mode != 2 || c->arith || bk < 0 || bk >= 3) return c->g_talker;
+    if (!c->g_talker_b[bk]) {
+        c->tk_reach_hint = 128 * (bk + 1);
+        const int rc = capture(c, &c->g_talker_b[bk], body_talker);
+        c->tk_reach_hint = 0;
+        if (rc) { c->g_talker_b[bk] = NULL; return c->g_talker; }
+    }
+    return c->g_talker_b[bk];
 }
 
 /* kernels per replay of each graph: run the body under a throwaway capture and read the launch counter */
@@ -285,6 +302,7 @@ int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, in
     }
     QTC_CUDA(cudaEventRecord(c->ev0, c->stream));
     int launched = 0;
+    const int pos0 = prefill_len;                    /* KV length after the prefill (the state was pushed with position 0) */
     const int poll = fixed > 0 ? limit : 8;          /* without a fixed budget, look for EOS every 8 frames */
     while (launched < limit) {
         const int upto = launched + poll < limit ? launched + poll : limit;
@@ -298,7 +316,8 @@ int qtc_generate_frames_resident(qtc_ctx *c, int prefill_len, int n_trailing, in
                 if (have >= want || launched + 1 == limit) { if (push_chunk(c, so, launched + 1)) return -1; }
                 deliver_chunks(c, so, false);
             }
-            if (launched + 1 < limit) { QTC_CUDA(cudaGraphLaunch(c->g_talker, c->stream)); c->launches += lt; }
+            /* the step after frame `launched` puts the token at position prefill_len + launched and sees that many + 1 positions */
+            if (launched + 1 < limit) { QTC_CUDA(cudaGraphLaunch(talker_graph_for(c, pos0 + launched + 1), c->stream)); c->launches += lt; }
         }
         if (pull_state(c)) return -1;
         if (so && fixed == 0) {

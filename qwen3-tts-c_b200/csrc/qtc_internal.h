@@ -183,6 +183,11 @@ struct qtc_ctx {
     std::vector<cudaEvent_t> frame_ev, chunk_ev;
     /* CUDA graphs of the frame loop (built lazily, keyed by params) */
     cudaGraphExec_t g_front, g_talker;
+    /* mode 2: the talker step's shared-memory K/V stage is sized for the positions the step can see, not for the pages the utterance
+     * holds (shared memory is L1 taken away: a stage of 32 instead of 64 positions per CTA is 0.9 % of the step at 190 positions):
+     * one captured graph per stage size, 128 positions apart, picked by the frame loop from the frame index */
+    cudaGraphExec_t g_talker_b[4];
+    int tk_reach_hint;            /* > 0: positions the next talker step(s) can see (set around a capture / a stage-API call) */
     int graph_key;
     int max_batch;
     BatchBuf *bb;                 /* lock-step batch state (qtc_batch.cu), allocated on first use */

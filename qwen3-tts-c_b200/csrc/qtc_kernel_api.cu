@@ -223,7 +223,10 @@ extern "C" double qwen_tts_cuda_bench_talker_step(qtc_ctx_t *c, int pos, int ite
         if (qtc_set_int(c, &c->state->pos, pos) || qtc_set_int(c, &c->state->done, 0)) return -1.0;
         if (do_flush && flush_l2(c->stream)) return -1.0;
         cudaEventRecord(e0, c->stream);
-        if (qtc_talker_forward_dev(c, c->next_embed)) return -1.0;
+        c->tk_reach_hint = ((pos + 1 + 127) / 128) * 128;      /* the K/V stage sized as the frame loop sizes it at this position (qtc_generate.cu: talker_graph_for) */
+        const int frc = qtc_talker_forward_dev(c, c->next_embed);
+        c->tk_reach_hint = 0;
+        if (frc) return -1.0;
         cudaEventRecord(e1, c->stream);
         if (cudaEventSynchronize(e1) != cudaSuccess) { qtc_set_error("bench: %s", cudaGetErrorString(cudaGetLastError())); return -1.0; }
         float ms = 0;

@@ -356,9 +356,11 @@ static int cluster_step(qtc_ctx *c, const LmDev *lm, LmBuffers *b, const int *po
     }
     a.xs_floats = (vec + 31) & ~31;
     /* K/V stage: positions this sequence can reach split 8 ways (the sub-talker: G + 2; the talker: the pages it holds), in steps of 16 */
-    const int reach = b == &c->tk ? c->kv.used[0] * QTC_KV_PAGE_POS : b->kv_max;
+    int reach = b == &c->tk ? c->kv.used[0] * QTC_KV_PAGE_POS : b->kv_max;
+    if (b == &c->tk && c->tk_reach_hint > 0 && c->tk_reach_hint < reach) reach = c->tk_reach_hint;
     a.att_cap = (((reach + CL_SIZE - 1) / CL_SIZE + 15) / 16) * 16;
     if (a.att_cap > CL_ATT_CAP) a.att_cap = CL_ATT_CAP;
+    { static int cap = -1; if (cap < 0) { const char *e = getenv("QTC_ATT_CAP"); cap = e ? atoi(e) : 0; } if (cap > 0 && b == &c->tk) a.att_cap = cap; }   /* A/B: the stage's size is shared memory taken from L1 */
     if (a.att_cap < 16) a.att_cap = 16;
     if (b != &c->tk && reach <= 64 && a.att_cap < 32) a.att_cap = 32;      /* the sub-talker: ranks 0 / 1 stage every earlier row (one warp per head) */
     while (prog && (size_t)(512 + 2 * lm->hidden + 2 * a.att_cap * 128) * 4 < sizeof(SampleSmem)) a.att_cap += 16;   /* the sampler's workspace overlays aux.. */
