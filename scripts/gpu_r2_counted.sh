@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: the switch / kernel variant this script measures is not in the library any more: apply profiles/r02_counted_accumulator_experiment.patch to re-run it
 # cluster kernel with counted accumulator words (the data is the barrier: no grid barrier between phases), and the prefill's split sums loaded in parallel
 TAG=${1:-counted}; OUT=gpurun_out/$TAG; mkdir -p $OUT
 timeout 150 python -m pytest tests/test_gpu_cluster.py -x -q > $OUT/pytest_cluster.log 2>&1; rc=$?; echo "pytest cluster exit $rc"; tail -5 $OUT/pytest_cluster.log

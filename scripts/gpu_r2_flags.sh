@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: flag 256 became the only path and QTC_PREFILL_STAGES was dropped after this run (profiles/README.md)
 # A/B on one box: cluster kernel with the down projection's partials added straight into the fixed-point accumulator (QTC_FUSED_FLAGS=256:
 # no cluster barrier / DSMEM fold in phase B), and the prefill GEMM with 2 pipeline stages (QTC_PREFILL_STAGES=2)
 TAG=${1:-flags}; OUT=gpurun_out/$TAG; mkdir -p $OUT

@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: the switch / kernel variant this script measures is not in the library any more: apply profiles/r02_l2_policy_experiment.patch to re-run it
 # L2 eviction policy on the cluster kernel's weight loads (QTC_L2_PIN = n: sub-talker layers < n evict_last, everything else - the talker's
 # stream included - evict_first; -1: no hint), same box; first the cluster kernel's parity tests on the tree as it stands
 TAG=${1:-l2pin}; OUT=gpurun_out/$TAG; mkdir -p $OUT

@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: the switch / kernel variant this script measures is not in the library any more: apply profiles/r02_mt2_experiment.patch to re-run it
 # k_gemm_tc with two weight-row tiles per CTA (MT = 2) and SM-count-sized K splits: parity, then config 4 and the prefill A/B (QTC_GEMM_MT=1 forces one tile)
 TAG=${1:-mt}; OUT=gpurun_out/$TAG; mkdir -p $OUT
 timeout 900 python -m pytest tests/test_gpu_batch.py tests/test_gpu_fused.py -x -q > $OUT/pytest.log 2>&1; echo "pytest exit $?"; tail -5 $OUT/pytest.log

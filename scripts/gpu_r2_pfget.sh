@@ -1,4 +1,5 @@
 #!/bin/bash
+# NOTE: the change this script measured (split sums loaded together) was not kept
 # prefill: K-split partial sums loaded together in the consumers (pf_get); parity of both prefill paths, then the latency object
 TAG=${1:-pfget}; OUT=gpurun_out/$TAG; mkdir -p $OUT
 timeout 600 python -m pytest tests/test_gpu_fused.py tests/test_gpu_parity.py tests/test_gpu_batch.py -x -q > $OUT/pytest.log 2>&1; echo "pytest exit $?"; tail -3 $OUT/pytest.log
