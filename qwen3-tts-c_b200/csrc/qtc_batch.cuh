@@ -470,6 +470,7 @@ struct BatchBuf {
     uint32_t *sub_rng;            /* [B] */
     uint32_t *seeds;              /* [B] bit pattern of (float)(sample_seed + b): RNG seed of utterance b */
     float *pcm_all = NULL; size_t pcm_cap = 0;   /* PCM of up to 64 decoded utterances, [.., max_tokens * 1920], on its way to the host */
+    float *qpcm = NULL; size_t qpcm_cap = 0;     /* generate_queue with overlapped decode: PCM of every request [n_utt, max_tokens * 1920] until the call ends */
     int *qcodes = NULL; size_t qcodes_cap = 0;   /* generate_queue: codes of retired utterances [n_utt, limit, G], kept for the decode at the end */
     float *scratch_f; int *scratch_i;  /* slow-path sampler scratch [B, vocab] */
     cudaGraphExec_t g_front, g_talker;
@@ -974,6 +975,24 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
         c->dev_mallocs++;
         QTC_CUDA(cudaDeviceSynchronize());               /* balloc clears on the NULL stream; the copies into the stash run on c->stream */
     }
+    /* QTC_QUEUE_OVERLAP (default on): a retired request is decoded right away on the second stream while the rows go on generating -
+     * the frame loop's kernels are short and latency-bound and leave most of the SMs to the vocoder; off: all decodes after the last frame */
+    static int overlap_env = -1;
+    if (overlap_env < 0) { const char *e = getenv("QTC_QUEUE_OVERLAP"); overlap_env = e ? atoi(e) : 1; }
+    const bool overlap = pcm_out && overlap_env != 0 && c->stream2 != NULL;
+    const size_t per = (size_t)max_tokens * 1920;
+    cudaEvent_t evq = NULL;
+    std::vector<int> qns(n_utt, 0);
+    if (overlap) {
+        if (bb->qpcm_cap < (size_t)n_utt * per) {
+            bb->qpcm_cap = (size_t)n_utt * per;
+            bb->qpcm = (float *)balloc(bb, bb->qpcm_cap * 4);
+            if (!bb->qpcm) { bb->qpcm_cap = 0; return -1; }
+            c->dev_mallocs++;
+            QTC_CUDA(cudaDeviceSynchronize());
+        }
+        QTC_CUDA(cudaEventCreateWithFlags(&evq, cudaEventDisableTiming));
+    }
     cudaEventRecord(c->ev2, c->stream);
     std::vector<int> row_utt(B, -1), row_end(B, 0), row_lim(B, 0), pos_host(B, QTC_Q_PARKED), nframes(n_utt, 0);
     std::vector<uint32_t> seed_host(B, 0);
@@ -1071,6 +1090,22 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
                 QTC_CUDA(cudaMemcpy(host_codes.data(), bb->codes + (size_t)b * bb->codes_cap * G, (size_t)n * G * 4, cudaMemcpyDeviceToHost));
                 memcpy(out_codes + (size_t)u * max_tokens * G, host_codes.data(), (size_t)n * G * 4);
                 if (pcm_out) QTC_CUDA(cudaMemcpyAsync(bb->qcodes + (size_t)u * limit * G, bb->codes + (size_t)b * bb->codes_cap * G, (size_t)n * G * 4, cudaMemcpyDeviceToDevice, c->stream));
+                if (overlap) {
+                    /* the codes are in the stash once the frame loop's stream reaches this point; the decode waits for exactly that */
+                    QTC_CUDA(cudaEventRecord(evq, c->stream));
+                    QTC_CUDA(cudaStreamWaitEvent(c->stream2, evq, 0));
+                    cudaStream_t keep = c->cstream;
+                    c->cstream = c->stream2;
+                    float *wav = NULL;
+                    int L = -1;
+                    if (qtc_codec_stream_begin(c, n) == 0) L = qtc_codec_stream_push(c, bb->qcodes + (size_t)u * limit * G, n, &wav);
+                    if (L > 0 && (size_t)L <= per) {
+                        if (cudaMemcpyAsync(bb->qpcm + (size_t)u * per, wav, (size_t)L * 4, cudaMemcpyDeviceToDevice, c->stream2) != cudaSuccess) L = -1;
+                    } else L = -1;
+                    c->cstream = keep;
+                    if (L <= 0) { cudaEventDestroy(evq); qtc_set_error("generate_queue: decode of request %d failed", u); return -1; }
+                    qns[u] = L;
+                }
             }
             row_utt[b] = -1;
             freed.push_back(b);
@@ -1091,7 +1126,20 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->perf.talker_ms = ms; c->perf.codec_tokens = total_frames;
-    if (pcm_out) {
+    if (overlap) {
+        /* every decode is already enqueued on the second stream: one more hop to the host */
+        cudaEventRecord(c->ev3, c->stream2);
+        bool full = true;
+        for (int u = 0; u < n_utt; u++) full = full && (size_t)qns[u] == per;
+        if (full) QTC_CUDA(cudaMemcpyAsync(pcm_out, bb->qpcm, (size_t)n_utt * per * 4, cudaMemcpyDeviceToHost, c->stream2));
+        else for (int u = 0; u < n_utt; u++) if (qns[u] > 0) QTC_CUDA(cudaMemcpyAsync(pcm_out + (size_t)u * per, bb->qpcm + (size_t)u * per, (size_t)qns[u] * 4, cudaMemcpyDeviceToHost, c->stream2));
+        QTC_CUDA(cudaStreamSynchronize(c->stream2));
+        cudaEventDestroy(evq);
+        c->last_pcm_dev = NULL; c->last_pcm_n = 0;
+        float dms = 0;
+        cudaEventElapsedTime(&dms, c->ev2, c->ev3);
+        c->perf.device_ms = dms;
+    } else if (pcm_out) {
         if (b_decode_all(c, bb, n_utt, bb->qcodes, (size_t)limit * G, nframes.data(), pcm_out, max_tokens)) return -1;
         float dms = 0;
         cudaEventElapsedTime(&dms, c->ev2, c->ev3);
