@@ -981,6 +981,7 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
     if (overlap_env < 0) { const char *e = getenv("QTC_QUEUE_OVERLAP"); overlap_env = e ? atoi(e) : 1; }
     const bool overlap = pcm_out && overlap_env != 0 && c->stream2 != NULL;
     const size_t per = (size_t)max_tokens * 1920;
+    struct EvGuard { cudaEvent_t e = NULL; ~EvGuard() { if (e) cudaEventDestroy(e); } } evg;      /* destroyed on every way out */
     cudaEvent_t evq = NULL;
     std::vector<int> qns(n_utt, 0);
     if (overlap) {
@@ -991,7 +992,8 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
             c->dev_mallocs++;
             QTC_CUDA(cudaDeviceSynchronize());
         }
-        QTC_CUDA(cudaEventCreateWithFlags(&evq, cudaEventDisableTiming));
+        QTC_CUDA(cudaEventCreateWithFlags(&evg.e, cudaEventDisableTiming));
+        evq = evg.e;
     }
     cudaEventRecord(c->ev2, c->stream);
     std::vector<int> row_utt(B, -1), row_end(B, 0), row_lim(B, 0), pos_host(B, QTC_Q_PARKED), nframes(n_utt, 0);
@@ -1103,7 +1105,7 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
                         if (cudaMemcpyAsync(bb->qpcm + (size_t)u * per, wav, (size_t)L * 4, cudaMemcpyDeviceToDevice, c->stream2) != cudaSuccess) L = -1;
                     } else L = -1;
                     c->cstream = keep;
-                    if (L <= 0) { cudaEventDestroy(evq); qtc_set_error("generate_queue: decode of request %d failed", u); return -1; }
+                    if (L <= 0) { qtc_set_error("generate_queue: decode of request %d failed", u); return -1; }
                     qns[u] = L;
                 }
             }
@@ -1134,7 +1136,6 @@ extern "C" int qwen_tts_cuda_generate_queue(qtc_ctx_t *c, int n_utt, int rows, c
         if (full) QTC_CUDA(cudaMemcpyAsync(pcm_out, bb->qpcm, (size_t)n_utt * per * 4, cudaMemcpyDeviceToHost, c->stream2));
         else for (int u = 0; u < n_utt; u++) if (qns[u] > 0) QTC_CUDA(cudaMemcpyAsync(pcm_out + (size_t)u * per, bb->qpcm + (size_t)u * per, (size_t)qns[u] * 4, cudaMemcpyDeviceToHost, c->stream2));
         QTC_CUDA(cudaStreamSynchronize(c->stream2));
-        cudaEventDestroy(evq);
         c->last_pcm_dev = NULL; c->last_pcm_n = 0;
         float dms = 0;
         cudaEventElapsedTime(&dms, c->ev2, c->ev3);
