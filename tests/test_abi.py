@@ -51,3 +51,27 @@ int main(void){ printf("%zu %zu %zu %zu %zu\n", sizeof(qtc_lm_t), sizeof(qtc_cod
         got = [int(x) for x in subprocess.check_output([os.path.join(d, "s")]).split()]
     want = [C.sizeof(B.Lm), C.sizeof(B.Codec), C.sizeof(B.ModelDesc), C.sizeof(B.GenParams), C.sizeof(B.Perf)]
     assert got == want
+
+
+def test_binding_arity_matches_header():
+    """every function the ctypes harness declares argtypes for takes as many arguments as its prototype in the header (the queue
+    entry point gained one in the course of round 2: a mirror that lags would pass garbage pointers)"""
+    src = open(os.path.join(ROOT, "include", "qwen_tts_cuda.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(qwen_tts_cuda_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
+        args = m.group(2).strip()
+        depth, n = 0, 0 if args in ("", "void") else 1
+        for ch in args:
+            depth += ch == "("
+            depth -= ch == ")"
+            n += ch == "," and depth == 0
+        protos[m.group(1)] = n
+    lib = B.load_cuda()
+    checked = 0
+    for name, n in protos.items():
+        fn = getattr(lib, name)
+        if fn.argtypes is not None:
+            assert len(fn.argtypes) == n, (name, len(fn.argtypes), n)
+            checked += 1
+    assert checked >= 20, checked
